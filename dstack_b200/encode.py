@@ -1,0 +1,522 @@
+"""Host-side encoding: offers -> dictionary-encoded table, job filters -> predicate records.
+
+Everything the GPU compares is a small integer.  Each attribute of the offers is replaced
+by its ordinal among the sorted distinct values of that attribute in the table, and each
+job bound is translated to an ordinal with the same IEEE-754 double comparisons the
+reference performs in Python (``gpuhunt.matches``), so the device
+never compares a float and results are bit-exact by construction.
+
+Row order: the table is stored in the order the reference returns offers --
+``heapq.merge`` of price-sorted per-backend lists in project-backend order followed by a
+stable partition on ``availability.is_available()``
+(``server/services/backends/__init__.py:449-451``).  That is a stable sort of the source
+list by ``(not available, price)``; a job's ``max_price`` then is a row cut-off in each of
+the two segments and "first k by price" is "first k matching rows".
+
+Nothing here evaluates a (job, offer) pair: this module only builds inputs for
+``libdsmatch.so``.
+"""
+
+from __future__ import annotations
+
+import dataclasses
+from dataclasses import dataclass, field
+from typing import Any, Dict, List, Optional, Sequence, Tuple, Union
+
+import numpy as np
+
+from ._gpuhunt import AcceleratorVendor, compute_capability_of
+from .models import BackendType, InstanceStatus
+
+# codes -------------------------------------------------------------------------------------
+
+BACKEND_CODES: Dict[str, int] = {b.value: i for i, b in enumerate(BackendType)}
+NO_BACKEND_CODE = len(BACKEND_CODES)  # pool rows may have backend = None
+VENDOR_CODES: Dict[Optional[str], int] = {None: 0, "nvidia": 1, "amd": 2, "google": 3, "intel": 4}
+STATUS_CODES: Dict[str, int] = {s.value: i for i, s in enumerate(InstanceStatus)}
+NO_STATUS_CODE = len(STATUS_CODES)
+
+# flag bits of the backend/flags dictionary
+FLAG_UNREACHABLE = 1
+FLAG_BLOCKS_UNKNOWN = 2   # total_blocks is None (still provisioning)
+FLAG_SHARED = 4           # total_blocks > 1
+FLAG_NO_OFFER = 8         # instance.offer is None
+FLAG_AUTO_DIVISIBLE = 16  # is_divisible_into_blocks(cpu, gpu, "auto")[0]
+
+KIND_RANGE, KIND_BITSET, KIND_GPU, KIND_BK = 1, 2, 3, 4
+COLF_NULL_PASSES = 1
+GPUF_MEM_BOUNDED, GPUF_CC_BOUNDED, GPUF_NAME_ANY = 1, 2, 8
+NO_ROW = 0xFFFFFFFF
+MAX_CODES = 65535
+LUT_THRESHOLD = 1024  # set columns with more dictionary entries go through a per-call remap
+
+
+def backend_code(b: Any) -> int:
+    if b is None:
+        return NO_BACKEND_CODE
+    return BACKEND_CODES[b.value if hasattr(b, "value") else str(b)]
+
+
+def vendor_code(v: Any) -> int:
+    if v is None:
+        return 0
+    return VENDOR_CODES[v.value if hasattr(v, "value") else str(v).lower()]
+
+
+def _cc_key(cc: Optional[Tuple[int, int]]) -> int:
+    return -1 if cc is None else int(cc[0]) * 1000 + int(cc[1])
+
+
+# offers in columnar form -------------------------------------------------------------------
+
+
+@dataclass
+class ShapeTable:
+    """Distinct resource shapes (instance types).  All resource predicates depend on the
+    shape only, so dictionaries are built over shapes, not offers."""
+
+    cpus: np.ndarray            # int64
+    memory_gib: np.ndarray      # float64: memory_mib / 1024 (offers) or CatalogItem.memory
+    disk_gib: np.ndarray        # float64, NaN = no disk size on the item (always passes)
+    gpu_count: np.ndarray       # int64
+    gpu_vendor: np.ndarray      # int8 vendor code, 0 = none
+    gpu_name: List[Optional[str]]  # original casing; None without GPUs
+    gpu_memory_gib: np.ndarray  # float64, NaN without GPUs
+
+    def __len__(self) -> int:
+        return len(self.cpus)
+
+
+@dataclass
+class OfferColumns:
+    """Offers in SOURCE order (per-backend lists concatenated in project-backend order)."""
+
+    shapes: ShapeTable
+    shape_id: np.ndarray        # int32 -> shapes
+    price: np.ndarray           # float64
+    spot: np.ndarray            # bool
+    available: np.ndarray       # bool: availability.is_available()
+    backend: np.ndarray         # int8: code of offer.backend
+    src_backend: np.ndarray     # int8: code of the Backend object that served the offer
+    region_id: np.ndarray       # int32 -> regions
+    regions: List[str]
+    itype_id: np.ndarray        # int32 -> itypes; -1 = no instance type known (passes)
+    itypes: List[str]
+    # pool-only admin attributes (None for catalog tables)
+    status: Optional[np.ndarray] = None      # int8 status code
+    flags: Optional[np.ndarray] = None       # int16 FLAG_* bits
+    fleet_id: Optional[np.ndarray] = None    # int32 -> fleets, -1 = no fleet
+    fleets: List[Any] = field(default_factory=list)
+    name_id: Optional[np.ndarray] = None     # int32 -> names
+    names: List[str] = field(default_factory=list)
+    zone_id: Optional[np.ndarray] = None     # int32 -> zones, -1 = unknown zone (passes)
+    zones: List[str] = field(default_factory=list)
+
+    def __len__(self) -> int:
+        return len(self.price)
+
+    @property
+    def is_pool(self) -> bool:
+        return self.fleet_id is not None
+
+
+def _auto_divisible(cpus: np.ndarray, gpu_eff: np.ndarray) -> np.ndarray:
+    """``is_divisible_into_blocks(cpu, gpu, "auto")[0]`` (server/services/offers.py:121-136)."""
+    b = np.where(gpu_eff == 0, cpus, np.minimum(cpus, gpu_eff))
+    ok = b >= 1
+    bs = np.where(ok, b, 1)
+    return ok & (cpus % bs == 0) & (gpu_eff % bs == 0)
+
+
+# encoded table ---------------------------------------------------------------------------
+
+
+@dataclass
+class Column:
+    name: str
+    kind: int
+    card: int                      # dictionary entries incl. null / dead entries
+    flags: int = 0
+    values: Optional[np.ndarray] = None   # RANGE: sorted distinct values (float64)
+    lookup: Optional[Dict[Any, int]] = None  # BITSET: value -> code
+
+
+@dataclass
+class EncodedTable:
+    """Device-ready table plus the host-side facts needed to pack jobs and map rows back."""
+
+    n_src: int
+    n_rows: int               # physical rows (padded)
+    split_row: int
+    n_avail: int
+    n_cols: int               # 8 or 16
+    rows: np.ndarray          # uint16 [n_rows, n_cols]
+    price: np.ndarray         # float64 [n_rows] (NaN on padding rows)
+    perm: np.ndarray          # int64 [n_rows]: physical row -> source index, -1 on padding
+    columns: List[Column]
+    gpu_entries: np.ndarray   # uint32 [n_gpu, 3]
+    bk_entries: np.ndarray    # uint32 [n_bk, 2]
+    gpu_dict: Dict[str, Any]  # count / memory / total / cc value arrays, name -> id
+    price_a: np.ndarray       # prices of the first segment (ascending)
+    price_b: np.ndarray       # prices of the second segment (ascending)
+    is_pool: bool
+
+    def col(self, name: str) -> int:
+        for i, c in enumerate(self.columns):
+            if c.name == name:
+                return i
+        raise KeyError(name)
+
+
+def _ordinals(values: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    uniq, inv = np.unique(values, return_inverse=True)
+    return uniq.astype(np.float64), inv.astype(np.int64)
+
+
+def _check_card(name: str, n: int) -> None:
+    if n > MAX_CODES:
+        raise ValueError(f"column {name!r} has {n} distinct values; the u16 row format allows {MAX_CODES}")
+
+
+def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True) -> EncodedTable:
+    n = len(oc)
+    sh = oc.shapes
+    price = np.asarray(oc.price, dtype=np.float64)
+    avail = np.asarray(oc.available, dtype=bool)
+    if np.isnan(price).any():
+        raise ValueError("NaN price")
+
+    if check_sorted_backends and n > 1 and not oc.is_pool:
+        # heapq.merge equals a sort only if every backend's list is price-sorted (gpuhunt's
+        # contract, contributing/GPUHUNT.md:33-35).  Refuse anything else loudly.
+        src = np.asarray(oc.src_backend)
+        same = src[1:] == src[:-1]
+        if (same & (price[1:] < price[:-1])).any():
+            raise ValueError("offers of a backend are not sorted by price; heapq.merge order would be "
+                             "job-dependent (server/services/backends/__init__.py:449)")
+        # lists must be contiguous per backend for source order to mean (backend_pos, position)
+        starts = np.concatenate(([True], ~same))
+        if len(np.unique(src[starts])) != int(starts.sum()):
+            raise ValueError("offers of one backend must be contiguous in the source list")
+
+    # ---- resource dictionaries over shapes
+    cpu_vals, cpu_ord = _ordinals(np.asarray(sh.cpus, dtype=np.float64))
+    mem_vals, mem_ord = _ordinals(np.asarray(sh.memory_gib, dtype=np.float64))
+    disk = np.asarray(sh.disk_gib, dtype=np.float64)
+    disk_null = np.isnan(disk)
+    disk_vals, disk_ord_nn = _ordinals(disk[~disk_null]) if (~disk_null).any() else (np.zeros(0), np.zeros(0, np.int64))
+    disk_ord = np.full(len(sh), len(disk_vals), dtype=np.int64)  # null entry = last
+    disk_ord[~disk_null] = disk_ord_nn
+    for nm, vals in (("cpu", cpu_vals), ("memory", mem_vals), ("disk", disk_vals)):
+        _check_card(nm, len(vals) + 1)
+
+    # ---- accelerator configuration dictionary
+    gcount = np.asarray(sh.gpu_count, dtype=np.int64)
+    has_gpu = gcount > 0
+    gmem = np.where(has_gpu, np.asarray(sh.gpu_memory_gib, dtype=np.float64), 0.0)
+    gmem = np.where(np.isnan(gmem), 0.0, gmem)
+    # vendor / name are taken as the item states them, also on items without GPUs: the
+    # reference tests them independently of the count (App. A.1 items 7, 8, 10)
+    gvend = np.asarray(sh.gpu_vendor, dtype=np.int64)
+    lower_names: Dict[str, int] = {}
+    name_id = np.full(len(sh), -1, dtype=np.int64)
+    for i, nm in enumerate(sh.gpu_name):
+        if nm is not None:
+            name_id[i] = lower_names.setdefault(nm.lower(), len(lower_names))
+    cnt_vals, cnt_ord = _ordinals(gcount.astype(np.float64))
+    gm_vals, gm_ord = _ordinals(gmem)
+    total = np.where(has_gpu, gcount.astype(np.float64) * gmem, 0.0)  # int * float, as Python does
+    tot_vals, tot_ord = _ordinals(total)
+    cc_key = np.array([_cc_key(compute_capability_of(nm)) for nm in sh.gpu_name], dtype=np.int64)
+    cc_vals = np.unique(cc_key[cc_key >= 0]).astype(np.float64)
+    cc_ord = np.where(cc_key >= 0, np.searchsorted(cc_vals, cc_key.astype(np.float64)), 0xFFFF)
+    gkey = np.stack([cnt_ord, gm_ord, gvend, name_id, has_gpu.astype(np.int64)], axis=1)
+    guniq, ginv = np.unique(gkey, axis=0, return_inverse=True)
+    ginv = np.asarray(ginv).reshape(-1)
+    _check_card("gpu", len(guniq))
+    # representative shape of each entry, to read total / cc ordinals
+    rep = np.zeros(len(guniq), dtype=np.int64)
+    rep[ginv] = np.arange(len(sh))
+    gpu_entries = np.zeros((len(guniq), 3), dtype=np.uint32)
+    e_name = np.where(guniq[:, 3] >= 0, guniq[:, 3], 0xFFFF)
+    gpu_entries[:, 0] = (guniq[:, 0] | (guniq[:, 1] << 16)).astype(np.uint32)
+    gpu_entries[:, 1] = (tot_ord[rep] | (cc_ord[rep] << 16)).astype(np.uint32)
+    gpu_entries[:, 2] = (e_name | (guniq[:, 2] << 16) | (guniq[:, 4] << 24)).astype(np.uint32)
+
+    # ---- backend / spot / status / flags dictionary (entry 0 = dead)
+    sid = np.asarray(oc.shape_id, dtype=np.int64)
+    gpu_eff = np.where(np.asarray(sh.gpu_vendor)[sid] == VENDOR_CODES["google"],
+                       np.minimum(gcount[sid], 1), gcount[sid])  # TPUs count as one (offers.py:110-112)
+    flags = np.zeros(n, dtype=np.int64) if oc.flags is None else np.asarray(oc.flags, dtype=np.int64).copy()
+    flags |= np.where(_auto_divisible(np.asarray(sh.cpus, dtype=np.int64)[sid], gpu_eff), FLAG_AUTO_DIVISIBLE, 0)
+    status = np.full(n, NO_STATUS_CODE, dtype=np.int64) if oc.status is None else np.asarray(oc.status, dtype=np.int64)
+    bkey = (np.asarray(oc.src_backend, dtype=np.int64) | (np.asarray(oc.backend, dtype=np.int64) << 5)
+            | (np.asarray(oc.spot, dtype=np.int64) << 10) | (status << 11) | (flags << 14))
+    present = np.unique(bkey)
+    _check_card("bk", len(present) + 1)
+    bk_code = np.searchsorted(present, bkey) + 1
+    bk_entries = np.zeros((len(present) + 1, 2), dtype=np.uint32)
+    bk_entries[1:, 0] = ((present & 31) | (((present >> 5) & 31) << 8) | (((present >> 10) & 1) << 16)
+                         | (((present >> 11) & 7) << 24)).astype(np.uint32)
+    bk_entries[1:, 1] = (present >> 14).astype(np.uint32)
+
+    # ---- set columns: code = id, plus one entry for "unknown" (-1) where that passes
+    def set_codes(ids: np.ndarray, card: int, name: str) -> Tuple[np.ndarray, int]:
+        ids = np.asarray(ids, dtype=np.int64)
+        _check_card(name, card + 1)
+        return np.where(ids < 0, card, ids), card + 1  # last entry = unknown
+
+    columns: List[Column] = [
+        Column("cpu", KIND_RANGE, len(cpu_vals), values=cpu_vals),
+        Column("memory", KIND_RANGE, len(mem_vals), values=mem_vals),
+        Column("disk", KIND_RANGE, len(disk_vals) + 1, flags=COLF_NULL_PASSES, values=disk_vals),
+        Column("gpu", KIND_GPU, len(guniq)),
+        Column("bk", KIND_BK, len(present) + 1),
+    ]
+    per_row: List[np.ndarray] = [cpu_ord[sid], mem_ord[sid], disk_ord[sid], ginv[sid], bk_code]
+    reg_codes, reg_card = set_codes(oc.region_id, len(oc.regions), "region")
+    it_codes, it_card = set_codes(oc.itype_id, len(oc.itypes), "itype")
+    columns += [
+        Column("region", KIND_BITSET, reg_card, lookup={r: i for i, r in enumerate(oc.regions)}),
+        Column("itype", KIND_BITSET, it_card, lookup={r: i for i, r in enumerate(oc.itypes)}),
+    ]
+    per_row += [reg_codes, it_codes]
+    if oc.is_pool:
+        fl_codes, fl_card = set_codes(oc.fleet_id, len(oc.fleets), "fleet")
+        nm_codes, nm_card = set_codes(oc.name_id, len(oc.names), "name")
+        zn_codes, zn_card = set_codes(oc.zone_id, len(oc.zones), "zone")
+        columns += [
+            Column("fleet", KIND_BITSET, fl_card, lookup={r: i for i, r in enumerate(oc.fleets)}),
+            Column("name", KIND_BITSET, nm_card, lookup={r: i for i, r in enumerate(oc.names)}),
+            Column("zone", KIND_BITSET, zn_card, lookup={r: i for i, r in enumerate(oc.zones)}),
+        ]
+        per_row += [fl_codes, nm_codes, zn_codes]
+    n_cols = 8 if len(columns) <= 8 else 16
+
+    # ---- row order and padding
+    order = np.lexsort((price, ~avail))  # stable: ties keep source order
+    n_avail = int(avail.sum())
+    split_row = (n_avail + 31) // 32 * 32
+    n_b = n - n_avail
+    n_rows = split_row + (n_b + 31) // 32 * 32
+    if n_rows == 0:
+        n_rows = 32
+        split_row = 32
+    perm = np.full(n_rows, -1, dtype=np.int64)
+    perm[:n_avail] = order[:n_avail]
+    perm[split_row:split_row + n_b] = order[n_avail:]
+    live = perm >= 0
+    rows = np.zeros((n_rows, n_cols), dtype=np.uint16)  # padding rows: bk code 0 = dead entry
+    src = perm[live]
+    for c, codes in enumerate(per_row):
+        rows[live, c] = codes[src].astype(np.uint16)
+    price_phys = np.full(n_rows, np.nan)
+    price_phys[live] = price[src]
+
+    return EncodedTable(
+        n_src=n, n_rows=n_rows, split_row=split_row, n_avail=n_avail, n_cols=n_cols, rows=rows,
+        price=price_phys, perm=perm, columns=columns, gpu_entries=gpu_entries, bk_entries=bk_entries,
+        gpu_dict=dict(count=cnt_vals, memory=gm_vals, total=tot_vals, cc=cc_vals, names=lower_names),
+        price_a=price[order[:n_avail]], price_b=price[order[n_avail:]], is_pool=oc.is_pool,
+    )
+
+
+# jobs -------------------------------------------------------------------------------------
+
+
+@dataclass
+class JobColumns:
+    """J job filters in columnar form.  NaN = bound not set.  Sets are CSR over the TABLE's
+    dictionary ids (``*_ptr`` length J+1; an id of -1 stands for a value the table does not
+    contain and matches nothing); ``*_any`` marks "no filter"."""
+
+    n: int
+    max_price: np.ndarray
+    spot: np.ndarray                 # int8: -1 either, 0 on-demand, 1 spot
+    cpu: np.ndarray                  # float64 [J,2] (min, max)
+    memory: np.ndarray
+    disk: np.ndarray
+    gpu_count: np.ndarray
+    gpu_memory: np.ndarray
+    gpu_total: np.ndarray
+    gpu_vendor: np.ndarray           # int8 vendor code, 0 = no filter
+    cc_min: np.ndarray               # int64 key major*1000+minor, -1 = no bound
+    gpu_name_any: np.ndarray         # bool
+    gpu_name_ptr: np.ndarray
+    gpu_name_ids: np.ndarray
+    src_backend_mask: np.ndarray     # uint32
+    off_backend_mask: np.ndarray     # uint32
+    exclude_not_available: np.ndarray  # bool
+    region_any: np.ndarray
+    region_ptr: np.ndarray
+    region_ids: np.ndarray
+    itype_any: np.ndarray
+    itype_ptr: np.ndarray
+    itype_ids: np.ndarray
+    # flags that rows must / must not carry, and the statuses accepted (pool filters, blocks=auto)
+    flag_req: Optional[np.ndarray] = None     # uint16
+    flag_forbid: Optional[np.ndarray] = None  # uint16
+    status_mask: Optional[np.ndarray] = None  # uint8 bit per status code; 0xFF any
+    fleet_any: Optional[np.ndarray] = None
+    fleet_ids: Optional[np.ndarray] = None    # int64 [J] single id (or -1)
+    name_any: Optional[np.ndarray] = None
+    name_ids: Optional[np.ndarray] = None
+    zone_any: Optional[np.ndarray] = None
+    zone_ptr: Optional[np.ndarray] = None
+    zone_ids: Optional[np.ndarray] = None
+
+
+def _range_words(vals: np.ndarray, bounds: np.ndarray) -> np.ndarray:
+    """(min,max) float bounds -> packed inclusive ordinal range ``lo | hi<<16``.
+
+    lo = first i with vals[i] >= min, hi = last i with vals[i] <= max: exactly the set the
+    reference's ``not (v < min) and not (v > max)`` keeps.  Empty -> (1, 0)."""
+    lo_b, hi_b = bounds[:, 0], bounds[:, 1]
+    lo = np.where(np.isnan(lo_b), 0, np.searchsorted(vals, np.nan_to_num(lo_b), side="left"))
+    hi = np.where(np.isnan(hi_b), len(vals) - 1, np.searchsorted(vals, np.nan_to_num(hi_b), side="right") - 1)
+    empty = (lo > hi) | (len(vals) == 0)
+    lo = np.where(empty, 1, lo).astype(np.uint32)
+    hi = np.where(empty, 0, hi).astype(np.uint32)
+    return lo | (hi << np.uint32(16))
+
+
+def _bitset_from_csr(any_mask: np.ndarray, ptr: np.ndarray, ids: np.ndarray, n_words: int,
+                     pass_bits: Sequence[int] = ()) -> np.ndarray:
+    """[J, n_words] uint32 with one bit per accepted code; ``any`` rows are all ones."""
+    j = len(any_mask)
+    out = np.zeros((j, n_words), dtype=np.uint32)
+    if len(ids):
+        owner = np.repeat(np.arange(j), np.diff(ptr))
+        ok = ids >= 0
+        o, i = owner[ok], ids[ok].astype(np.int64)
+        np.bitwise_or.at(out, (o, i >> 5), (np.uint32(1) << (i & 31).astype(np.uint32)))
+    for b in pass_bits:
+        out[:, b >> 5] |= np.uint32(1) << np.uint32(b & 31)
+    out[any_mask] = np.uint32(0xFFFFFFFF)
+    return out
+
+
+@dataclass
+class PackedJobs:
+    records: np.ndarray            # uint32 [J, rec_words]
+    layout: Dict[str, Any]         # n_used, kind[], card[], flags[], aux[], rec_off[], rec_words
+    luts: Dict[int, np.ndarray]    # column -> uint16 remap, uploaded per call
+
+
+def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
+    j = jc.n
+    parts: List[np.ndarray] = []
+    offs: List[int] = []
+    kinds: List[int] = []
+    cards: List[int] = []
+    cflags: List[int] = []
+    aux: List[int] = []
+    luts: Dict[int, np.ndarray] = {}
+
+    # words 0,1: row cut-offs (max_price and exclude_not_available)
+    mp = np.asarray(jc.max_price, dtype=np.float64)
+    cut_a = np.where(np.isnan(mp), t.split_row, np.searchsorted(t.price_a, np.nan_to_num(mp), side="right"))
+    cut_b = np.where(np.isnan(mp), t.n_rows, t.split_row + np.searchsorted(t.price_b, np.nan_to_num(mp), side="right"))
+    cut_b = np.where(np.asarray(jc.exclude_not_available, dtype=bool), t.split_row, cut_b)
+    parts.append(np.stack([cut_a, cut_b], axis=1).astype(np.uint32))
+    pos = 2
+
+    def add(words: np.ndarray, kind: int, card: int, flags: int = 0, ax: int = 0) -> None:
+        nonlocal pos
+        words = np.ascontiguousarray(words, dtype=np.uint32).reshape(j, -1)
+        parts.append(words)
+        offs.append(pos)
+        kinds.append(kind)
+        cards.append(card)
+        cflags.append(flags)
+        aux.append(ax)
+        pos += words.shape[1]
+
+    def add_set(col_idx: int, any_mask, ptr, ids, unknown_passes: bool) -> None:
+        col = t.columns[col_idx]
+        card = col.card  # ids 0..card-2, last = unknown
+        any_mask = np.asarray(any_mask, dtype=bool)
+        ids = np.asarray(ids, dtype=np.int64)
+        if card > LUT_THRESHOLD:
+            # per-call remap: class 0 = values no job mentions, classes 1.. = mentioned values,
+            # last class = unknown
+            mentioned = np.unique(ids[ids >= 0])
+            lut = np.zeros(card, dtype=np.uint16)
+            lut[mentioned] = np.arange(1, len(mentioned) + 1, dtype=np.uint16)
+            unk = len(mentioned) + 1
+            lut[card - 1] = unk
+            ids = np.where(ids >= 0, np.searchsorted(mentioned, np.maximum(ids, 0)) + 1, -1)
+            card = unk + 1
+            luts[col_idx] = lut
+        nw = (card + 31) // 32
+        bits = _bitset_from_csr(any_mask, ptr, ids, nw, pass_bits=[card - 1] if unknown_passes else [])
+        add(bits, KIND_BITSET, card)
+
+    c = t.col
+    add(_range_words(t.columns[c("cpu")].values, jc.cpu), KIND_RANGE, t.columns[c("cpu")].card)
+    add(_range_words(t.columns[c("memory")].values, jc.memory), KIND_RANGE, t.columns[c("memory")].card)
+    dcol = t.columns[c("disk")]
+    add(_range_words(dcol.values, jc.disk), KIND_RANGE, dcol.card, COLF_NULL_PASSES)
+
+    # accelerator sub-predicate
+    gd = t.gpu_dict
+    n_names = max(1, len(gd["names"]))
+    nwn = (n_names + 31) // 32
+    gflags = np.zeros(j, dtype=np.uint32)
+    gm = np.asarray(jc.gpu_memory, dtype=np.float64)
+    gflags |= np.where(~np.isnan(gm).all(axis=1), GPUF_MEM_BOUNDED, 0).astype(np.uint32)
+    ccm = np.asarray(jc.cc_min, dtype=np.int64)
+    gflags |= np.where(ccm >= 0, GPUF_CC_BOUNDED, 0).astype(np.uint32)
+    gflags |= np.where(np.asarray(jc.gpu_name_any, dtype=bool), GPUF_NAME_ANY, 0).astype(np.uint32)
+    cc_ord = np.searchsorted(gd["cc"], np.maximum(ccm, 0).astype(np.float64), side="left").astype(np.uint32)
+    gv = np.asarray(jc.gpu_vendor, dtype=np.int64)
+    vmask = np.where(gv == 0, 0xFF, 1 << gv).astype(np.uint32)
+    name_bits = _bitset_from_csr(np.zeros(j, dtype=bool), jc.gpu_name_ptr, jc.gpu_name_ids, nwn)
+    gwords = np.concatenate([
+        _range_words(gd["count"], jc.gpu_count)[:, None],
+        _range_words(gd["memory"], gm)[:, None],
+        _range_words(gd["total"], jc.gpu_total)[:, None],
+        (np.minimum(cc_ord, 0xFFFE) | (gflags << np.uint32(16)))[:, None],
+        vmask[:, None],
+        name_bits,
+    ], axis=1)
+    add(gwords, KIND_GPU, t.columns[c("gpu")].card, ax=nwn)
+
+    # backend / spot / status / flags
+    spot = np.asarray(jc.spot, dtype=np.int64)
+    spot_mask = np.where(spot < 0, 3, np.where(spot == 0, 1, 2)).astype(np.uint32)
+    st_mask = np.full(j, 0xFF, dtype=np.uint32) if jc.status_mask is None else np.asarray(jc.status_mask, dtype=np.uint32)
+    req = np.zeros(j, dtype=np.uint32) if jc.flag_req is None else np.asarray(jc.flag_req, dtype=np.uint32)
+    forbid = np.zeros(j, dtype=np.uint32) if jc.flag_forbid is None else np.asarray(jc.flag_forbid, dtype=np.uint32)
+    bwords = np.stack([
+        np.asarray(jc.src_backend_mask, dtype=np.uint32),
+        np.asarray(jc.off_backend_mask, dtype=np.uint32),
+        spot_mask | (st_mask << np.uint32(8)),
+        req | (forbid << np.uint32(16)),
+    ], axis=1)
+    add(bwords, KIND_BK, t.columns[c("bk")].card)
+
+    add_set(c("region"), jc.region_any, jc.region_ptr, jc.region_ids, unknown_passes=False)
+    add_set(c("itype"), jc.itype_any, jc.itype_ptr, jc.itype_ids, unknown_passes=True)
+    if t.is_pool:
+        ar = np.arange(j + 1)
+        fany = np.ones(j, bool) if jc.fleet_any is None else jc.fleet_any
+        fids = np.full(j, -1, np.int64) if jc.fleet_ids is None else jc.fleet_ids
+        add_set(c("fleet"), fany, ar, fids, unknown_passes=False)
+        nany = np.ones(j, bool) if jc.name_any is None else jc.name_any
+        nids = np.full(j, -1, np.int64) if jc.name_ids is None else jc.name_ids
+        add_set(c("name"), nany, ar, nids, unknown_passes=False)
+        zany = np.ones(j, bool) if jc.zone_any is None else jc.zone_any
+        zptr = np.zeros(j + 1, np.int64) if jc.zone_ptr is None else jc.zone_ptr
+        zids = np.zeros(0, np.int64) if jc.zone_ids is None else jc.zone_ids
+        add_set(c("zone"), zany, zptr, zids, unknown_passes=True)
+
+    rec_words = (pos + 3) // 4 * 4
+    rec = np.zeros((j, rec_words), dtype=np.uint32)
+    o = 0
+    for p in parts:
+        rec[:, o:o + p.shape[1]] = p
+        o += p.shape[1]
+    layout = dict(n_used=len(kinds), kind=kinds, card=cards, flags=cflags, aux=aux, rec_off=offs,
+                  rec_words=rec_words)
+    return PackedJobs(records=rec, layout=layout, luts=luts)

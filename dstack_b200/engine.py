@@ -1,0 +1,177 @@
+"""Device-resident offer tables and the batched matcher on top of ``libdsmatch.so``.
+
+``DeviceTable``  an :class:`~dstack_b200.encode.EncodedTable` uploaded to one GPU.
+``Matcher``      a context (CUDA stream + scratch) that runs job batches against tables and
+                 maps the rows that come back to positions in the caller's source list.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import threading
+from dataclasses import dataclass
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import native
+from .encode import EncodedTable, JobColumns, PackedJobs, encode_table, pack_jobs, OfferColumns
+
+NO_ROW = native.NO_ROW
+
+
+@dataclass
+class TopK:
+    """Per job: source positions of the first ``k`` matches in reference order (-1 = none),
+    number of matches, and the highest price among all matches (NaN if none)."""
+
+    index: np.ndarray      # int64 [J, k]
+    count: np.ndarray      # int64 [J]
+    max_price: np.ndarray  # float64 [J]
+
+
+class Matcher:
+    def __init__(self, device: int = 0, stream: Optional[int] = None):
+        self._lib = native.lib()
+        h = C.c_void_p()
+        native.check(self._lib.dsm_ctx_create(device, C.c_void_p(stream or 0), C.byref(h)))
+        self._h = h
+        self.device = device
+
+    # -- lifecycle
+    def close(self) -> None:
+        if self._h is not None:
+            self._lib.dsm_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self) -> C.c_void_p:
+        if self._h is None:
+            raise RuntimeError("matcher is closed")
+        return self._h
+
+    def launch_count(self) -> int:
+        return int(self._lib.dsm_launch_count(self.handle))
+
+    def sync(self) -> None:
+        native.check(self._lib.dsm_sync(self.handle))
+
+    # -- tables
+    def upload(self, table: EncodedTable) -> "DeviceTable":
+        return DeviceTable(self, table)
+
+    # -- helpers
+    def _layout(self, packed: PackedJobs) -> native.Layout:
+        lut_ptrs: Dict[int, int] = {}
+        for col, lut in packed.luts.items():
+            lut = np.ascontiguousarray(lut, dtype=np.uint16)
+            out = C.c_void_p()
+            native.check(self._lib.dsm_lut_upload(self.handle, col, native.ptr(lut), len(lut), C.byref(out)))
+            lut_ptrs[col] = out.value
+        return native.make_layout(packed.layout, lut_ptrs)
+
+    def plan(self, dt: "DeviceTable", packed: PackedJobs) -> Dict[str, int]:
+        out = (C.c_uint32 * 8)()
+        lay = native.make_layout(packed.layout)
+        native.check(self._lib.dsm_plan_query(self.handle, dt.handle, C.byref(lay), len(packed.records), C.byref(out)))
+        keys = ["grid", "items", "ranges_a", "ranges_b", "slots", "smem", "entries", "groups"]
+        return dict(zip(keys, [int(x) for x in out]))
+
+    # -- matching with host buffers (H2D + kernels + D2H inside the call)
+    def topk_rows(self, dt: "DeviceTable", packed: PackedJobs, k: int,
+                  out: Optional[Tuple[np.ndarray, np.ndarray, np.ndarray]] = None):
+        """Raw result in physical-row space: (idx [J,k] u32, cnt [J] u32, max_row [J] u32)."""
+        j = len(packed.records)
+        rec = np.ascontiguousarray(packed.records, dtype=np.uint32)
+        if out is None:
+            out = (np.empty((j, k), np.uint32), np.empty(j, np.uint32), np.empty(j, np.uint32))
+        lay = self._layout(packed)
+        native.check(self._lib.dsm_match_topk(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j, k,
+                                              native.ptr(out[0]), native.ptr(out[1]), native.ptr(out[2])))
+        return out
+
+    def bitmap_rows(self, dt: "DeviceTable", packed: PackedJobs) -> np.ndarray:
+        j = len(packed.records)
+        rec = np.ascontiguousarray(packed.records, dtype=np.uint32)
+        bits = np.empty((j, dt.table.n_rows // 32), np.uint32)
+        lay = self._layout(packed)
+        native.check(self._lib.dsm_match_bitmap(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j,
+                                                native.ptr(bits)))
+        return bits
+
+    # -- results in source space
+    def match_topk(self, dt: "DeviceTable", jobs: JobColumns, k: int) -> TopK:
+        t = dt.table
+        if t.n_src == 0:
+            return TopK(np.full((jobs.n, k), -1, np.int64), np.zeros(jobs.n, np.int64), np.full(jobs.n, np.nan))
+        idx, cnt, mx = self.topk_rows(dt, pack_jobs(t, jobs), k)
+        src = np.where(idx == NO_ROW, -1, t.perm[np.minimum(idx, t.n_rows - 1)])
+        price = np.where(mx == NO_ROW, np.nan, t.price[np.minimum(mx, t.n_rows - 1)])
+        return TopK(src.astype(np.int64), cnt.astype(np.int64), price)
+
+    def match_all(self, dt: "DeviceTable", jobs: JobColumns, order: str = "source") -> List[np.ndarray]:
+        """Every match per job as source positions, in ``"source"`` (input) order or in
+        ``"rank"`` (reference result) order."""
+        t = dt.table
+        if t.n_src == 0:
+            return [np.zeros(0, np.int64) for _ in range(jobs.n)]
+        bits = self.bitmap_rows(dt, pack_jobs(t, jobs))
+        out = []
+        for j in range(jobs.n):
+            rows = np.flatnonzero(np.unpackbits(bits[j].view(np.uint8), bitorder="little"))
+            src = t.perm[rows]
+            out.append(np.sort(src) if order == "source" else src)
+        return out
+
+
+class DeviceTable:
+    def __init__(self, matcher: Matcher, table: EncodedTable):
+        self.table = table
+        self._lib = native.lib()
+        self._matcher = matcher
+        desc = native.TableDesc(table.n_rows, table.split_row, table.n_cols,
+                                len(table.gpu_entries), len(table.bk_entries))
+        rows = np.ascontiguousarray(table.rows, dtype=np.uint16)
+        price = np.ascontiguousarray(table.price, dtype=np.float64)
+        ge = np.ascontiguousarray(table.gpu_entries, dtype=np.uint32)
+        be = np.ascontiguousarray(table.bk_entries, dtype=np.uint32)
+        h = C.c_void_p()
+        native.check(self._lib.dsm_table_create(matcher.handle, C.byref(desc), native.ptr(rows), native.ptr(price),
+                                                native.ptr(ge), native.ptr(be), C.byref(h)))
+        self._h = h
+
+    @property
+    def handle(self) -> C.c_void_p:
+        if self._h is None:
+            raise RuntimeError("table is closed")
+        return self._h
+
+    def close(self) -> None:
+        if self._h is not None:
+            self._lib.dsm_table_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default: Dict[int, Matcher] = {}
+_default_lock = threading.Lock()
+
+
+def default_matcher(device: int = 0) -> Matcher:
+    """One shared matcher per device for the drop-in functions."""
+    with _default_lock:
+        m = _default.get(device)
+        if m is None:
+            m = _default[device] = Matcher(device)
+        return m

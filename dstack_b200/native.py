@@ -1,0 +1,135 @@
+"""ctypes binding of ``libdsmatch.so`` (C ABI in ``include/dsmatch.h``).
+
+There is no CPU fallback: if the shared library is missing or a call fails, an exception is
+raised.  ctypes releases the GIL for the duration of every foreign call, so several host
+threads can drive their own contexts concurrently (the reference calls this path from a
+thread pool and from interleaved asyncio tasks, SURVEY.md section 8b "Threading").
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Any, Dict, Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdsmatch.so")
+MAX_COLS = 16
+NO_ROW = 0xFFFFFFFF
+
+EXPORTS = [
+    "dsm_ctx_create", "dsm_ctx_destroy", "dsm_last_error", "dsm_build_info", "dsm_table_create",
+    "dsm_table_destroy", "dsm_lut_upload", "dsm_match_topk", "dsm_match_bitmap",
+    "dsm_match_topk_dev", "dsm_match_bitmap_dev", "dsm_merge_shards_dev", "dsm_gather_price_dev",
+    "dsm_sync", "dsm_host_alloc", "dsm_host_free", "dsm_launch_count", "dsm_plan_query",
+]
+
+
+class DsmError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libdsmatch error {code}: {message}")
+        self.code = code
+
+
+class TableDesc(C.Structure):
+    _fields_ = [("n_rows", C.c_uint32), ("split_row", C.c_uint32), ("n_cols", C.c_uint32),
+                ("n_gpu_entries", C.c_uint32), ("n_bk_entries", C.c_uint32)]
+
+
+class Layout(C.Structure):
+    _fields_ = [("n_used", C.c_uint32),
+                ("kind", C.c_uint32 * MAX_COLS), ("card", C.c_uint32 * MAX_COLS),
+                ("flags", C.c_uint32 * MAX_COLS), ("aux", C.c_uint32 * MAX_COLS),
+                ("rec_off", C.c_uint32 * MAX_COLS), ("rec_words", C.c_uint32),
+                ("lut", C.c_void_p * MAX_COLS)]
+
+
+_lib: Optional[C.CDLL] = None
+
+
+def lib() -> C.CDLL:
+    """Load the library once.  Raises if it has not been built (``python -c 'import
+    __graft_entry__ as g; g.build()'``)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(f"{LIB_PATH} not found: build the CUDA extension first "
+                          "(__graft_entry__.build()); there is no CPU fallback")
+    L = C.CDLL(LIB_PATH)
+    vp, u32, u64 = C.c_void_p, C.c_uint32, C.c_uint64
+    L.dsm_last_error.restype = C.c_char_p
+    L.dsm_build_info.restype = C.c_char_p
+    L.dsm_launch_count.restype = u64
+    L.dsm_launch_count.argtypes = [vp]
+    L.dsm_ctx_create.argtypes = [C.c_int, vp, C.POINTER(vp)]
+    L.dsm_ctx_destroy.argtypes = [vp]
+    L.dsm_table_create.argtypes = [vp, C.POINTER(TableDesc), vp, vp, vp, vp, C.POINTER(vp)]
+    L.dsm_table_destroy.argtypes = [vp]
+    L.dsm_lut_upload.argtypes = [vp, u32, vp, u32, C.POINTER(vp)]
+    L.dsm_match_topk.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, u32, vp, vp, vp]
+    L.dsm_match_bitmap.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp]
+    L.dsm_match_topk_dev.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, u32, vp, vp, vp]
+    L.dsm_match_bitmap_dev.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp]
+    L.dsm_merge_shards_dev.argtypes = [vp, u32, u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    L.dsm_gather_price_dev.argtypes = [vp, vp, vp, u32, vp]
+    L.dsm_sync.argtypes = [vp]
+    L.dsm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
+    L.dsm_host_free.argtypes = [vp]
+    L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, C.POINTER(u32 * 8)]
+    for name in EXPORTS:
+        fn = getattr(L, name)
+        if name not in ("dsm_last_error", "dsm_build_info", "dsm_launch_count"):
+            fn.restype = C.c_int
+    _lib = L
+    return L
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise DsmError(rc, lib().dsm_last_error().decode(errors="replace"))
+
+
+def ptr(a: Optional[np.ndarray]) -> Optional[int]:
+    return None if a is None else a.ctypes.data
+
+
+def make_layout(d: Dict[str, Any], lut_ptrs: Optional[Dict[int, int]] = None) -> Layout:
+    L = Layout()
+    L.n_used = d["n_used"]
+    L.rec_words = d["rec_words"]
+    for i in range(d["n_used"]):
+        L.kind[i] = d["kind"][i]
+        L.card[i] = d["card"][i]
+        L.flags[i] = d["flags"][i]
+        L.aux[i] = d["aux"][i]
+        L.rec_off[i] = d["rec_off"][i]
+    for i, p in (lut_ptrs or {}).items():
+        L.lut[i] = p
+    return L
+
+
+class PinnedArray:
+    """A numpy view over ``cudaHostAlloc`` memory (for the host-buffer entry points)."""
+
+    def __init__(self, shape, dtype):
+        self.nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        check(lib().dsm_host_alloc(max(self.nbytes, 16), C.byref(p)))
+        self._p = p
+        buf = (C.c_char * max(self.nbytes, 16)).from_address(p.value)
+        self.array = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def free(self) -> None:
+        if self._p is not None:
+            self.array = None
+            lib().dsm_host_free(self._p)
+            self._p = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass

@@ -1,0 +1,202 @@
+/*
+ * dsmatch.h -- C ABI of libdsmatch.so: B200 (sm_100a) offer matching for dstack.
+ *
+ * The reference (solovyevt/dstack) has NO FFI for this path: the hot loops are plain
+ * Python.  These entry points are therefore the boundary a
+ * maintainer would bind with ctypes; each one names the reference
+ * code whose work it takes over (paths relative to src/dstack/_internal).
+ *
+ * Model
+ *   table   a device-resident, dictionary-encoded offer table: one row of n_cols u16 codes
+ *           per offer, rows stored in the reference's result order
+ *           (not-available last, then price, then project-backend order, then in-backend order:
+ *           server/services/backends/__init__.py:449-451), so "top-k by price" is "first k
+ *           matches" and a job's max_price is a row-index cut-off.
+ *   jobs    one fixed-size predicate record per job (u32 words, format below), built by the
+ *           host from Requirements + profile filters
+ *           (core/backends/base/offers.py:112-146, server/services/offers.py:46-100).
+ *   match   every (job, row) pair is evaluated on the GPU: a table-build kernel turns the
+ *           records into bit-sliced acceptance tables (bit j of word = job j accepts this
+ *           dictionary entry), the match kernel ANDs one gathered word per column for 32
+ *           rows x 128 jobs at a time, and a merge kernel orders the per-range partial
+ *           results.  This replaces gpuhunt.matches per (job, offer)
+ *           (core/backends/base/offers.py:154-157, server/services/pools.py:496-502,533-543)
+ *           and the merge / partition / slice ranker (backends/__init__.py:449-451,
+ *           background/tasks/process_submitted_jobs.py:450, services/runs.py:341-348).
+ *
+ * All functions return 0 on success or a negative DSM_E_* code; dsm_last_error() gives the
+ * message for the calling thread.  No exceptions cross the boundary.  A context owns a CUDA
+ * stream and its scratch memory; calls on one context serialise, different contexts may be
+ * used from different host threads concurrently.  Nothing here falls back to the CPU.
+ */
+#ifndef DSMATCH_H
+#define DSMATCH_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DSM_MAX_COLS 16
+#define DSM_JOBS_PER_GROUP 128u /* J_t: jobs evaluated per pass over the rows */
+#define DSM_NO_ROW 0xFFFFFFFFu
+
+enum dsm_error {
+  DSM_OK = 0,
+  DSM_E_CUDA = -1,         /* a CUDA runtime call failed (message has the cudaError string) */
+  DSM_E_ARG = -2,          /* bad argument */
+  DSM_E_DICT_TOO_LARGE = -3, /* acceptance tables of one job group exceed shared memory */
+  DSM_E_NO_DEVICE = -4,
+  DSM_E_TOO_LARGE = -5     /* request exceeds a fixed-capacity entry point's limit */
+};
+
+/* Column kinds: how the table-build kernel turns a job's record into acceptance bits. */
+enum dsm_col_kind {
+  DSM_COL_UNUSED = 0,
+  /* 1 word: lo | hi<<16 (inclusive ordinals).  Entry e passes iff lo <= e <= hi; with
+   * DSM_COLF_NULL_PASSES the last entry (card-1) passes for every job.
+   * cpu / memory / disk bounds: App. A.1 items 4,5,12 of SURVEY.md. */
+  DSM_COL_RANGE = 1,
+  /* ceil(card/32) words: entry e passes iff bit e is set (region, instance type, fleet,
+   * instance name, zone ... sets: server/services/offers.py:93-100, pools.py:458-483). */
+  DSM_COL_BITSET = 2,
+  /* accelerator configuration dictionary, record = 5 + aux words:
+   *   w0 count lo|hi<<16   w1 memory lo|hi<<16   w2 total-memory lo|hi<<16
+   *   w3 cc_min | flags<<16 (DSM_GPUF_*)   w4 vendor mask (bit = vendor code)
+   *   w5.. GPU-name bitset (aux words).  App. A.1 items 6-11. */
+  DSM_COL_GPU = 3,
+  /* backend/spot/status/flags dictionary, record = 4 words:
+   *   w0 serving-backend mask  w1 offer-backend mask  w2 spot mask | status mask<<8
+   *   w3 required flags | forbidden flags<<16.  App. A.1 item 3 and
+   *   server/services/offers.py:81-94, pools.py:460-488. */
+  DSM_COL_BK = 4
+};
+
+#define DSM_COLF_NULL_PASSES 1u
+
+#define DSM_GPUF_MEM_BOUNDED 1u
+#define DSM_GPUF_CC_BOUNDED 2u
+#define DSM_GPUF_NAME_ANY 8u
+
+/* Dictionary entry of a DSM_COL_GPU column (3 words, built by the host encoder):
+ *   w0 count ordinal | memory ordinal<<16
+ *   w1 total-memory ordinal | compute-capability ordinal<<16 (0xFFFF unknown)
+ *   w2 name id (0xFFFF none) | vendor code<<16 | has_gpu<<24
+ * Dictionary entry of a DSM_COL_BK column (2 words):
+ *   w0 serving backend | offer backend<<8 | spot<<16 | status<<24      w1 flags
+ * Entry 0 of the DSM_COL_BK column is reserved as the dead entry: rows that carry it never
+ * match (padding rows). */
+#define DSM_GPU_ENTRY_WORDS 3
+#define DSM_BK_ENTRY_WORDS 2
+
+typedef struct dsm_table_desc {
+  uint32_t n_rows;     /* physical rows incl. padding; multiple of 32 */
+  uint32_t split_row;  /* rows [0,split) are the "available" segment, [split,n_rows) the rest;
+                          multiple of 32 */
+  uint32_t n_cols;     /* codes per row: 8 (16-byte rows) or 16 (32-byte rows) */
+  uint32_t n_gpu_entries; /* entries of the DSM_COL_GPU dictionary (0 if none) */
+  uint32_t n_bk_entries;  /* entries of the DSM_COL_BK dictionary (0 if none) */
+} dsm_table_desc;
+
+/* Per-call description of the job records and of the acceptance tables built from them. */
+typedef struct dsm_layout {
+  uint32_t n_used;               /* columns that take part, 1..n_cols; column i reads code i */
+  uint32_t kind[DSM_MAX_COLS];
+  uint32_t card[DSM_MAX_COLS];   /* table entries of the column for this call */
+  uint32_t flags[DSM_MAX_COLS];  /* DSM_COLF_* */
+  uint32_t aux[DSM_MAX_COLS];    /* DSM_COL_GPU: words of the GPU-name bitset */
+  uint32_t rec_off[DSM_MAX_COLS];/* word offset of the column's predicate in a record */
+  uint32_t rec_words;            /* record stride in u32 words; word 0 = cut-off row inside
+                                    the first segment, word 1 = cut-off row inside the second
+                                    (rows >= cut-off fail: max_price / exclude_not_available) */
+  /* optional per-call remap of a column's codes (device pointer to card_of_table u16
+   * values, or NULL): lets a high-cardinality column be looked up through the few classes
+   * the jobs of this call mention.  Set by dsm_lut_upload. */
+  const uint16_t* lut[DSM_MAX_COLS];
+} dsm_layout;
+
+typedef struct dsm_ctx dsm_ctx;
+typedef struct dsm_table dsm_table;
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+
+/* Create a context on `device` (a CUDA ordinal).  stream = 0 makes the context own a new
+ * non-blocking stream; otherwise pass a cudaStream_t to run on (e.g. torch's current stream). */
+int dsm_ctx_create(int device, void* stream, dsm_ctx** out);
+int dsm_ctx_destroy(dsm_ctx* ctx);
+const char* dsm_last_error(void);
+/* Compile-time facts: "sm_100a", jobs per group, version. */
+const char* dsm_build_info(void);
+
+/* Upload an encoded table.  rows: n_rows*n_cols u16 (host).  price: n_rows f64 (host), used
+ * only to pick the max-price match; may be NULL.  gpu_entries / bk_entries: dictionaries of
+ * the composite columns (host).  Replaces the per-(job,offer) offer_to_catalog_item walk
+ * (core/backends/base/offers.py:86-109): attributes are encoded once per table. */
+int dsm_table_create(dsm_ctx* ctx, const dsm_table_desc* desc, const uint16_t* rows,
+                     const double* price, const uint32_t* gpu_entries,
+                     const uint32_t* bk_entries, dsm_table** out);
+int dsm_table_destroy(dsm_table* t);
+
+/* Copy a per-call code->class remap to the device (see dsm_layout.lut).  The returned device
+ * pointer stays valid until the next dsm_lut_upload for the same (ctx, column). */
+int dsm_lut_upload(dsm_ctx* ctx, uint32_t column, const uint16_t* lut, uint32_t n,
+                   const uint16_t** dev_out);
+
+/* ---- matching, host buffers (H2D of the records and D2H of the results inside) ---------- */
+
+/* For each job: the first k matching rows in table order (= the reference's offers[:k]),
+ * the number of matching rows (= len(offers)) and the row holding the highest price among
+ * the matches (= max(offer.price)), DSM_NO_ROW if none.
+ * out_idx: n_jobs*k u32, unused slots DSM_NO_ROW.  out_cnt, out_max: n_jobs u32.
+ * Reference: get_instance_offers + slicing, see the header comment. */
+int dsm_match_topk(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                   const uint32_t* jobs, uint32_t n_jobs, uint32_t k, uint32_t* out_idx,
+                   uint32_t* out_cnt, uint32_t* out_max);
+
+/* For each job the full match bitmap: out_bits[j*(n_rows/32) + b] bit l = row 32*b+l matches.
+ * Used where the reference returns every match in input order: match_requirements
+ * (core/backends/base/offers.py:149-158) and filter_pool_instances (pools.py:409-503). */
+int dsm_match_bitmap(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                     const uint32_t* jobs, uint32_t n_jobs, uint32_t* out_bits);
+
+/* ---- matching, device buffers (inputs already resident; asynchronous on the ctx stream) - */
+
+int dsm_match_topk_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                       const uint32_t* d_jobs, uint32_t n_jobs, uint32_t k, uint32_t* d_idx,
+                       uint32_t* d_cnt, uint32_t* d_max);
+int dsm_match_bitmap_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                         const uint32_t* d_jobs, uint32_t n_jobs, uint32_t* d_bits);
+
+/* Merge per-shard results of a catalog sharded over n_shards GPUs in table order
+ * (shard s holds rows that rank before shard s+1).  Inputs are the all-gathered device
+ * arrays [n_shards][n_jobs][k], [n_shards][n_jobs], [n_shards][n_jobs] and the per-shard
+ * max-price values [n_shards][n_jobs] f64; indices come out as global rows
+ * (shard_base[s] + local).  Asynchronous on the ctx stream. */
+int dsm_merge_shards_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                         const uint32_t* d_idx_all, const uint32_t* d_cnt_all,
+                         const uint32_t* d_max_all, const double* d_maxprice_all,
+                         const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
+                         uint64_t* d_max_out, double* d_maxprice_out);
+
+/* Gather price[row] for rows produced by dsm_match_topk_dev (DSM_NO_ROW -> NaN). */
+int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_rows, uint32_t n,
+                         double* d_out);
+
+/* ---- utilities ------------------------------------------------------------------------ */
+
+int dsm_sync(dsm_ctx* ctx);
+/* Pinned host memory for record / result buffers of the host-buffer entry points. */
+int dsm_host_alloc(size_t bytes, void** out);
+int dsm_host_free(void* p);
+/* Kernel launches issued by this context since creation (bench.py's gpu_launches). */
+uint64_t dsm_launch_count(const dsm_ctx* ctx);
+/* Launch geometry chosen for a call: grid CTAs, work items, row ranges per job group, slots. */
+int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                   uint32_t n_jobs, uint32_t out[8]);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DSMATCH_H */

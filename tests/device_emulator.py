@@ -1,0 +1,104 @@
+"""numpy emulation of what libdsmatch's kernels compute, for CPU-only tests of the host encoder.
+
+TEST INFRASTRUCTURE: lives under tests/, is never imported by ``dstack_b200`` and is not a
+fallback.  It re-implements the record/table formats documented in ``include/dsmatch.h``
+so that ``encode.py`` / ``ingest.py`` can be checked against the oracle without a GPU; the
+``-m gpu`` tests then check the real kernels against the same oracle.
+"""
+
+from __future__ import annotations
+
+import numpy as np
+
+from dstack_b200.encode import (COLF_NULL_PASSES, GPUF_CC_BOUNDED, GPUF_MEM_BOUNDED, GPUF_NAME_ANY, KIND_BITSET,
+                                KIND_BK, KIND_GPU, KIND_RANGE, NO_ROW, EncodedTable, PackedJobs)
+
+
+def acceptance(table: EncodedTable, packed: PackedJobs):
+    """Per used column: bool [J, card] -- bit (j, e) of the acceptance tables."""
+    rec = packed.records.astype(np.uint64)
+    lay = packed.layout
+    out = []
+    for c in range(lay["n_used"]):
+        kind, card, off = lay["kind"][c], lay["card"][c], lay["rec_off"][c]
+        e = np.arange(card, dtype=np.uint64)[None, :]
+        if kind == KIND_RANGE:
+            w = rec[:, off][:, None]
+            ok = (e >= (w & 0xFFFF)) & (e <= (w >> 16))
+            if lay["flags"][c] & COLF_NULL_PASSES:
+                ok[:, card - 1] = True
+        elif kind == KIND_BITSET:
+            nw = (card + 31) // 32
+            words = rec[:, off:off + nw]
+            ok = ((words[:, (e[0] >> 5).astype(np.int64)] >> (e & 31)) & 1).astype(bool)
+        elif kind == KIND_GPU:
+            ent = table.gpu_entries.astype(np.uint64)
+            cnt, mem = (ent[:, 0] & 0xFFFF)[None, :], (ent[:, 0] >> 16)[None, :]
+            tot, cc = (ent[:, 1] & 0xFFFF)[None, :], (ent[:, 1] >> 16)[None, :]
+            name, vendor = (ent[:, 2] & 0xFFFF)[None, :], ((ent[:, 2] >> 16) & 0xFF)[None, :]
+            has_gpu = (((ent[:, 2] >> 24) & 1) == 1)[None, :]
+            r0, r1, r2, r3, r4 = (rec[:, off + i][:, None] for i in range(5))
+            gflags, cc_min = r3 >> 16, r3 & 0xFFFF
+            ok = (cnt >= (r0 & 0xFFFF)) & (cnt <= (r0 >> 16))
+            ok &= ((r4 >> vendor) & 1).astype(bool)
+            nwn = lay["aux"][c]
+            bits = rec[:, off + 5:off + 5 + nwn]
+            safe = np.where(name == 0xFFFF, 0, name).astype(np.int64)
+            name_ok = ((bits[:, (safe[0] >> 5)] >> (safe & 31).astype(np.uint64)) & 1).astype(bool) & (name != 0xFFFF)
+            ok &= np.where((gflags & GPUF_NAME_ANY) != 0, True, name_ok)
+            mem_ok = has_gpu & (mem >= (r1 & 0xFFFF)) & (mem <= (r1 >> 16))
+            ok &= np.where((gflags & GPUF_MEM_BOUNDED) != 0, mem_ok, True)
+            cc_ok = (cc != 0xFFFF) & (cc >= cc_min)
+            ok &= np.where((gflags & GPUF_CC_BOUNDED) != 0, cc_ok, True)
+            ok &= (tot >= (r2 & 0xFFFF)) & (tot <= (r2 >> 16))
+        elif kind == KIND_BK:
+            ent = table.bk_entries.astype(np.uint64)
+            src, offb = (ent[:, 0] & 0xFF)[None, :], ((ent[:, 0] >> 8) & 0xFF)[None, :]
+            spot, status = ((ent[:, 0] >> 16) & 0xFF)[None, :], (ent[:, 0] >> 24)[None, :]
+            fl = ent[:, 1][None, :]
+            r0, r1, r2, r3 = (rec[:, off + i][:, None] for i in range(4))
+            ok = np.ones((len(rec), card), bool)
+            ok[:, 0] = False
+            ok &= ((r0 >> src) & 1).astype(bool) & ((r1 >> offb) & 1).astype(bool)
+            ok &= ((r2 >> spot) & 1).astype(bool) & ((r2 >> (8 + status)) & 1).astype(bool)
+            req, forbid = r3 & 0xFFFF, r3 >> 16
+            ok &= ((fl & req) == req) & ((fl & forbid) == 0)
+        else:
+            raise ValueError(kind)
+        out.append(ok)
+    return out
+
+
+def match_matrix(table: EncodedTable, packed: PackedJobs) -> np.ndarray:
+    """bool [J, n_rows]: what k_match's bitmap mode produces."""
+    acc = acceptance(table, packed)
+    j = len(packed.records)
+    rows = np.arange(table.n_rows)
+    cut_a = packed.records[:, 0].astype(np.int64)[:, None]
+    cut_b = packed.records[:, 1].astype(np.int64)[:, None]
+    m = np.where(rows[None, :] < table.split_row, rows[None, :] < cut_a, rows[None, :] < cut_b)
+    for c, ok in enumerate(acc):
+        codes = table.rows[:, c].astype(np.int64)
+        if c in packed.luts:
+            codes = packed.luts[c][codes].astype(np.int64)
+        m &= ok[:, codes]
+    return m
+
+
+def topk(table: EncodedTable, packed: PackedJobs, k: int):
+    m = match_matrix(table, packed)
+    j = len(m)
+    idx = np.full((j, k), NO_ROW, dtype=np.uint32)
+    cnt = m.sum(axis=1).astype(np.uint32)
+    mx = np.full(j, NO_ROW, dtype=np.uint32)
+    for i in range(j):
+        rows = np.flatnonzero(m[i])
+        idx[i, :min(k, len(rows))] = rows[:k]
+        if len(rows):
+            a = rows[rows < table.split_row]
+            b = rows[rows >= table.split_row]
+            best = a[-1] if len(a) else b[-1]
+            if len(a) and len(b) and table.price[b[-1]] > table.price[a[-1]]:
+                best = b[-1]
+            mx[i] = best
+    return idx, cnt, mx

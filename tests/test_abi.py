@@ -1,0 +1,35 @@
+"""The C-ABI library loads and exports every symbol include/dsmatch.h declares (no GPU needed)."""
+
+import os
+import re
+
+from dstack_b200 import native
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "dsmatch.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(dsm_[a-z_0-9]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = native.lib()
+    names = _declared()
+    assert len(names) >= 15
+    for name in names:
+        assert hasattr(lib, name), f"{name} declared in include/dsmatch.h but not exported"
+    assert set(native.EXPORTS) <= set(names)
+
+
+def test_build_info_names_the_target():
+    assert b"sm_100a" in native.lib().dsm_build_info()
+
+
+def test_struct_sizes_match_header():
+    import ctypes as C
+
+    assert C.sizeof(native.TableDesc) == 5 * 4
+    # u32 n_used + 5 arrays of 16 u32 + u32 rec_words (+4 padding) + 16 pointers
+    assert C.sizeof(native.Layout) == 4 + 5 * 64 + 4 + 16 * 8

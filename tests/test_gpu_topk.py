@@ -1,0 +1,66 @@
+"""Parity of the CUDA path (through the C ABI) with the oracle.  Bit-exact: integer/index work."""
+
+import numpy as np
+import pytest
+
+from dstack_b200 import synth
+from dstack_b200.encode import NO_ROW, encode_table, pack_jobs
+from oracle import columnar
+
+pytestmark = pytest.mark.gpu
+
+
+def _check(matcher, cat, sj, k):
+    table = encode_table(cat.columns)
+    dt = matcher.upload(table)
+    try:
+        got = matcher.match_topk(dt, sj.columns, k)
+        want = columnar.topk(cat.columns, sj.columns, k)
+        assert np.array_equal(got.count, want.count)
+        assert np.array_equal(got.index, want.index)
+        assert np.array_equal(np.nan_to_num(got.max_price, nan=-1.0), np.nan_to_num(want.max_price, nan=-1.0))
+        return got
+    finally:
+        dt.close()
+
+
+@pytest.mark.parametrize("k", [15, 16, 50])
+def test_topk_64_jobs_100k_offers(matcher, k):
+    cat = synth.make_catalog(100_000, seed=3, n_shapes=2048)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, 64, seed=4)
+    got = _check(matcher, cat, sj, k)
+    assert (got.count > 0).sum() >= 16
+
+
+@pytest.mark.parametrize("n_offers,n_jobs", [(1, 1), (31, 3), (32, 129), (33, 128), (1000, 257), (4097, 1)])
+def test_topk_ragged_sizes(matcher, n_offers, n_jobs):
+    cat = synth.make_catalog(n_offers, seed=21, n_shapes=64)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, n_jobs, seed=22)
+    _check(matcher, cat, sj, 16)
+
+
+def test_bitmap_equals_oracle_matrix(matcher):
+    cat = synth.make_catalog(20_000, seed=8, n_shapes=512)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, 200, seed=9)
+    dt = matcher.upload(table)
+    try:
+        rows = matcher.match_all(dt, sj.columns, order="source")
+    finally:
+        dt.close()
+    want = columnar.match_matrix(cat.columns, sj.columns)
+    for j in range(sj.columns.n):
+        assert np.array_equal(rows[j], np.flatnonzero(want[j]))
+
+
+def test_all_not_available_and_all_available(matcher):
+    for avail in (0, 3):  # UNKNOWN (available) / NOT_AVAILABLE
+        cat = synth.make_catalog(3000, seed=2, n_shapes=64)
+        cat.availability[:] = avail
+        cat.columns.available[:] = synth.AVAILABILITY[avail].is_available()
+        table = encode_table(cat.columns)
+        sj = synth.make_jobs(cat, table, 40, seed=5)
+        sj.columns.exclude_not_available[::2] = True
+        _check(matcher, cat, sj, 16)
