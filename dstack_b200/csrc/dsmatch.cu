@@ -27,6 +27,8 @@
 #include <mutex>
 #include <new>
 #include <string>
+#include <utility>
+#include <vector>
 
 #include "../../include/dsmatch.h"
 
@@ -536,6 +538,11 @@ struct dsm_ctx {
   int sm_count;
   std::mutex mu;
   uint64_t launches;
+  // optional timing of the match kernel alone (bench.py's roofline): event pairs recorded
+  // around each k_match launch while enabled, read back by dsm_timing_read
+  bool timing = false;
+  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
+  size_t timing_used = 0;
   DevBuf tabs, part_cnt, part_last, part_idx, d_jobs, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
 };
@@ -703,9 +710,21 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   uint32_t nc = L->n_used;
   if (t->desc.n_cols == 16 && nc < 9) return fail(DSM_E_ARG, "16-column tables need n_used >= 9");
   if (t->desc.n_cols == 8 && nc > 8) return fail(DSM_E_ARG, "8-column tables allow n_used <= 8");
+  std::pair<cudaEvent_t, cudaEvent_t>* tev = nullptr;
+  if (ctx->timing) {
+    if (ctx->timing_used == ctx->timing_events.size()) {
+      std::pair<cudaEvent_t, cudaEvent_t> pr;
+      CK(cudaEventCreate(&pr.first));
+      CK(cudaEventCreate(&pr.second));
+      ctx->timing_events.push_back(pr);
+    }
+    tev = &ctx->timing_events[ctx->timing_used++];
+    CK(cudaEventRecord(tev->first, ctx->stream));
+  }
   cudaError_t e = bitmap ? launch_match<true>(nc, mp, has_lut, pl.grid, pl.smem, ctx->stream)
                          : launch_match<false>(nc, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
+  if (tev) CK(cudaEventRecord(tev->second, ctx->stream));
   ctx->launches++;
 
   if (!bitmap) {
@@ -770,6 +789,7 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
                     &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);
+  for (auto& pr : ctx->timing_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return 0;
@@ -957,6 +977,31 @@ int dsm_host_free(void* p) {
 }
 
 uint64_t dsm_launch_count(const dsm_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+int dsm_timing_enable(dsm_ctx* ctx, int on) {
+  if (!ctx) return fail(DSM_E_ARG, "NULL ctx");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  ctx->timing = on != 0;
+  ctx->timing_used = 0;
+  return 0;
+}
+
+int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches) {
+  if (!ctx || !total_ms || !n_launches) return fail(DSM_E_ARG, "NULL argument");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  double sum = 0.0;
+  for (size_t i = 0; i < ctx->timing_used; ++i) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, ctx->timing_events[i].first, ctx->timing_events[i].second));
+    sum += ms;
+  }
+  *total_ms = sum;
+  *n_launches = (uint32_t)ctx->timing_used;
+  ctx->timing_used = 0;
+  return 0;
+}
 
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, uint32_t n_jobs,
                    uint32_t out[8]) {

@@ -24,6 +24,7 @@ EXPORTS = [
     "dsm_table_destroy", "dsm_lut_upload", "dsm_match_topk", "dsm_match_bitmap",
     "dsm_match_topk_dev", "dsm_match_bitmap_dev", "dsm_merge_shards_dev", "dsm_gather_price_dev",
     "dsm_sync", "dsm_host_alloc", "dsm_host_free", "dsm_launch_count", "dsm_plan_query",
+    "dsm_timing_enable", "dsm_timing_read",
 ]
 
 
@@ -78,6 +79,8 @@ def lib() -> C.CDLL:
     L.dsm_sync.argtypes = [vp]
     L.dsm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
     L.dsm_host_free.argtypes = [vp]
+    L.dsm_timing_enable.argtypes = [vp, C.c_int]
+    L.dsm_timing_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
     L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, C.POINTER(u32 * 8)]
     for name in EXPORTS:
         fn = getattr(L, name)

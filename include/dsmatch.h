@@ -192,6 +192,11 @@ int dsm_host_alloc(size_t bytes, void** out);
 int dsm_host_free(void* p);
 /* Kernel launches issued by this context since creation (bench.py's gpu_launches). */
 uint64_t dsm_launch_count(const dsm_ctx* ctx);
+/* Time the match kernel alone: while enabled, a CUDA event pair brackets every k_match launch
+ * on the context's stream; dsm_timing_read synchronises, returns the summed kernel time and
+ * the number of launches since the last read, and resets the counter. */
+int dsm_timing_enable(dsm_ctx* ctx, int on);
+int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches);
 /* Launch geometry chosen for a call: grid CTAs, work items, row ranges per job group, slots. */
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
                    uint32_t n_jobs, uint32_t out[8]);

@@ -116,8 +116,9 @@ def rank_order(oc: OfferColumns) -> np.ndarray:
     return np.lexsort((np.asarray(oc.price, dtype=np.float64), ~np.asarray(oc.available, dtype=bool)))
 
 
-def topk(oc: OfferColumns, jc: JobColumns, k: int, job_chunk: int = 64) -> TopK:
-    order = rank_order(oc)
+def topk(oc: OfferColumns, jc: JobColumns, k: int, order: Optional[np.ndarray] = None) -> TopK:
+    if order is None:
+        order = rank_order(oc)
     price_ranked = np.asarray(oc.price, dtype=np.float64)[order]
     j = jc.n
     idx = np.full((j, k), -1, dtype=np.int64)
