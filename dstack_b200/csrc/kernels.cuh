@@ -1,0 +1,529 @@
+// kernels.cuh -- device code of libdsmatch (sm_100a).  Included by dsmatch.cu only.
+//
+//   k_build_tables  job records -> bit-sliced acceptance tables (one u32 per 32 jobs per entry)
+//   k_match         rows x job groups -> per-slot partial results (count, first-k, last match)
+//   k_merge         per-job ordered merge of the partials
+//   k_merge_shards  per-job merge of all-gathered per-GPU results
+//
+// Work decomposition of k_match.  The work is the flattened space (job group, 32-row block),
+// group-major, of size T = groups * blocks.  CTA c owns the contiguous chunk
+// [T*c/G, T*(c+1)/G) -- every CTA gets the same amount of work to within one block.  A chunk
+// lies in one group or straddles a few; per group it is further cut at the segment boundary
+// (available | not available) and each piece is split evenly over the 8 warps.  A piece's
+// results go to slot ((c - first CTA of the group) * 2 + segment) * 8 + warp, so slots of a
+// job are in row order and k_merge can take "the first k matches" by walking them.
+
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/dsmatch.h"
+
+#define JPG DSM_JOBS_PER_GROUP  // 128 jobs per group
+#define TPG 4                   // 32-job tiles per group
+#define MATCH_THREADS 256
+#define MATCH_WARPS 8
+#ifndef MATCH_CTAS_PER_SM
+#define MATCH_CTAS_PER_SM 3
+#endif
+#define SLOTS_PER_CTA (2 * MATCH_WARPS)
+
+// ------------------------------------------------------------------------------------------
+// small device helpers
+// ------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// TMA 1-D bulk copy global -> shared, completion on an mbarrier (SASS: UBLKCP).
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32_t bytes,
+                                         uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+          "r"(smem_u32(dst_smem)),
+      "l"(src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// Streaming 128-bit row load (rows are read once per job group; keep them out of L1).
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "l"(p));
+  return r;
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+               : "r"(addr));
+  return r;
+}
+
+// 32x32 bit-matrix transpose across a warp: on return lane j holds, in bit l, bit j of the
+// value lane l passed in.  Five butterfly steps: exchange with lane^s, rotate the partner's
+// word by s (left for lanes with bit s clear, right otherwise) and keep own bits under `keep`.
+struct XposeCtl {
+  uint32_t rot[5];
+  uint32_t keep[5];
+};
+__device__ __forceinline__ void transpose_setup(XposeCtl& c, uint32_t lane) {
+  const uint32_t lowmask[5] = {0x0000FFFFu, 0x00FF00FFu, 0x0F0F0F0Fu, 0x33333333u, 0x55555555u};
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const uint32_t s = 16u >> i;
+    const bool upper = (lane & s) != 0;
+    c.rot[i] = upper ? 32u - s : s;
+    c.keep[i] = upper ? ~lowmask[i] : lowmask[i];
+  }
+}
+__device__ __forceinline__ uint32_t transpose32(uint32_t x, const XposeCtl& c) {
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    const uint32_t y = __shfl_xor_sync(0xFFFFFFFFu, x, 16u >> i);
+    const uint32_t moved = __funnelshift_l(y, y, c.rot[i]);
+    x = (x & c.keep[i]) | (moved & ~c.keep[i]);
+  }
+  return x;
+}
+
+// ------------------------------------------------------------------------------------------
+// parameters
+// ------------------------------------------------------------------------------------------
+
+struct LayoutDev {
+  uint32_t n_used;
+  uint32_t kind[DSM_MAX_COLS];
+  uint32_t card[DSM_MAX_COLS];
+  uint32_t flags[DSM_MAX_COLS];
+  uint32_t aux[DSM_MAX_COLS];
+  uint32_t rec_off[DSM_MAX_COLS];
+  uint32_t base[DSM_MAX_COLS];  // first table entry of the column inside a group's table
+  uint32_t rec_words;
+  uint32_t n_entries;           // entries per group table (sum of card)
+};
+
+struct BuildParams {
+  LayoutDev lay;
+  const uint32_t* recs;
+  uint32_t n_jobs;
+  const uint32_t* gpu_entries;
+  const uint32_t* bk_entries;
+  uint4* tabs;  // [groups][n_entries] x 4 words
+};
+
+// Chunking of the flattened (group, block) space shared by k_match and k_merge.
+struct Chunking {
+  unsigned long long total;  // groups * blocks
+  uint32_t grid;             // CTAs
+  uint32_t n_blocks;         // 32-row blocks per group
+  __host__ __device__ unsigned long long begin(uint32_t c) const { return total * c / grid; }
+  __host__ __device__ uint32_t cta_of(unsigned long long pos) const {
+    uint32_t c = (uint32_t)(pos * grid / total);
+    while (c + 1 < grid && begin(c + 1) <= pos) ++c;
+    while (c > 0 && begin(c) > pos) --c;
+    return c;
+  }
+};
+
+struct MatchParams {
+  const uint4* rows;
+  const uint4* tabs;
+  const uint32_t* recs;
+  const uint16_t* lut[DSM_MAX_COLS];
+  uint32_t base[DSM_MAX_COLS];
+  Chunking ch;
+  uint32_t rec_words;
+  uint32_t n_entries;
+  uint32_t n_jobs;
+  uint32_t split_block;  // first block of the second segment
+  uint32_t k;
+  uint32_t slots;        // slots per job (allocation stride)
+  uint32_t* part_cnt;    // [jobs_pad][slots]
+  uint32_t* part_last;   // [jobs_pad][slots]
+  uint32_t* part_idx;    // [jobs_pad][slots][k]
+  uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
+};
+
+struct MergeParams {
+  const uint32_t* part_cnt;
+  const uint32_t* part_last;
+  const uint32_t* part_idx;
+  const double* price;
+  Chunking ch;
+  uint32_t n_jobs, k, slots;
+  uint32_t* out_idx;
+  uint32_t* out_cnt;
+  uint32_t* out_max;
+};
+
+// ------------------------------------------------------------------------------------------
+// k_build_tables: grid (groups*4, n_used), block 256 = 8 warps; lane = job of the tile,
+// warps stride over the column's dictionary entries; one ballot = one table word.
+// ------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
+  const uint32_t tile = blockIdx.x;
+  const uint32_t col = blockIdx.y;
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t job = tile * 32u + lane;
+  const bool live = job < p.n_jobs;
+  const uint32_t* rec = p.recs + (size_t)(live ? job : 0) * p.lay.rec_words + p.lay.rec_off[col];
+  const uint32_t kind = p.lay.kind[col];
+  const uint32_t card = p.lay.card[col];
+  uint4* out = p.tabs + (size_t)(tile / TPG) * p.lay.n_entries + p.lay.base[col];
+  const uint32_t sub = tile % TPG;
+
+  uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0, r4 = 0;
+  if (live) {
+    r0 = rec[0];
+    if (kind == DSM_COL_GPU) { r1 = rec[1]; r2 = rec[2]; r3 = rec[3]; r4 = rec[4]; }
+    if (kind == DSM_COL_BK) { r1 = rec[1]; r2 = rec[2]; r3 = rec[3]; }
+  }
+
+  for (uint32_t e = warp; e < card; e += 8u) {
+    bool ok = false;
+    if (live) {
+      if (kind == DSM_COL_RANGE) {
+        const uint32_t lo = r0 & 0xFFFFu, hi = r0 >> 16;
+        ok = (e >= lo && e <= hi);
+        if ((p.lay.flags[col] & DSM_COLF_NULL_PASSES) && e == card - 1u) ok = true;
+      } else if (kind == DSM_COL_BITSET) {
+        ok = (rec[e >> 5] >> (e & 31u)) & 1u;
+      } else if (kind == DSM_COL_GPU) {
+        const uint32_t* ent = p.gpu_entries + (size_t)e * DSM_GPU_ENTRY_WORDS;
+        const uint32_t e0 = ent[0], e1 = ent[1], e2 = ent[2];
+        const uint32_t cnt = e0 & 0xFFFFu, mem = e0 >> 16;
+        const uint32_t tot = e1 & 0xFFFFu, cc = e1 >> 16;
+        const uint32_t name = e2 & 0xFFFFu, vendor = (e2 >> 16) & 0xFFu, has_gpu = (e2 >> 24) & 1u;
+        const uint32_t gflags = r3 >> 16, cc_min = r3 & 0xFFFFu;
+        ok = cnt >= (r0 & 0xFFFFu) && cnt <= (r0 >> 16);                       // item 6
+        ok = ok && ((r4 >> vendor) & 1u);                                      // item 7
+        if (!(gflags & DSM_GPUF_NAME_ANY))                                     // item 8
+          ok = ok && name != 0xFFFFu && ((rec[5 + (name >> 5)] >> (name & 31u)) & 1u);
+        if (gflags & DSM_GPUF_MEM_BOUNDED)                                     // item 9
+          ok = ok && has_gpu && mem >= (r1 & 0xFFFFu) && mem <= (r1 >> 16);
+        if (gflags & DSM_GPUF_CC_BOUNDED)                                      // item 10
+          ok = ok && cc != 0xFFFFu && cc >= cc_min;
+        ok = ok && tot >= (r2 & 0xFFFFu) && tot <= (r2 >> 16);                 // item 11
+      } else if (kind == DSM_COL_BK) {
+        const uint32_t* ent = p.bk_entries + (size_t)e * DSM_BK_ENTRY_WORDS;
+        const uint32_t e0 = ent[0], fl = ent[1];
+        const uint32_t src = e0 & 0xFFu, off = (e0 >> 8) & 0xFFu, spot = (e0 >> 16) & 0xFFu,
+                       status = e0 >> 24;
+        ok = e != 0u;  // entry 0 is the dead entry
+        ok = ok && ((r0 >> src) & 1u) && ((r1 >> off) & 1u);
+        ok = ok && ((r2 >> spot) & 1u) && ((r2 >> (8u + status)) & 1u);
+        const uint32_t req = r3 & 0xFFFFu, forbid = r3 >> 16;
+        ok = ok && ((fl & req) == req) && ((fl & forbid) == 0u);
+      }
+    }
+    const uint32_t word = __ballot_sync(0xFFFFFFFFu, ok);
+    if (lane == 0) reinterpret_cast<uint32_t*>(out + e)[sub] = word;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_match
+// ------------------------------------------------------------------------------------------
+
+template <int NC>
+struct RowCodes {
+  uint32_t w[(NC + 1) / 2];
+};
+
+template <int NC, bool ROW32>
+__device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCodes<NC>& rc) {
+  if constexpr (!ROW32) {
+    const uint4 v = ldg_stream(rows + row);
+    const uint32_t t[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < (NC + 1) / 2; ++i) rc.w[i] = t[i];
+  } else {
+    const uint4 v0 = ldg_stream(rows + 2 * (size_t)row);
+    uint4 v1 = make_uint4(0, 0, 0, 0);
+    if constexpr (NC > 8) v1 = ldg_stream(rows + 2 * (size_t)row + 1);
+    const uint32_t t[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+    for (int i = 0; i < (NC + 1) / 2; ++i) rc.w[i] = t[i];
+  }
+}
+
+template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT>
+__global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  uint4* s_tab = reinterpret_cast<uint4*>(smem_raw);
+  uint32_t* s_cut = reinterpret_cast<uint32_t*>(smem_raw + (size_t)p.n_entries * 16u);  // [2][128]
+  __shared__ __align__(8) uint64_t s_bar;
+
+  const uint32_t tid = threadIdx.x;
+  const uint32_t lane = tid & 31u;
+  const uint32_t warp = tid >> 5;
+  XposeCtl xc;
+  transpose_setup(xc, lane);
+
+  uint32_t taddr[NC];  // shared-memory byte address of each column's first table entry
+#pragma unroll
+  for (int c = 0; c < NC; ++c) taddr[c] = smem_u32(s_tab) + p.base[c] * 16u;
+
+  if (tid == 0) {
+    mbar_init(&s_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  const uint32_t n_blocks = p.ch.n_blocks;
+  unsigned long long pos = p.ch.begin(blockIdx.x);
+  const unsigned long long end = p.ch.begin(blockIdx.x + 1);
+  uint32_t parity = 0;
+
+  while (pos < end) {
+    const uint32_t group = (uint32_t)(pos / n_blocks);
+    const uint32_t blk_lo = (uint32_t)(pos - (unsigned long long)group * n_blocks);
+    const unsigned long long room = end - pos;
+    const uint32_t blk_hi = room < (n_blocks - blk_lo) ? blk_lo + (uint32_t)room : n_blocks;
+    pos += blk_hi - blk_lo;
+
+    // ---- stage this group's acceptance table (TMA bulk copy) and cut-off rows
+    __syncthreads();  // everyone is done reading the previous table
+    if (tid == 0) {
+      const uint32_t bytes = p.n_entries * 16u;
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      mbar_expect_tx(&s_bar, bytes);
+      bulk_g2s(s_tab, p.tabs + (size_t)group * p.n_entries, bytes, &s_bar);
+    }
+    if (tid < JPG) {
+      const uint32_t job = group * JPG + tid;
+      uint32_t ca = 0, cb = 0;  // padding jobs accept nothing
+      if (job < p.n_jobs) {
+        ca = p.recs[(size_t)job * p.rec_words + 0];
+        cb = p.recs[(size_t)job * p.rec_words + 1];
+      }
+      s_cut[tid] = ca;
+      s_cut[JPG + tid] = cb;
+    }
+    mbar_wait(&s_bar, parity);
+    parity ^= 1u;
+    __syncthreads();
+
+    const uint32_t c_rel = blockIdx.x - p.ch.cta_of((unsigned long long)group * n_blocks);
+
+#pragma unroll 1
+    for (uint32_t seg = 0; seg < 2; ++seg) {
+      // the piece of [blk_lo, blk_hi) inside this segment, split evenly over the warps
+      const uint32_t lo = seg == 0 ? blk_lo : max(blk_lo, p.split_block);
+      const uint32_t hi = seg == 0 ? min(blk_hi, p.split_block) : blk_hi;
+      const uint32_t len = hi > lo ? hi - lo : 0u;
+      const uint32_t b0 = lo + (uint32_t)(((unsigned long long)len * warp) / MATCH_WARPS);
+      const uint32_t b1 = lo + (uint32_t)(((unsigned long long)len * (warp + 1)) / MATCH_WARPS);
+      const uint32_t* cut = s_cut + seg * JPG;
+      const uint32_t slot = (c_rel * 2u + seg) * MATCH_WARPS + warp;
+
+      // rows below a job's cut-off pass the price/availability test.  full: all rows of this
+      // warp's range pass; part: the cut-off lies inside the range; neither: none pass.
+      uint32_t full[TPG], part[TPG];
+#pragma unroll
+      for (int t = 0; t < TPG; ++t) {
+        const uint32_t c = cut[t * 32 + lane];
+        full[t] = __ballot_sync(0xFFFFFFFFu, c >= b1 * 32u);
+        part[t] = __ballot_sync(0xFFFFFFFFu, c > b0 * 32u && c < b1 * 32u);
+      }
+
+      uint32_t cnt[TPG], last[TPG];
+#pragma unroll
+      for (int t = 0; t < TPG; ++t) { cnt[t] = 0; last[t] = DSM_NO_ROW; }
+
+      RowCodes<NC> rc;
+      if (b0 < b1) load_row<NC, ROW32>(p.rows, b0 * 32u + lane, rc);
+
+#pragma unroll 1
+      for (uint32_t blk = b0; blk < b1; ++blk) {
+        const RowCodes<NC> cur = rc;
+        if (blk + 1 < b1) load_row<NC, ROW32>(p.rows, (blk + 1) * 32u + lane, rc);  // prefetch
+        const uint32_t row = blk * 32u + lane;
+
+        // gather one 128-bit word group per column and AND them
+        uint4 m = make_uint4(full[0], full[1], full[2], full[3]);
+        if (part[0] | part[1] | part[2] | part[3]) {  // warp-uniform, rare
+          uint32_t pw[TPG] = {0, 0, 0, 0};
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) {
+            uint32_t rest = part[t];
+            while (rest) {
+              const uint32_t j = __ffs(rest) - 1;
+              rest &= rest - 1;
+              pw[t] |= (row < cut[t * 32 + j]) ? (1u << j) : 0u;
+            }
+          }
+          m.x |= pw[0]; m.y |= pw[1]; m.z |= pw[2]; m.w |= pw[3];
+        }
+#pragma unroll
+        for (int c = 0; c < NC; ++c) {
+          uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
+          if constexpr (HAS_LUT) {
+            if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+          }
+          const uint4 a = lds128(taddr[c] + (code << 4));
+          m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
+        }
+
+        const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          const uint32_t T = transpose32(mm[t], xc);  // lane j: rows of the block matching job 32t+j
+          if constexpr (BITMAP) {
+            const uint32_t job = group * JPG + t * 32 + lane;
+            if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T;
+          } else {
+            if (T) {
+              last[t] = blk * 32u + 31u - __clz(T);
+              if (cnt[t] < p.k) {
+                uint32_t* dst = p.part_idx + ((size_t)(group * JPG + t * 32 + lane) * p.slots + slot) * p.k;
+                uint32_t w = T, n = cnt[t];
+                while (w && n < p.k) {
+                  dst[n++] = blk * 32u + (__ffs(w) - 1);
+                  w &= w - 1;
+                }
+              }
+              cnt[t] += __popc(T);
+            }
+          }
+        }
+      }
+
+      if constexpr (!BITMAP) {
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          const size_t o = (size_t)(group * JPG + t * 32 + lane) * p.slots + slot;
+          p.part_cnt[o] = cnt[t];
+          p.part_last[o] = last[t];
+        }
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_merge: one warp per job walks the job's slots in row order, 32 slots at a time.
+// ------------------------------------------------------------------------------------------
+
+__global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t job = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (job >= p.n_jobs) return;
+  const uint32_t group = job / JPG;
+  const unsigned long long g0 = (unsigned long long)group * p.ch.n_blocks;
+  const uint32_t c_first = p.ch.cta_of(g0);
+  const uint32_t c_last = p.ch.cta_of(g0 + p.ch.n_blocks - 1);
+  const uint32_t n_slots = (c_last - c_first + 1) * SLOTS_PER_CTA;
+  const uint32_t* cnt = p.part_cnt + (size_t)job * p.slots;
+  const uint32_t* lst = p.part_last + (size_t)job * p.slots;
+  const uint32_t* idx = p.part_idx + (size_t)job * p.slots * p.k;
+  uint32_t* out = p.out_idx + (size_t)job * p.k;
+
+  uint32_t total = 0, have = 0;
+  uint32_t last_a = DSM_NO_ROW, last_b = DSM_NO_ROW;
+  for (uint32_t s0 = 0; s0 < n_slots; s0 += 32) {
+    const uint32_t s = s0 + lane;
+    const uint32_t c = s < n_slots ? cnt[s] : 0u;
+    uint32_t incl = c;  // inclusive prefix sum over the 32 slots
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= (uint32_t)d) incl += v;
+    }
+    const uint32_t before = have + (incl - c);  // matches that precede this slot
+    if (c && before < p.k) {
+      const uint32_t take = min(min(c, p.k), p.k - before);
+      const uint32_t* src = idx + (size_t)s * p.k;
+      for (uint32_t i = 0; i < take; ++i) out[before + i] = src[i];
+    }
+    const bool seg_b = (s / MATCH_WARPS) & 1u;
+    const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c != 0 && !seg_b);
+    const uint32_t hit_b = __ballot_sync(0xFFFFFFFFu, c != 0 && seg_b);
+    const uint32_t l = c ? lst[s] : DSM_NO_ROW;
+    if (hit_a) last_a = __shfl_sync(0xFFFFFFFFu, l, 31 - __clz(hit_a));
+    if (hit_b) last_b = __shfl_sync(0xFFFFFFFFu, l, 31 - __clz(hit_b));
+    const uint32_t sum = __shfl_sync(0xFFFFFFFFu, incl, 31);
+    total += sum;
+    have = min(p.k, have + sum);  // saturating: only used against k
+  }
+  for (uint32_t i = have + lane; i < p.k; i += 32) out[i] = DSM_NO_ROW;
+  if (lane == 0) {
+    p.out_cnt[job] = total;
+    uint32_t best = last_a;
+    if (last_b != DSM_NO_ROW) {
+      if (best == DSM_NO_ROW) best = last_b;
+      else if (p.price != nullptr && p.price[last_b] > p.price[last_a]) best = last_b;
+    }
+    p.out_max[job] = best;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// utility kernels
+// ------------------------------------------------------------------------------------------
+
+__global__ void k_gather_price(const double* price, const uint32_t* rows, uint32_t n, double* out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t r = rows[i];
+  out[i] = (r == DSM_NO_ROW || price == nullptr) ? __longlong_as_double(0x7FF8000000000000LL) : price[r];
+}
+
+// Shards are in table order: concatenate per-shard first-k lists, sum counts, keep the
+// highest-priced max row.  One thread per job.
+__global__ void k_merge_shards(uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                               const uint32_t* idx_all, const uint32_t* cnt_all,
+                               const uint32_t* max_all, const double* maxprice_all,
+                               const uint64_t* shard_base, uint64_t* idx_out, uint64_t* cnt_out,
+                               uint64_t* max_out, double* maxprice_out) {
+  const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+  if (job >= n_jobs) return;
+  uint64_t total = 0;
+  uint32_t have = 0;
+  uint64_t best = ~0ull;
+  double best_price = 0.0;
+  for (uint32_t s = 0; s < n_shards; ++s) {
+    const size_t o = (size_t)s * n_jobs + job;
+    const uint32_t c = cnt_all[o];
+    if (c == 0) continue;
+    const uint32_t take = min(min(c, k), k - have);
+    for (uint32_t i = 0; i < take; ++i)
+      idx_out[(size_t)job * k + have + i] = shard_base[s] + idx_all[o * k + i];
+    have += take;
+    total += c;
+    const uint32_t m = max_all[o];
+    if (m != DSM_NO_ROW) {
+      const double pr = maxprice_all[o];
+      if (best == ~0ull || pr > best_price) { best = shard_base[s] + m; best_price = pr; }
+    }
+  }
+  for (uint32_t i = have; i < k; ++i) idx_out[(size_t)job * k + i] = ~0ull;
+  cnt_out[job] = total;
+  max_out[job] = best;
+  maxprice_out[job] = (best == ~0ull) ? __longlong_as_double(0x7FF8000000000000LL) : best_price;
+}

@@ -412,6 +412,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     cflags: List[int] = []
     aux: List[int] = []
     luts: Dict[int, np.ndarray] = {}
+    trivial: List[bool] = []  # per column: every job accepts every entry
 
     # words 0,1: row cut-offs (max_price and exclude_not_available)
     mp = np.asarray(jc.max_price, dtype=np.float64)
@@ -430,6 +431,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
         cards.append(card)
         cflags.append(flags)
         aux.append(ax)
+        trivial.append(False)
         pos += words.shape[1]
 
     def add_set(col_idx: int, any_mask, ptr, ids, unknown_passes: bool) -> None:
@@ -451,6 +453,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
         nw = (card + 31) // 32
         bits = _bitset_from_csr(any_mask, ptr, ids, nw, pass_bits=[card - 1] if unknown_passes else [])
         add(bits, KIND_BITSET, card)
+        trivial[-1] = bool(any_mask.all())
 
     c = t.col
     add(_range_words(t.columns[c("cpu")].values, jc.cpu), KIND_RANGE, t.columns[c("cpu")].card)
@@ -517,6 +520,12 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     for p in parts:
         rec[:, o:o + p.shape[1]] = p
         o += p.shape[1]
+    # trailing columns on which no job of this call filters need not be gathered at all
+    n_used = len(kinds)
+    while n_used > c("bk") + 1 and trivial[n_used - 1]:
+        n_used -= 1
+        luts.pop(n_used, None)
+    kinds, cards, cflags, aux, offs = (x[:n_used] for x in (kinds, cards, cflags, aux, offs))
     layout = dict(n_used=len(kinds), kind=kinds, card=cards, flags=cflags, aux=aux, rec_off=offs,
                   rec_words=rec_words)
     return PackedJobs(records=rec, layout=layout, luts=luts)
