@@ -255,6 +255,7 @@ struct RowCodes {
   uint32_t w[(NC + 1) / 2];
 };
 
+// `rows` already points at this lane's row of block 0; `row` is the first row of the block.
 template <int NC, bool ROW32>
 __device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCodes<NC>& rc) {
   if constexpr (!ROW32) {
@@ -296,6 +297,8 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   __syncthreads();
 
   const uint32_t n_blocks = p.ch.n_blocks;
+  const uint32_t kk = p.k;
+  const uint4* rows_lane = p.rows + (ROW32 ? 2u * lane : lane);  // this lane's row inside a block
   unsigned long long pos = p.ch.begin(blockIdx.x);
   const unsigned long long end = p.ch.begin(blockIdx.x + 1);
   uint32_t parity = 0;
@@ -352,17 +355,20 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         part[t] = __ballot_sync(0xFFFFFFFFu, c > b0 * 32u && c < b1 * 32u);
       }
 
-      uint32_t cnt[TPG], last[TPG];
+      uint32_t cnt[TPG], last_word[TPG], last_blk[TPG];
 #pragma unroll
-      for (int t = 0; t < TPG; ++t) { cnt[t] = 0; last[t] = DSM_NO_ROW; }
+      for (int t = 0; t < TPG; ++t) { cnt[t] = 0; last_word[t] = 0; last_blk[t] = 0; }
 
-      RowCodes<NC> rc;
-      if (b0 < b1) load_row<NC, ROW32>(p.rows, b0 * 32u + lane, rc);
+      // rows are prefetched two blocks ahead (L2 latency is longer than one block of work)
+      RowCodes<NC> rc0, rc1;
+      if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, rc0);
+      if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rc1);
 
 #pragma unroll 1
       for (uint32_t blk = b0; blk < b1; ++blk) {
-        const RowCodes<NC> cur = rc;
-        if (blk + 1 < b1) load_row<NC, ROW32>(p.rows, (blk + 1) * 32u + lane, rc);  // prefetch
+        const RowCodes<NC> cur = rc0;
+        rc0 = rc1;
+        if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, rc1);
         const uint32_t row = blk * 32u + lane;
 
         // gather one 128-bit word group per column and AND them
@@ -390,27 +396,52 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
           m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
         }
 
-        const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
+        // four independent 32x32 transposes, interleaved step by step so the shuffles overlap:
+        // afterwards lane j holds in T[t] the rows of this block that match job 32t+j
+        uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
 #pragma unroll
-        for (int t = 0; t < TPG; ++t) {
-          const uint32_t T = transpose32(mm[t], xc);  // lane j: rows of the block matching job 32t+j
-          if constexpr (BITMAP) {
+        for (int i = 0; i < 5; ++i) {
+          uint32_t y[TPG];
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(0xFFFFFFFFu, T[t], 16u >> i);
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) {
+            const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
+            T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
+          }
+        }
+
+        if constexpr (BITMAP) {
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) {
             const uint32_t job = group * JPG + t * 32 + lane;
-            if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T;
-          } else {
-            if (T) {
-              last[t] = blk * 32u + 31u - __clz(T);
-              if (cnt[t] < p.k) {
-                uint32_t* dst = p.part_idx + ((size_t)(group * JPG + t * 32 + lane) * p.slots + slot) * p.k;
-                uint32_t w = T, n = cnt[t];
-                while (w && n < p.k) {
+            if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T[t];
+          }
+        } else {
+          // branch-free bookkeeping; the (rare) first-k append is behind one warp-uniform vote
+          bool want = false;
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) {
+            const bool hit = T[t] != 0u;
+            want = want || (hit && cnt[t] < kk);
+            last_word[t] = hit ? T[t] : last_word[t];
+            last_blk[t] = hit ? blk : last_blk[t];
+          }
+          if (__any_sync(0xFFFFFFFFu, want)) {
+#pragma unroll
+            for (int t = 0; t < TPG; ++t) {
+              if (T[t] != 0u && cnt[t] < kk) {
+                uint32_t* dst = p.part_idx + ((size_t)(group * JPG + t * 32 + lane) * p.slots + slot) * kk;
+                uint32_t w = T[t], n = cnt[t];
+                while (w && n < kk) {
                   dst[n++] = blk * 32u + (__ffs(w) - 1);
                   w &= w - 1;
                 }
               }
-              cnt[t] += __popc(T);
             }
           }
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) cnt[t] += __popc(T[t]);
         }
       }
 
@@ -419,7 +450,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         for (int t = 0; t < TPG; ++t) {
           const size_t o = (size_t)(group * JPG + t * 32 + lane) * p.slots + slot;
           p.part_cnt[o] = cnt[t];
-          p.part_last[o] = last[t];
+          p.part_last[o] = last_word[t] ? last_blk[t] * 32u + 31u - __clz(last_word[t]) : DSM_NO_ROW;
         }
       }
     }
