@@ -20,6 +20,7 @@
 // ranker at server/services/backends/__init__.py:449-451 (see include/dsmatch.h).
 
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <mutex>
@@ -103,7 +104,7 @@ static int ensure(DevBuf& b, size_t bytes) {
 struct Plan {
   LayoutDev lay;
   Chunking ch;
-  uint32_t n_groups, n_blocks, split_block, slots, smem;
+  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift;
 };
 
 static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, uint32_t n_jobs,
@@ -133,9 +134,20 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     base += L->card[c];
   }
   d.n_entries = base;
-  pl.smem = base * 16u + 2u * JPG * 4u;
-  if (pl.smem > MAX_SMEM_BYTES)
+  // Replicate the table in shared memory as far as it fits: 8 copies make the gathers
+  // bank-conflict free.  Prefer keeping MATCH_CTAS_PER_SM CTAs resident, then fewer copies.
+  const uint32_t cuts = 2u * JPG * 4u;
+  if (base * 16u + cuts > MAX_SMEM_BYTES)
     return fail(DSM_E_DICT_TOO_LARGE, "acceptance tables need more shared memory than one CTA has");
+  const char* force_rep = getenv("DSM_REP_SHIFT");  // tuning / tests only
+  pl.rep_shift = 0;
+  for (uint32_t rs = 3; rs >= 1; --rs) {
+    const uint32_t need = base * 16u * ((1u << rs) + 1u) + cuts;
+    if (need <= MAX_SMEM_BYTES / MATCH_CTAS_PER_SM) { pl.rep_shift = rs; break; }
+  }
+  if (force_rep) pl.rep_shift = (uint32_t)atoi(force_rep) & 3u;
+  pl.smem = base * 16u * (pl.rep_shift ? (1u << pl.rep_shift) + 1u : 1u) + cuts;
+  if (pl.smem > MAX_SMEM_BYTES) { pl.rep_shift = 0; pl.smem = base * 16u + cuts; }
   pl.n_groups = (n_jobs + JPG - 1) / JPG;
   pl.n_blocks = t->desc.n_rows / 32u;
   pl.split_block = t->desc.split_row / 32u;
@@ -215,7 +227,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   if (!bitmap) {
     if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
     if ((rc = ensure(ctx->part_last, jobs_pad * pl.slots * 4))) return rc;
-    if ((rc = ensure(ctx->part_idx, jobs_pad * pl.slots * k * 4))) return rc;
+    if ((rc = ensure(ctx->part_idx, jobs_pad * pl.slots * k * 8))) return rc;  // (block, word) entries
   }
 
   BuildParams bp;
@@ -243,6 +255,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   mp.ch = pl.ch;
   mp.rec_words = L->rec_words;
   mp.n_entries = pl.lay.n_entries;
+  mp.rep_shift = pl.rep_shift;
   mp.n_jobs = n_jobs;
   mp.split_block = pl.split_block;
   mp.k = k;
@@ -543,6 +556,16 @@ int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches) {
   ctx->timing_used = 0;
   return 0;
 }
+
+#ifdef DSM_CTA_TIMING
+// debug builds only: copy the per-CTA (start ns, end ns, SM id) triples of the last k_match
+int dsm_debug_cta_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_ctas) {
+  CK(cudaSetDevice(ctx->device));
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaMemcpyFromSymbol(out, g_cta_times, (size_t)n_ctas * 3 * 8));
+  return 0;
+}
+#endif
 
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, uint32_t n_jobs,
                    uint32_t out[8]) {

@@ -157,13 +157,14 @@ struct MatchParams {
   Chunking ch;
   uint32_t rec_words;
   uint32_t n_entries;
+  uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0..3)
   uint32_t n_jobs;
   uint32_t split_block;  // first block of the second segment
   uint32_t k;
   uint32_t slots;        // slots per job (allocation stride)
   uint32_t* part_cnt;    // [jobs_pad][slots]
   uint32_t* part_last;   // [jobs_pad][slots]
-  uint32_t* part_idx;    // [jobs_pad][slots][k]
+  uint32_t* part_idx;    // [jobs_pad][slots][k] x (block, match word)
   uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
 };
 
@@ -250,6 +251,11 @@ __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
 // k_match
 // ------------------------------------------------------------------------------------------
 
+#ifdef DSM_CTA_TIMING
+// debug builds only (tools/cta_times.py): start / end globaltimer and SM id of every CTA
+__device__ unsigned long long g_cta_times[4096 * 3];
+#endif
+
 template <int NC>
 struct RowCodes {
   uint32_t w[(NC + 1) / 2];
@@ -275,9 +281,16 @@ __device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCod
 
 template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
+  // shared memory: [staging: E entries][table: E entries x R copies][cut-offs: 2 x 128]
+  // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
+  // R = 8 copy r lies in bank group r (4 banks), lane l reads copy l%8, and the 8 lanes of every
+  // quarter-warp phase of a 128-bit gather hit 8 different bank groups: no bank conflicts
+  // whatever the codes are.  R < 8 (large dictionaries) only reduces them.
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  uint4* s_tab = reinterpret_cast<uint4*>(smem_raw);
-  uint32_t* s_cut = reinterpret_cast<uint32_t*>(smem_raw + (size_t)p.n_entries * 16u);  // [2][128]
+  const uint32_t rep_shift = p.rep_shift;
+  uint4* s_stage = reinterpret_cast<uint4*>(smem_raw);
+  uint4* s_tab = rep_shift ? s_stage + p.n_entries : s_stage;
+  uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + ((size_t)p.n_entries << rep_shift));  // [2][128]
   __shared__ __align__(8) uint64_t s_bar;
 
   const uint32_t tid = threadIdx.x;
@@ -286,9 +299,11 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   XposeCtl xc;
   transpose_setup(xc, lane);
 
-  uint32_t taddr[NC];  // shared-memory byte address of each column's first table entry
+  const uint32_t code_shift = 4u + rep_shift;
+  uint32_t taddr[NC];  // shared-memory byte address of this lane's copy of each column's entry 0
 #pragma unroll
-  for (int c = 0; c < NC; ++c) taddr[c] = smem_u32(s_tab) + p.base[c] * 16u;
+  for (int c = 0; c < NC; ++c)
+    taddr[c] = smem_u32(s_tab) + (p.base[c] << code_shift) + ((lane & ((1u << rep_shift) - 1u)) << 4);
 
   if (tid == 0) {
     mbar_init(&s_bar, 1);
@@ -302,6 +317,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   unsigned long long pos = p.ch.begin(blockIdx.x);
   const unsigned long long end = p.ch.begin(blockIdx.x + 1);
   uint32_t parity = 0;
+#ifdef DSM_CTA_TIMING
+  unsigned long long dbg_t0 = 0;
+  if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
+#endif
 
   while (pos < end) {
     const uint32_t group = (uint32_t)(pos / n_blocks);
@@ -316,7 +335,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       const uint32_t bytes = p.n_entries * 16u;
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
       mbar_expect_tx(&s_bar, bytes);
-      bulk_g2s(s_tab, p.tabs + (size_t)group * p.n_entries, bytes, &s_bar);
+      bulk_g2s(s_stage, p.tabs + (size_t)group * p.n_entries, bytes, &s_bar);
     }
     if (tid < JPG) {
       const uint32_t job = group * JPG + tid;
@@ -330,6 +349,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     }
     mbar_wait(&s_bar, parity);
     parity ^= 1u;
+    if (rep_shift) {  // fan the staged table out into its R interleaved copies
+      const uint32_t n_copy = p.n_entries << rep_shift;
+      for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = s_stage[i >> rep_shift];
+    }
     __syncthreads();
 
     const uint32_t c_rel = blockIdx.x - p.ch.cta_of((unsigned long long)group * n_blocks);
@@ -355,9 +378,13 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         part[t] = __ballot_sync(0xFFFFFFFFu, c > b0 * 32u && c < b1 * 32u);
       }
 
-      uint32_t cnt[TPG], last_word[TPG], last_blk[TPG];
+      uint32_t cnt[TPG], ent[TPG], last_word[TPG], last_blk[TPG];
 #pragma unroll
-      for (int t = 0; t < TPG; ++t) { cnt[t] = 0; last_word[t] = 0; last_blk[t] = 0; }
+      for (int t = 0; t < TPG; ++t) { cnt[t] = 0; ent[t] = 0; last_word[t] = 0; last_blk[t] = 0; }
+      // first-k log of (job = 32t + lane, this slot): [jobs_pad][slots][k] entries of 8 bytes
+      uint2* log_lane = reinterpret_cast<uint2*>(p.part_idx) +
+                        ((size_t)(group * JPG + lane) * p.slots + slot) * kk;
+      const size_t log_tile_stride = (size_t)32 * p.slots * kk;
 
       // rows are prefetched two blocks ahead (L2 latency is longer than one block of work)
       RowCodes<NC> rc0, rc1;
@@ -392,7 +419,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
           if constexpr (HAS_LUT) {
             if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
           }
-          const uint4 a = lds128(taddr[c] + (code << 4));
+          const uint4 a = lds128(taddr[c] + (code << code_shift));
           m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
         }
 
@@ -428,15 +455,13 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
             last_blk[t] = hit ? blk : last_blk[t];
           }
           if (__any_sync(0xFFFFFFFFu, want)) {
+            // a job that still lacks k matches logs (block, match word); k_merge expands the
+            // words to rows.  At most k entries per (job, slot): every entry has >= 1 match.
 #pragma unroll
             for (int t = 0; t < TPG; ++t) {
               if (T[t] != 0u && cnt[t] < kk) {
-                uint32_t* dst = p.part_idx + ((size_t)(group * JPG + t * 32 + lane) * p.slots + slot) * kk;
-                uint32_t w = T[t], n = cnt[t];
-                while (w && n < kk) {
-                  dst[n++] = blk * 32u + (__ffs(w) - 1);
-                  w &= w - 1;
-                }
+                log_lane[(size_t)t * log_tile_stride + ent[t]] = make_uint2(blk, T[t]);
+                ent[t] += 1;
               }
             }
           }
@@ -455,6 +480,18 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       }
     }
   }
+#ifdef DSM_CTA_TIMING
+  __syncthreads();
+  if (tid == 0 && blockIdx.x < 4096) {
+    unsigned long long t1;
+    uint32_t smid;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_cta_times[blockIdx.x * 3 + 0] = dbg_t0;
+    g_cta_times[blockIdx.x * 3 + 1] = t1;
+    g_cta_times[blockIdx.x * 3 + 2] = smid;
+  }
+#endif
 }
 
 // ------------------------------------------------------------------------------------------
@@ -472,7 +509,7 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
   const uint32_t n_slots = (c_last - c_first + 1) * SLOTS_PER_CTA;
   const uint32_t* cnt = p.part_cnt + (size_t)job * p.slots;
   const uint32_t* lst = p.part_last + (size_t)job * p.slots;
-  const uint32_t* idx = p.part_idx + (size_t)job * p.slots * p.k;
+  const uint2* log = reinterpret_cast<const uint2*>(p.part_idx) + (size_t)job * p.slots * p.k;
   uint32_t* out = p.out_idx + (size_t)job * p.k;
 
   uint32_t total = 0, have = 0;
@@ -488,9 +525,19 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
     }
     const uint32_t before = have + (incl - c);  // matches that precede this slot
     if (c && before < p.k) {
-      const uint32_t take = min(min(c, p.k), p.k - before);
-      const uint32_t* src = idx + (size_t)s * p.k;
-      for (uint32_t i = 0; i < take; ++i) out[before + i] = src[i];
+      // expand the slot's log of (block, match word) entries into rows, ascending
+      uint32_t take = min(c, p.k - before);
+      const uint2* src = log + (size_t)s * p.k;
+      uint32_t o = before;
+      for (uint32_t i = 0; take; ++i) {
+        const uint2 e = src[i];
+        uint32_t w = e.y;
+        while (w && take) {
+          out[o++] = e.x * 32u + (__ffs(w) - 1);
+          w &= w - 1;
+          --take;
+        }
+      }
     }
     const bool seg_b = (s / MATCH_WARPS) & 1u;
     const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c != 0 && !seg_b);

@@ -15,7 +15,7 @@ from typing import Any, Dict, Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdsmatch.so")
+LIB_PATH = os.environ.get("DSM_LIB") or os.path.join(_HERE, "libdsmatch.so")
 MAX_COLS = 16
 NO_ROW = 0xFFFFFFFF
 
