@@ -4,7 +4,7 @@
 //
 //   records [J][rec_words] u32 --k_build_tables--> tabs [groups][E][4] u32        (scratch)
 //   rows [N][n_cols] u16 + tabs --k_match--> per-slot partials                     (scratch)
-//        part_cnt [J][S], part_last [J][S], part_idx [J][S][k]
+//        part_cnt [J][S], part_last [J][S], part_log [J][S][k] x (block, match word)
 //   partials + price --k_merge--> idx [J][k], cnt [J], max [J]
 //
 // k_match is the hot kernel.  One thread owns one row (a single 128-bit load of its 8 codes,
@@ -82,7 +82,7 @@ struct dsm_ctx {
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
   size_t timing_used = 0;
-  DevBuf tabs, part_cnt, part_last, part_idx, d_jobs, d_idx, d_cnt, d_max, d_bits;
+  DevBuf tabs, counter, part_cnt, part_last, part_log, d_jobs, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
 };
 
@@ -103,8 +103,8 @@ static int ensure(DevBuf& b, size_t bytes) {
 
 struct Plan {
   LayoutDev lay;
-  Chunking ch;
-  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift;
+  Pieces pc;
+  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, grid;
 };
 
 static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, uint32_t n_jobs,
@@ -152,23 +152,34 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   pl.n_blocks = t->desc.n_rows / 32u;
   pl.split_block = t->desc.split_row / 32u;
 
-  // One chunk of the flattened (group, block) space per CTA; as many CTAs as fit on the GPU
-  // at once (a multiple of the SM count), fewer when there is not enough work to give every
-  // warp a few blocks.
+  // Resident CTAs: a multiple of the SM count.  Work units (piece, group): about UNITS_PER_CTA
+  // per resident CTA so that the dynamic draw balances the SMs, but every warp of a unit keeps
+  // at least a couple of blocks.
   uint32_t per_sm = MATCH_CTAS_PER_SM;
   const uint32_t smem_cap = 220u * 1024u;
   while (per_sm > 1 && per_sm * (pl.smem + 1024u) > smem_cap) --per_sm;
-  const unsigned long long total = (unsigned long long)pl.n_groups * pl.n_blocks;
-  unsigned long long grid = (unsigned long long)ctx->sm_count * per_sm;
-  const unsigned long long min_chunk = MATCH_WARPS * 2ull;
-  if (grid * min_chunk > total) grid = (total + min_chunk - 1) / min_chunk;
-  if (grid < 1) grid = 1;
-  pl.ch.total = total;
-  pl.ch.grid = (uint32_t)grid;
-  pl.ch.n_blocks = pl.n_blocks;
-  const unsigned long long chunk_min = total / grid;  // >= 1
-  const unsigned long long ctas_per_group = (pl.n_blocks + chunk_min - 1) / chunk_min + 1;
-  pl.slots = (uint32_t)ctas_per_group * SLOTS_PER_CTA;
+  const uint32_t resident = (uint32_t)ctx->sm_count * per_sm;
+  const char* env_units = getenv("DSM_UNITS_PER_CTA");  // tuning only
+  const uint32_t units_per_cta = env_units ? (uint32_t)atoi(env_units) : 4u;
+  uint32_t want = (resident * (units_per_cta ? units_per_cta : 1u) + pl.n_groups - 1) / pl.n_groups;
+  if (want < 1) want = 1;
+  const uint32_t a_blocks = pl.split_block, b_blocks = pl.n_blocks - pl.split_block;
+  const uint32_t min_piece = MATCH_WARPS * 2u;
+  auto pieces_for = [&](uint32_t blocks) -> uint32_t {
+    if (blocks == 0) return 0u;
+    uint32_t n = (uint32_t)(((unsigned long long)want * blocks + pl.n_blocks - 1) / pl.n_blocks);
+    const uint32_t cap = blocks / min_piece;
+    if (n > cap) n = cap;
+    return n < 1 ? 1u : n;
+  };
+  pl.pc.n_groups = pl.n_groups;
+  pl.pc.n_blocks = pl.n_blocks;
+  pl.pc.split_block = pl.split_block;
+  pl.pc.pa = pieces_for(a_blocks);
+  pl.pc.pb = pieces_for(b_blocks);
+  pl.slots = pl.pc.per_group() * MATCH_WARPS;
+  const uint32_t units = pl.pc.count();
+  pl.grid = units < resident ? units : resident;
   return 0;
 }
 
@@ -224,10 +235,11 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
 
   const size_t jobs_pad = (size_t)pl.n_groups * JPG;
   if ((rc = ensure(ctx->tabs, (size_t)pl.n_groups * pl.lay.n_entries * 16))) return rc;
+  if ((rc = ensure(ctx->counter, 256))) return rc;
   if (!bitmap) {
     if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
     if ((rc = ensure(ctx->part_last, jobs_pad * pl.slots * 4))) return rc;
-    if ((rc = ensure(ctx->part_idx, jobs_pad * pl.slots * k * 8))) return rc;  // (block, word) entries
+    if ((rc = ensure(ctx->part_log, jobs_pad * pl.slots * k * 8))) return rc;  // (block, word) entries
   }
 
   BuildParams bp;
@@ -237,6 +249,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   bp.gpu_entries = t->gpu_entries;
   bp.bk_entries = t->bk_entries;
   bp.tabs = (uint4*)ctx->tabs.p;
+  bp.work_counter = (uint32_t*)ctx->counter.p;
   k_build_tables<<<dim3(pl.n_groups * TPG, pl.lay.n_used), 256, 0, ctx->stream>>>(bp);
   CK(cudaGetLastError());
   ctx->launches++;
@@ -252,17 +265,17 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     has_lut = has_lut || L->lut[c] != nullptr;
     mp.base[c] = pl.lay.base[c];
   }
-  mp.ch = pl.ch;
+  mp.pc = pl.pc;
   mp.rec_words = L->rec_words;
   mp.n_entries = pl.lay.n_entries;
   mp.rep_shift = pl.rep_shift;
   mp.n_jobs = n_jobs;
-  mp.split_block = pl.split_block;
   mp.k = k;
   mp.slots = pl.slots;
+  mp.work_counter = (uint32_t*)ctx->counter.p;
   mp.part_cnt = (uint32_t*)ctx->part_cnt.p;
   mp.part_last = (uint32_t*)ctx->part_last.p;
-  mp.part_idx = (uint32_t*)ctx->part_idx.p;
+  mp.part_log = (uint2*)ctx->part_log.p;
   mp.bits = d_bits;
 
   std::pair<cudaEvent_t, cudaEvent_t>* tev = nullptr;
@@ -276,8 +289,8 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     tev = &ctx->timing_events[ctx->timing_used++];
     CK(cudaEventRecord(tev->first, ctx->stream));
   }
-  cudaError_t e = bitmap ? launch_match<true>(L->n_used, row32, mp, has_lut, pl.ch.grid, pl.smem, ctx->stream)
-                         : launch_match<false>(L->n_used, row32, mp, has_lut, pl.ch.grid, pl.smem, ctx->stream);
+  cudaError_t e = bitmap ? launch_match<true>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
+                         : launch_match<false>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   if (tev) CK(cudaEventRecord(tev->second, ctx->stream));
   ctx->launches++;
@@ -286,12 +299,12 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     MergeParams gp;
     gp.part_cnt = mp.part_cnt;
     gp.part_last = mp.part_last;
-    gp.part_idx = mp.part_idx;
+    gp.part_log = mp.part_log;
     gp.price = t->price;
-    gp.ch = pl.ch;
     gp.n_jobs = n_jobs;
     gp.k = k;
     gp.slots = pl.slots;
+    gp.slots_a = pl.pc.pa * MATCH_WARPS;
     gp.out_idx = d_idx;
     gp.out_cnt = d_cnt;
     gp.out_max = d_max;
@@ -339,7 +352,7 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->tabs, &ctx->part_cnt, &ctx->part_last, &ctx->part_idx, &ctx->d_jobs,
+  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->part_last, &ctx->part_log, &ctx->d_jobs,
                     &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);
@@ -573,10 +586,10 @@ int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* lay
   Plan pl;
   int rc = make_plan(ctx, t, layout, n_jobs, pl);
   if (rc) return rc;
-  out[0] = pl.ch.grid;
-  out[1] = (uint32_t)(pl.ch.total > 0xFFFFFFFFull ? 0xFFFFFFFFu : pl.ch.total);
-  out[2] = pl.n_blocks;
-  out[3] = pl.split_block;
+  out[0] = pl.grid;
+  out[1] = pl.pc.count();
+  out[2] = pl.pc.pa;
+  out[3] = pl.pc.pb;
   out[4] = pl.slots;
   out[5] = pl.smem;
   out[6] = pl.lay.n_entries;

@@ -1,17 +1,17 @@
 // kernels.cuh -- device code of libdsmatch (sm_100a).  Included by dsmatch.cu only.
 //
 //   k_build_tables  job records -> bit-sliced acceptance tables (one u32 per 32 jobs per entry)
-//   k_match         rows x job groups -> per-slot partial results (count, first-k, last match)
+//   k_match         rows x job groups -> per-slot partial results (count, first-k log, last match)
 //   k_merge         per-job ordered merge of the partials
 //   k_merge_shards  per-job merge of all-gathered per-GPU results
 //
-// Work decomposition of k_match.  The work is the flattened space (job group, 32-row block),
-// group-major, of size T = groups * blocks.  CTA c owns the contiguous chunk
-// [T*c/G, T*(c+1)/G) -- every CTA gets the same amount of work to within one block.  A chunk
-// lies in one group or straddles a few; per group it is further cut at the segment boundary
-// (available | not available) and each piece is split evenly over the 8 warps.  A piece's
-// results go to slot ((c - first CTA of the group) * 2 + segment) * 8 + warp, so slots of a
-// job are in row order and k_merge can take "the first k matches" by walking them.
+// Work decomposition of k_match.  The rows of the table are cut into P pieces per job group
+// (pa pieces in the "available" segment, pb in the rest; a piece never straddles the segment
+// boundary).  The unit of work is (piece position, job group); CTAs draw units from an atomic
+// counter in position-major order, so every CTA sees cheap and expensive rows and dense and
+// sparse job groups alike and the SMs finish together.  Inside a unit the piece is split evenly
+// over the 8 warps; warp w's results go to slot position*8 + w of each of the group's 128 jobs,
+// so a job's slots are in row order and k_merge takes "the first k matches" by walking them.
 
 #pragma once
 
@@ -27,7 +27,6 @@
 #ifndef MATCH_CTAS_PER_SM
 #define MATCH_CTAS_PER_SM 3
 #endif
-#define SLOTS_PER_CTA (2 * MATCH_WARPS)
 
 // ------------------------------------------------------------------------------------------
 // small device helpers
@@ -82,9 +81,10 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   return r;
 }
 
-// 32x32 bit-matrix transpose across a warp: on return lane j holds, in bit l, bit j of the
-// value lane l passed in.  Five butterfly steps: exchange with lane^s, rotate the partner's
-// word by s (left for lanes with bit s clear, right otherwise) and keep own bits under `keep`.
+// 32x32 bit-matrix transpose across a warp (used interleaved, four at a time, in k_match): five
+// butterfly steps; at step i a lane exchanges its word with lane^s (s = 16 >> i), rotates the
+// partner's word left by s (lanes with bit s clear) or right by s (the others) and keeps its
+// own bits under `keep`.  Afterwards lane j holds in bit l what lane l held in bit j.
 struct XposeCtl {
   uint32_t rot[5];
   uint32_t keep[5];
@@ -98,15 +98,6 @@ __device__ __forceinline__ void transpose_setup(XposeCtl& c, uint32_t lane) {
     c.rot[i] = upper ? 32u - s : s;
     c.keep[i] = upper ? ~lowmask[i] : lowmask[i];
   }
-}
-__device__ __forceinline__ uint32_t transpose32(uint32_t x, const XposeCtl& c) {
-#pragma unroll
-  for (int i = 0; i < 5; ++i) {
-    const uint32_t y = __shfl_xor_sync(0xFFFFFFFFu, x, 16u >> i);
-    const uint32_t moved = __funnelshift_l(y, y, c.rot[i]);
-    x = (x & c.keep[i]) | (moved & ~c.keep[i]);
-  }
-  return x;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -131,20 +122,28 @@ struct BuildParams {
   uint32_t n_jobs;
   const uint32_t* gpu_entries;
   const uint32_t* bk_entries;
-  uint4* tabs;  // [groups][n_entries] x 4 words
+  uint4* tabs;             // [groups][n_entries] x 4 words
+  uint32_t* work_counter;  // reset here for the k_match that follows in the stream
 };
 
-// Chunking of the flattened (group, block) space shared by k_match and k_merge.
-struct Chunking {
-  unsigned long long total;  // groups * blocks
-  uint32_t grid;             // CTAs
-  uint32_t n_blocks;         // 32-row blocks per group
-  __host__ __device__ unsigned long long begin(uint32_t c) const { return total * c / grid; }
-  __host__ __device__ uint32_t cta_of(unsigned long long pos) const {
-    uint32_t c = (uint32_t)(pos * grid / total);
-    while (c + 1 < grid && begin(c + 1) <= pos) ++c;
-    while (c > 0 && begin(c) > pos) --c;
-    return c;
+// Pieces of the row axis (see the header comment); shared by k_match and k_merge.
+struct Pieces {
+  uint32_t n_groups;
+  uint32_t n_blocks;     // 32-row blocks of the table
+  uint32_t split_block;  // first block of the second segment
+  uint32_t pa, pb;       // pieces in the first / second segment
+  __host__ __device__ uint32_t per_group() const { return pa + pb; }
+  __host__ __device__ uint32_t count() const { return n_groups * (pa + pb); }
+  __host__ __device__ void blocks_of(uint32_t pos, uint32_t& lo, uint32_t& hi) const {
+    if (pos < pa) {
+      lo = (uint32_t)((unsigned long long)split_block * pos / pa);
+      hi = (uint32_t)((unsigned long long)split_block * (pos + 1) / pa);
+    } else {
+      const unsigned long long nb = n_blocks - split_block;
+      const uint32_t i = pos - pa;
+      lo = split_block + (uint32_t)(nb * i / pb);
+      hi = split_block + (uint32_t)(nb * (i + 1) / pb);
+    }
   }
 };
 
@@ -154,27 +153,26 @@ struct MatchParams {
   const uint32_t* recs;
   const uint16_t* lut[DSM_MAX_COLS];
   uint32_t base[DSM_MAX_COLS];
-  Chunking ch;
+  Pieces pc;
   uint32_t rec_words;
   uint32_t n_entries;
   uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0..3)
   uint32_t n_jobs;
-  uint32_t split_block;  // first block of the second segment
   uint32_t k;
-  uint32_t slots;        // slots per job (allocation stride)
+  uint32_t slots;        // slots per job = pieces per group * 8
+  uint32_t* work_counter;
   uint32_t* part_cnt;    // [jobs_pad][slots]
   uint32_t* part_last;   // [jobs_pad][slots]
-  uint32_t* part_idx;    // [jobs_pad][slots][k] x (block, match word)
+  uint2* part_log;       // [jobs_pad][slots][k] x (block, match word)
   uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
 };
 
 struct MergeParams {
   const uint32_t* part_cnt;
   const uint32_t* part_last;
-  const uint32_t* part_idx;
+  const uint2* part_log;
   const double* price;
-  Chunking ch;
-  uint32_t n_jobs, k, slots;
+  uint32_t n_jobs, k, slots, slots_a;  // slots below slots_a belong to the first segment
   uint32_t* out_idx;
   uint32_t* out_cnt;
   uint32_t* out_max;
@@ -190,6 +188,7 @@ __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
   const uint32_t col = blockIdx.y;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warp = threadIdx.x >> 5;
+  if (tile == 0 && col == 0 && threadIdx.x == 0) *p.work_counter = 0u;
   const uint32_t job = tile * 32u + lane;
   const bool live = job < p.n_jobs;
   const uint32_t* rec = p.recs + (size_t)(live ? job : 0) * p.lay.rec_words + p.lay.rec_off[col];
@@ -292,6 +291,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   uint4* s_tab = rep_shift ? s_stage + p.n_entries : s_stage;
   uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + ((size_t)p.n_entries << rep_shift));  // [2][128]
   __shared__ __align__(8) uint64_t s_bar;
+  __shared__ uint32_t s_unit;
 
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31u;
@@ -309,179 +309,182 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     mbar_init(&s_bar, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  __syncthreads();
 
-  const uint32_t n_blocks = p.ch.n_blocks;
+  const Pieces pc = p.pc;
+  const uint32_t n_units = pc.count();
+  const uint32_t n_blocks = pc.n_blocks;
   const uint32_t kk = p.k;
   const uint4* rows_lane = p.rows + (ROW32 ? 2u * lane : lane);  // this lane's row inside a block
-  unsigned long long pos = p.ch.begin(blockIdx.x);
-  const unsigned long long end = p.ch.begin(blockIdx.x + 1);
   uint32_t parity = 0;
+  uint32_t cur_group = 0xFFFFFFFFu;
 #ifdef DSM_CTA_TIMING
   unsigned long long dbg_t0 = 0;
   if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
 #endif
 
-  while (pos < end) {
-    const uint32_t group = (uint32_t)(pos / n_blocks);
-    const uint32_t blk_lo = (uint32_t)(pos - (unsigned long long)group * n_blocks);
-    const unsigned long long room = end - pos;
-    const uint32_t blk_hi = room < (n_blocks - blk_lo) ? blk_lo + (uint32_t)room : n_blocks;
-    pos += blk_hi - blk_lo;
-
-    // ---- stage this group's acceptance table (TMA bulk copy) and cut-off rows
-    __syncthreads();  // everyone is done reading the previous table
-    if (tid == 0) {
-      const uint32_t bytes = p.n_entries * 16u;
-      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      mbar_expect_tx(&s_bar, bytes);
-      bulk_g2s(s_stage, p.tabs + (size_t)group * p.n_entries, bytes, &s_bar);
-    }
-    if (tid < JPG) {
-      const uint32_t job = group * JPG + tid;
-      uint32_t ca = 0, cb = 0;  // padding jobs accept nothing
-      if (job < p.n_jobs) {
-        ca = p.recs[(size_t)job * p.rec_words + 0];
-        cb = p.recs[(size_t)job * p.rec_words + 1];
-      }
-      s_cut[tid] = ca;
-      s_cut[JPG + tid] = cb;
-    }
-    mbar_wait(&s_bar, parity);
-    parity ^= 1u;
-    if (rep_shift) {  // fan the staged table out into its R interleaved copies
-      const uint32_t n_copy = p.n_entries << rep_shift;
-      for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = s_stage[i >> rep_shift];
-    }
+  for (;;) {
+    __syncthreads();  // the previous unit is finished: table and s_unit may be overwritten
+    if (tid == 0) s_unit = atomicAdd(p.work_counter, 1u);
     __syncthreads();
+    const uint32_t unit = s_unit;
+    if (unit >= n_units) break;
+    const uint32_t pos = unit / pc.n_groups;  // position-major: all groups' piece 0 first
+    const uint32_t group = unit - pos * pc.n_groups;
 
-    const uint32_t c_rel = blockIdx.x - p.ch.cta_of((unsigned long long)group * n_blocks);
-
-#pragma unroll 1
-    for (uint32_t seg = 0; seg < 2; ++seg) {
-      // the piece of [blk_lo, blk_hi) inside this segment, split evenly over the warps
-      const uint32_t lo = seg == 0 ? blk_lo : max(blk_lo, p.split_block);
-      const uint32_t hi = seg == 0 ? min(blk_hi, p.split_block) : blk_hi;
-      const uint32_t len = hi > lo ? hi - lo : 0u;
-      const uint32_t b0 = lo + (uint32_t)(((unsigned long long)len * warp) / MATCH_WARPS);
-      const uint32_t b1 = lo + (uint32_t)(((unsigned long long)len * (warp + 1)) / MATCH_WARPS);
-      const uint32_t* cut = s_cut + seg * JPG;
-      const uint32_t slot = (c_rel * 2u + seg) * MATCH_WARPS + warp;
-
-      // rows below a job's cut-off pass the price/availability test.  full: all rows of this
-      // warp's range pass; part: the cut-off lies inside the range; neither: none pass.
-      uint32_t full[TPG], part[TPG];
-#pragma unroll
-      for (int t = 0; t < TPG; ++t) {
-        const uint32_t c = cut[t * 32 + lane];
-        full[t] = __ballot_sync(0xFFFFFFFFu, c >= b1 * 32u);
-        part[t] = __ballot_sync(0xFFFFFFFFu, c > b0 * 32u && c < b1 * 32u);
+    if (group != cur_group) {
+      // ---- stage this group's acceptance table (TMA bulk copy) and cut-off rows
+      if (tid == 0) {
+        const uint32_t bytes = p.n_entries * 16u;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(&s_bar, bytes);
+        bulk_g2s(s_stage, p.tabs + (size_t)group * p.n_entries, bytes, &s_bar);
       }
+      if (tid < JPG) {
+        const uint32_t job = group * JPG + tid;
+        uint32_t ca = 0, cb = 0;  // padding jobs accept nothing
+        if (job < p.n_jobs) {
+          ca = p.recs[(size_t)job * p.rec_words + 0];
+          cb = p.recs[(size_t)job * p.rec_words + 1];
+        }
+        s_cut[tid] = ca;
+        s_cut[JPG + tid] = cb;
+      }
+      mbar_wait(&s_bar, parity);
+      parity ^= 1u;
+      if (rep_shift) {  // fan the staged table out into its R interleaved copies
+        const uint32_t n_copy = p.n_entries << rep_shift;
+        for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = s_stage[i >> rep_shift];
+      }
+      __syncthreads();
+      cur_group = group;
+    }
 
-      uint32_t cnt[TPG], ent[TPG], last_word[TPG], last_blk[TPG];
+    // ---- this warp's rows of the piece
+    uint32_t lo, hi;
+    pc.blocks_of(pos, lo, hi);
+    const uint32_t len = hi - lo;
+    const uint32_t b0 = lo + (uint32_t)(((unsigned long long)len * warp) / MATCH_WARPS);
+    const uint32_t b1 = lo + (uint32_t)(((unsigned long long)len * (warp + 1)) / MATCH_WARPS);
+    const uint32_t slot = pos * MATCH_WARPS + warp;
+
+    // Rows below a job's cut-off pass its price / availability test.  full[t] holds the jobs
+    // of tile t that pass on every row of the current block; it only changes at an "event"
+    // block, the block a cut-off falls into, where the per-row comparison is done.
+    uint32_t cutv[TPG];  // lane j: cut-off row of job 32t+j in this segment
 #pragma unroll
-      for (int t = 0; t < TPG; ++t) { cnt[t] = 0; ent[t] = 0; last_word[t] = 0; last_blk[t] = 0; }
-      // first-k log of (job = 32t + lane, this slot): [jobs_pad][slots][k] entries of 8 bytes
-      uint2* log_lane = reinterpret_cast<uint2*>(p.part_idx) +
-                        ((size_t)(group * JPG + lane) * p.slots + slot) * kk;
-      const size_t log_tile_stride = (size_t)32 * p.slots * kk;
+    for (int t = 0; t < TPG; ++t) cutv[t] = s_cut[(pos >= pc.pa ? JPG : 0u) + t * 32 + lane];
+    uint32_t full[TPG];
+    uint32_t next_evt = b0;  // forces the classification on the first block
 
-      // rows are prefetched two blocks ahead (L2 latency is longer than one block of work)
-      RowCodes<NC> rc0, rc1;
-      if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, rc0);
-      if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rc1);
+    uint32_t cnt[TPG], ent[TPG], last_word[TPG], last_blk[TPG];
+#pragma unroll
+    for (int t = 0; t < TPG; ++t) { cnt[t] = 0; ent[t] = 0; last_word[t] = 0; last_blk[t] = 0; full[t] = 0; }
+    // first-k log of (job = 32t + lane, this slot): [jobs_pad][slots][k] entries of 8 bytes
+    uint2* log_lane = p.part_log + ((size_t)(group * JPG + lane) * p.slots + slot) * kk;
+    const size_t log_tile_stride = (size_t)32 * p.slots * kk;
+
+    // rows are prefetched two blocks ahead (L2 latency is longer than one block of work)
+    RowCodes<NC> rc0, rc1;
+    if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, rc0);
+    if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rc1);
 
 #pragma unroll 1
-      for (uint32_t blk = b0; blk < b1; ++blk) {
-        const RowCodes<NC> cur = rc0;
-        rc0 = rc1;
-        if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, rc1);
+    for (uint32_t blk = b0; blk < b1; ++blk) {
+      const RowCodes<NC> cur = rc0;
+      rc0 = rc1;
+      if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, rc1);
+
+      uint4 m;
+      if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
         const uint32_t row = blk * 32u + lane;
-
-        // gather one 128-bit word group per column and AND them
-        uint4 m = make_uint4(full[0], full[1], full[2], full[3]);
-        if (part[0] | part[1] | part[2] | part[3]) {  // warp-uniform, rare
-          uint32_t pw[TPG] = {0, 0, 0, 0};
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) {
-            uint32_t rest = part[t];
-            while (rest) {
-              const uint32_t j = __ffs(rest) - 1;
-              rest &= rest - 1;
-              pw[t] |= (row < cut[t * 32 + j]) ? (1u << j) : 0u;
-            }
-          }
-          m.x |= pw[0]; m.y |= pw[1]; m.z |= pw[2]; m.w |= pw[3];
-        }
-#pragma unroll
-        for (int c = 0; c < NC; ++c) {
-          uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
-          if constexpr (HAS_LUT) {
-            if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-          }
-          const uint4 a = lds128(taddr[c] + (code << code_shift));
-          m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
-        }
-
-        // four independent 32x32 transposes, interleaved step by step so the shuffles overlap:
-        // afterwards lane j holds in T[t] the rows of this block that match job 32t+j
-        uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-        for (int i = 0; i < 5; ++i) {
-          uint32_t y[TPG];
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(0xFFFFFFFFu, T[t], 16u >> i);
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) {
-            const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
-            T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
-          }
-        }
-
-        if constexpr (BITMAP) {
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) {
-            const uint32_t job = group * JPG + t * 32 + lane;
-            if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T[t];
-          }
-        } else {
-          // branch-free bookkeeping; the (rare) first-k append is behind one warp-uniform vote
-          bool want = false;
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) {
-            const bool hit = T[t] != 0u;
-            want = want || (hit && cnt[t] < kk);
-            last_word[t] = hit ? T[t] : last_word[t];
-            last_blk[t] = hit ? blk : last_blk[t];
-          }
-          if (__any_sync(0xFFFFFFFFu, want)) {
-            // a job that still lacks k matches logs (block, match word); k_merge expands the
-            // words to rows.  At most k entries per (job, slot): every entry has >= 1 match.
-#pragma unroll
-            for (int t = 0; t < TPG; ++t) {
-              if (T[t] != 0u && cnt[t] < kk) {
-                log_lane[(size_t)t * log_tile_stride + ent[t]] = make_uint2(blk, T[t]);
-                ent[t] += 1;
-              }
-            }
-          }
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) cnt[t] += __popc(T[t]);
-        }
-      }
-
-      if constexpr (!BITMAP) {
+        const uint32_t row_end = (blk + 1u) * 32u;
+        uint32_t pw[TPG] = {0, 0, 0, 0};
+        uint32_t nxt = 0xFFFFFFFFu;
 #pragma unroll
         for (int t = 0; t < TPG; ++t) {
-          const size_t o = (size_t)(group * JPG + t * 32 + lane) * p.slots + slot;
-          p.part_cnt[o] = cnt[t];
-          p.part_last[o] = last_word[t] ? last_blk[t] * 32u + 31u - __clz(last_word[t]) : DSM_NO_ROW;
+          full[t] = __ballot_sync(0xFFFFFFFFu, cutv[t] >= row_end);
+          uint32_t part = __ballot_sync(0xFFFFFFFFu, cutv[t] > blk * 32u && cutv[t] < row_end);
+          while (part) {
+            const uint32_t j = __ffs(part) - 1;
+            part &= part - 1;
+            pw[t] |= (row < __shfl_sync(0xFFFFFFFFu, cutv[t], j)) ? (1u << j) : 0u;
+          }
+          if (cutv[t] >= row_end) nxt = min(nxt, cutv[t] >> 5);  // block where this job leaves `full`
         }
+        next_evt = __reduce_min_sync(0xFFFFFFFFu, nxt);
+        m = make_uint4(full[0] | pw[0], full[1] | pw[1], full[2] | pw[2], full[3] | pw[3]);
+      } else {
+        m = make_uint4(full[0], full[1], full[2], full[3]);
+      }
+
+      // gather one 128-bit word group per column and AND them
+#pragma unroll
+      for (int c = 0; c < NC; ++c) {
+        uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
+        if constexpr (HAS_LUT) {
+          if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+        }
+        const uint4 a = lds128(taddr[c] + (code << code_shift));
+        m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
+      }
+
+      // four independent 32x32 transposes, interleaved step by step so the shuffles overlap:
+      // afterwards lane j holds in T[t] the rows of this block that match job 32t+j
+      uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        uint32_t y[TPG];
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(0xFFFFFFFFu, T[t], 16u >> i);
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
+          T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
+        }
+      }
+
+      if constexpr (BITMAP) {
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          const uint32_t job = group * JPG + t * 32 + lane;
+          if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T[t];
+        }
+      } else {
+        // branch-free bookkeeping; the first-k log is behind one warp-uniform vote
+        bool want = false;
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          const bool hit = T[t] != 0u;
+          want = want || (hit && cnt[t] < kk);
+          last_word[t] = hit ? T[t] : last_word[t];
+          last_blk[t] = hit ? blk : last_blk[t];
+        }
+        if (__any_sync(0xFFFFFFFFu, want)) {
+          // a job that still lacks k matches logs (block, match word); k_merge expands the
+          // words to rows.  At most k entries per (job, slot): every entry has >= 1 match.
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) {
+            if (T[t] != 0u && cnt[t] < kk) {
+              log_lane[(size_t)t * log_tile_stride + ent[t]] = make_uint2(blk, T[t]);
+              ent[t] += 1;
+            }
+          }
+        }
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) cnt[t] += __popc(T[t]);
+      }
+    }
+
+    if constexpr (!BITMAP) {
+#pragma unroll
+      for (int t = 0; t < TPG; ++t) {
+        const size_t o = (size_t)(group * JPG + t * 32 + lane) * p.slots + slot;
+        p.part_cnt[o] = cnt[t];
+        p.part_last[o] = last_word[t] ? last_blk[t] * 32u + 31u - __clz(last_word[t]) : DSM_NO_ROW;
       }
     }
   }
 #ifdef DSM_CTA_TIMING
-  __syncthreads();
   if (tid == 0 && blockIdx.x < 4096) {
     unsigned long long t1;
     uint32_t smid;
@@ -502,14 +505,10 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t job = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (job >= p.n_jobs) return;
-  const uint32_t group = job / JPG;
-  const unsigned long long g0 = (unsigned long long)group * p.ch.n_blocks;
-  const uint32_t c_first = p.ch.cta_of(g0);
-  const uint32_t c_last = p.ch.cta_of(g0 + p.ch.n_blocks - 1);
-  const uint32_t n_slots = (c_last - c_first + 1) * SLOTS_PER_CTA;
+  const uint32_t n_slots = p.slots;
   const uint32_t* cnt = p.part_cnt + (size_t)job * p.slots;
   const uint32_t* lst = p.part_last + (size_t)job * p.slots;
-  const uint2* log = reinterpret_cast<const uint2*>(p.part_idx) + (size_t)job * p.slots * p.k;
+  const uint2* log = p.part_log + (size_t)job * p.slots * p.k;
   uint32_t* out = p.out_idx + (size_t)job * p.k;
 
   uint32_t total = 0, have = 0;
@@ -539,7 +538,7 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
         }
       }
     }
-    const bool seg_b = (s / MATCH_WARPS) & 1u;
+    const bool seg_b = s >= p.slots_a;
     const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c != 0 && !seg_b);
     const uint32_t hit_b = __ballot_sync(0xFFFFFFFFu, c != 0 && seg_b);
     const uint32_t l = c ? lst[s] : DSM_NO_ROW;

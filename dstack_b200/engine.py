@@ -80,7 +80,7 @@ class Matcher:
         out = (C.c_uint32 * 8)()
         lay = native.make_layout(packed.layout)
         native.check(self._lib.dsm_plan_query(self.handle, dt.handle, C.byref(lay), len(packed.records), C.byref(out)))
-        keys = ["grid", "total_blocks", "blocks", "split_block", "slots", "smem", "entries", "groups"]
+        keys = ["grid", "units", "pieces_a", "pieces_b", "slots", "smem", "entries", "groups"]
         return dict(zip(keys, [int(x) for x in out]))
 
     # -- matching with host buffers (H2D + kernels + D2H inside the call)

@@ -38,8 +38,8 @@ t1 = buf[:, 1].astype(np.int64)
 sm = buf[:, 2].astype(np.int64)
 base = t0.min()
 dur = (t1 - t0) / 1e3
-print(f"kernel span {(t1.max() - base) / 1e3:.1f} us; CTA duration us: min {dur.min():.1f} mean {dur.mean():.1f} max {dur.max():.1f}")
-print("start offsets us: max", (t0.max() - base) / 1e3)
+print(f"kernel span {(t1.max() - base) / 1e3:.1f} us; CTA duration us: min {dur.min():.1f} "
+      f"mean {dur.mean():.1f} max {dur.max():.1f}; start spread {(t0.max() - base) / 1e3:.2f} us")
 per_sm_end = {}
 for s, e in zip(sm, t1):
     per_sm_end[s] = max(per_sm_end.get(s, 0), e)
@@ -47,20 +47,3 @@ ends = np.array(sorted((v - base) / 1e3 for v in per_sm_end.values()))
 print("per-SM finish us: min %.1f median %.1f max %.1f; SMs used %d" % (ends.min(), np.median(ends), ends.max(), len(ends)))
 cnt = np.bincount(sm)
 print("CTAs per SM histogram:", np.bincount(cnt[cnt > 0]))
-order = np.argsort(dur)
-print("fastest CTAs (id, sm, us):", [(int(i), int(sm[i]), round(float(dur[i]), 1)) for i in order[:6]])
-print("slowest CTAs (id, sm, us):", [(int(i), int(sm[i]), round(float(dur[i]), 1)) for i in order[-6:]])
-# duration vs position inside the group (chunk position modulo blocks per group)
-blocks = plan["blocks"]
-total = plan["groups"] * blocks
-begin = (np.arange(n, dtype=np.int64) * total) // n
-posg = (begin % blocks) / blocks
-for lo in np.arange(0, 1, 0.125):
-    sel = (posg >= lo) & (posg < lo + 0.125)
-    if sel.any():
-        print(f"  group position {lo:.3f}-{lo + .125:.3f}: mean CTA us {dur[sel].mean():.1f} (n={int(sel.sum())})")
-grp = begin // blocks
-for g in range(0, plan["groups"], max(1, plan["groups"] // 8)):
-    sel = grp == g
-    if sel.any():
-        print(f"  group {g}: mean CTA us {dur[sel].mean():.1f}")
