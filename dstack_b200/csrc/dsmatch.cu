@@ -141,7 +141,7 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     return fail(DSM_E_DICT_TOO_LARGE, "acceptance tables need more shared memory than one CTA has");
   const char* force_rep = getenv("DSM_REP_SHIFT");  // tuning / tests only
   pl.rep_shift = 0;
-  for (uint32_t rs = 3; rs >= 1; --rs) {
+  for (uint32_t rs = 3; rs >= 3; --rs) {  // 8 copies or none: 2 and 4 copies measured slower than none
     const uint32_t need = base * 16u * ((1u << rs) + 1u) + cuts;
     if (need <= MAX_SMEM_BYTES / MATCH_CTAS_PER_SM) { pl.rep_shift = rs; break; }
   }

@@ -65,14 +65,22 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-// Streaming 128-bit row load (rows are read once per job group; keep them out of L1).
+// 128-bit row load through L1: the line was requested PREFETCH_BLOCKS blocks earlier by
+// prefetch_l1, so this normally hits L1 (each row is used once per unit; L1 is only the
+// landing buffer of the software prefetch).
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 r;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+  asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
                : "l"(p));
   return r;
 }
+__device__ __forceinline__ void prefetch_l1(const void* p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
+#ifndef PREFETCH_BLOCKS
+#define PREFETCH_BLOCKS 6
+#endif
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -387,12 +395,17 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     RowCodes<NC> rc0, rc1;
     if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, rc0);
     if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rc1);
+#pragma unroll
+    for (uint32_t a = 2; a < PREFETCH_BLOCKS; ++a)
+      if (b0 + a < b1) prefetch_l1(rows_lane + (size_t)(b0 + a) * (ROW32 ? 64u : 32u));
 
 #pragma unroll 1
     for (uint32_t blk = b0; blk < b1; ++blk) {
       const RowCodes<NC> cur = rc0;
       rc0 = rc1;
       if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, rc1);
+      if (blk + PREFETCH_BLOCKS < b1)
+        prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
 
       uint4 m;
       if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
