@@ -570,6 +570,107 @@ int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches) {
   return 0;
 }
 
+// ------------------------------------------------------------------------------------------
+// dsm_match_bitmap_static: the bitmap match without any allocation
+// ------------------------------------------------------------------------------------------
+//
+// The other entry points grow their scratch with cudaMalloc on first use.  Some hosts of this
+// library cannot do that at call time: a scheduler thread that shares the GPU with serving or
+// training work must not run into the device-wide synchronisation and driver locks that
+// cudaMalloc / cudaFree can take while other streams are busy, and a process whose device memory
+// is already handed out in full to a pool allocator (a framework's caching allocator, a fixed
+// MIG slice) may simply be refused a new allocation.  For them the scratch of this variant --
+// the acceptance tables k_build_tables writes and k_match reads, and the work counter -- lives
+// in a fixed array in the library's device image.  Every GPU that loads the library carries the
+// array until the process exits; DSM_STATIC_SCRATCH_BYTES is its size and the hard limit.
+//
+// g_static_scratch names the array for DEVICE code.  In host code the same name is only the
+// host-side handle of the symbol, not a device address -- a kernel handed that value would fault
+// or touch unrelated memory -- so the address the kernels get is looked up once per device with
+// cudaGetSymbolAddress while that device is current.
+static __device__ __align__(256) unsigned char g_static_scratch[DSM_STATIC_SCRATCH_BYTES];
+
+#define DSM_STATIC_MAX_DEVICES 64
+static std::mutex g_static_mu;
+static void* g_static_dev_ptr[DSM_STATIC_MAX_DEVICES];  // device address of the array, per GPU
+
+// Caller has made `device` current.
+static int static_scratch_address(int device, unsigned char** out) {
+  if (device < 0 || device >= DSM_STATIC_MAX_DEVICES)
+    return fail(DSM_E_ARG, "device ordinal beyond the static scratch table");
+  std::lock_guard<std::mutex> g(g_static_mu);
+  if (g_static_dev_ptr[device] == nullptr) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_static_scratch));
+    g_static_dev_ptr[device] = p;
+  }
+  *out = static_cast<unsigned char*>(g_static_dev_ptr[device]);
+  return 0;
+}
+
+int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                            const uint32_t* d_jobs, uint32_t n_jobs, uint32_t* d_bits) {
+  if (!ctx || !t || !layout || !d_jobs || !d_bits) return fail(DSM_E_ARG, "NULL argument");
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  Plan pl;
+  int rc = make_plan(ctx, t, layout, n_jobs, pl);  // pure arithmetic, allocates nothing
+  if (rc) return rc;
+  const bool row32 = t->desc.n_cols == 16;
+  if (row32 && layout->n_used < 5) return fail(DSM_E_ARG, "16-column tables need n_used >= 5");
+
+  // layout of the array: [0,256) work counter, then the tables [groups][entries] x 16 bytes
+  const size_t table_bytes = (size_t)pl.n_groups * pl.lay.n_entries * 16;
+  if (256 + table_bytes > DSM_STATIC_SCRATCH_BYTES) {
+    char msg[256];
+    snprintf(msg, sizeof msg,
+             "dsm_match_bitmap_static: %u job groups x %u dictionary entries need %zu bytes of "
+             "scratch, the built-in array holds %u; split the batch or use dsm_match_bitmap_dev",
+             pl.n_groups, pl.lay.n_entries, 256 + table_bytes, (unsigned)DSM_STATIC_SCRATCH_BYTES);
+    return fail(DSM_E_TOO_LARGE, "%s", msg);
+  }
+  CK(cudaSetDevice(ctx->device));
+  unsigned char* scratch = nullptr;
+  if ((rc = static_scratch_address(ctx->device, &scratch))) return rc;
+
+  BuildParams bp;
+  bp.lay = pl.lay;
+  bp.recs = d_jobs;
+  bp.n_jobs = n_jobs;
+  bp.gpu_entries = t->gpu_entries;
+  bp.bk_entries = t->bk_entries;
+  bp.tabs = reinterpret_cast<uint4*>(scratch + 256);
+  bp.work_counter = reinterpret_cast<uint32_t*>(scratch);  // k_build_tables zeroes it
+  k_build_tables<<<dim3(pl.n_groups * TPG, pl.lay.n_used), 256, 0, ctx->stream>>>(bp);
+  CK(cudaGetLastError());
+  ctx->launches++;
+
+  MatchParams mp;
+  memset(&mp, 0, sizeof mp);
+  mp.rows = t->rows;
+  mp.tabs = bp.tabs;
+  mp.recs = d_jobs;
+  bool has_lut = false;
+  for (uint32_t c = 0; c < layout->n_used; ++c) {
+    mp.lut[c] = layout->lut[c];
+    has_lut = has_lut || layout->lut[c] != nullptr;
+    mp.base[c] = pl.lay.base[c];
+  }
+  mp.pc = pl.pc;
+  mp.rec_words = layout->rec_words;
+  mp.n_entries = pl.lay.n_entries;
+  mp.rep_shift = pl.rep_shift;
+  mp.n_jobs = n_jobs;
+  mp.k = 1;
+  mp.slots = pl.slots;
+  mp.work_counter = bp.work_counter;
+  mp.bits = d_bits;
+  cudaError_t e = launch_match<true>(layout->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
+  ctx->launches++;
+  return 0;
+}
+
 #ifdef DSM_CTA_TIMING
 // debug builds only: copy the per-CTA (start ns, end ns, SM id) triples of the last k_match
 int dsm_debug_cta_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_ctas) {

@@ -169,6 +169,33 @@ int dsm_match_topk_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layou
 int dsm_match_bitmap_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
                          const uint32_t* d_jobs, uint32_t n_jobs, uint32_t* d_bits);
 
+/* dsm_match_bitmap_dev for callers that must not allocate.  This entry point has no counterpart
+ * in the reference (which never touches a GPU); it exists for two kinds of host:
+ *   - a scheduler thread sharing the GPU with serving or training streams, which cannot afford
+ *     the device-wide synchronisation and driver locking a cudaMalloc / cudaFree may cause;
+ *   - a process whose device memory is already fully owned by a pool (a framework's caching
+ *     allocator, a fixed MIG slice), where a fresh allocation can be refused.
+ * Same arguments and same result as dsm_match_bitmap_dev: d_jobs (records) and d_bits (output,
+ * n_jobs * n_rows/32 words) are the caller's device buffers.  The scratch the other entry
+ * points allocate -- the acceptance tables and the work counter -- lives in a fixed array of
+ * DSM_STATIC_SCRATCH_BYTES inside the library's device image, so every GPU that loads the
+ * library holds that much until the process exits.  No cudaMalloc, cudaFree or other
+ * allocating call is made.
+ *   Limit: 256 + ceil(n_jobs/128) * (sum of layout.card) * 16 bytes must fit in the array
+ *   (e.g. 465 dictionary entries -> up to ~36,000 jobs per call); larger requests fail with
+ *   DSM_E_TOO_LARGE and a message saying how much was needed.  A layout that uses lut[] needs
+ *   its dsm_lut_upload done beforehand (that call does allocate).
+ *   First call on a GPU: the array's device address is looked up once per device
+ *   (cudaGetSymbolAddress, with that device current); make that first call before starting any
+ *   stream capture.
+ *   Sharing: all calls on a GPU use the one array and it keeps the previous call's contents.
+ *   Everything that has to start from zero (the work counter) is reset by the call itself and
+ *   the tables are rewritten for every job group used, but two calls whose kernels overlap on
+ *   the same GPU -- different contexts, streams or threads -- race on it: serialise them. */
+#define DSM_STATIC_SCRATCH_BYTES (2u << 20)
+int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                            const uint32_t* d_jobs, uint32_t n_jobs, uint32_t* d_bits);
+
 /* Merge per-shard results of a catalog sharded over n_shards GPUs in table order
  * (shard s holds rows that rank before shard s+1).  Inputs are the all-gathered device
  * arrays [n_shards][n_jobs][k], [n_shards][n_jobs], [n_shards][n_jobs] and the per-shard
