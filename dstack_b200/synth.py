@@ -331,9 +331,10 @@ def make_pool(n_instances: int, seed: int = 2, n_fleets: int = 200) -> List[Any]
         elif tb_draw < 0.20:
             total_blocks = int(rng.choice([2, 4, 8]))
         st_draw = rng.random()
+        other = [M.InstanceStatus.PENDING, M.InstanceStatus.PROVISIONING,
+                 M.InstanceStatus.TERMINATING, M.InstanceStatus.TERMINATED]
         status = (M.InstanceStatus.IDLE if st_draw < 0.7 else M.InstanceStatus.BUSY if st_draw < 0.9
-                  else rng.choice([M.InstanceStatus.PENDING, M.InstanceStatus.PROVISIONING,
-                                   M.InstanceStatus.TERMINATING, M.InstanceStatus.TERMINATED]))
+                  else other[int(rng.integers(0, len(other)))])
         backend = M.BackendType(provs[int(rng.integers(0, len(provs)))])
         region = f"{backend.value}-region-{int(rng.integers(0, 6))}"
         gpus = []
