@@ -56,48 +56,48 @@ def workload(n_gpus: int, override: str = ""):
 
 
 class ClockSampler:
-    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-              "clocks_event_reasons.sw_power_cap")
+    """Polls SM clock and throttle reasons through NVML from a thread while the timed regions
+    run (the regions last milliseconds, so `nvidia-smi -lms` is too coarse)."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, index: int):
-        self.samples = []
-        self.proc = None
+        self.sm, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self.thread = None
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
-                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except Exception:
-            self.proc = None
+            import pynvml
 
-    def _read(self):
-        for line in self.proc.stdout:
-            parts = [p.strip() for p in line.split(",")]
-            if len(parts) >= 7:
-                self.samples.append(parts)
+            pynvml.nvmlInit()
+            visible = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(visible.split(",")[index]) if visible and visible.split(",")[index].isdigit() else index
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+        except Exception as e:  # no NVML: report that instead of a number
+            self.error = repr(e)
+
+    def _poll(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+                mask = int(nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.0005)
 
     def stop(self):
-        if self.proc is None:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
-        sm, mx, reasons = [], [], set()
-        for p in self.samples:
-            try:
-                sm.append(float(p[0]))
-                mx.append(float(p[1]))
-            except ValueError:
-                continue
-            for name, val in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        if self.thread is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable: " + getattr(self, "error", "?")]}
+        self._stop.set()
+        self.thread.join(timeout=2)
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.sm)}
 
 
 # ------------------------------------------------------------------------------------------ CPU baseline
@@ -196,16 +196,6 @@ def run_reference(args, wl, rank: int):
 # ------------------------------------------------------------------------------------------ ours
 
 
-def subset_columns(oc, idx):
-    """Rows `idx` (ascending source positions) of an OfferColumns, dictionaries shared."""
-    import dataclasses
-
-    return dataclasses.replace(
-        oc, shape_id=oc.shape_id[idx], price=oc.price[idx], spot=oc.spot[idx], available=oc.available[idx],
-        backend=oc.backend[idx], src_backend=oc.src_backend[idx], region_id=oc.region_id[idx],
-        itype_id=oc.itype_id[idx])
-
-
 def verify(cat_cols, sj, k, index, count, max_price, rng, n_sample=24, order=None):
     """Full-size parity: sampled jobs against the numpy oracle on the whole catalog, plus
     size-independent properties for every job."""
@@ -255,9 +245,7 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
     import torch
 
     from dstack_b200 import native, synth
-    from dstack_b200.encode import NO_ROW, encode_table, pack_jobs
-    from dstack_b200.engine import Matcher
-    from oracle import columnar
+    from dstack_b200.sharded import ShardedMatcher, rank_order
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback for the product path")
@@ -274,70 +262,26 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
     t_setup = time.perf_counter()
     cat = synth.make_catalog(N, seed=wl["seed"], n_shapes=wl["shapes"])
     full = cat.columns
-    order = columnar.rank_order(full)
-    if world > 1:
-        lo, hi = rank * N // world, (rank + 1) * N // world
-        mine = np.sort(order[lo:hi])
-        cols = subset_columns(full, mine)
-    else:
-        mine = None
-        cols = full
-    table = encode_table(cols)
-    full_table_for_ids = table  # dictionaries the job ids refer to are shared by every shard
-    sj = synth.make_jobs(cat, full_table_for_ids, J, seed=wl["seed"])
-    packed = pack_jobs(table, sj.columns)
+    order = rank_order(full)
+    sm = ShardedMatcher(full, rank=rank, world=world, device=local_rank, order=order)
+    table = sm.table
+    sj = synth.make_jobs(cat, table, J, seed=wl["seed"])  # dictionaries are shared by every shard
+    packed = sm.pack(sj.columns)
     rec_words = packed.layout["rec_words"]
     setup_s = time.perf_counter() - t_setup
 
-    stream = torch.cuda.Stream(device=dev)
+    stream = sm.stream
+    m = sm.matcher
+    h = m.handle
     with torch.cuda.stream(stream):
-        m = Matcher(local_rank, stream=stream.cuda_stream)
-        dt = m.upload(table)
-        lay = m._layout(packed)
-        h = m.handle
+        b = sm.prepare(packed, k)
         pin_rec = native.PinnedArray((J, rec_words), np.uint32)
         pin_rec.array[:] = packed.records
         pin_idx = native.PinnedArray((J, k), np.uint32)
         pin_cnt = native.PinnedArray((J,), np.uint32)
         pin_max = native.PinnedArray((J,), np.uint32)
-        d_rec = torch.from_numpy(packed.records.view(np.int32)).to(dev)
-        d_idx = torch.empty((J, k), dtype=torch.int32, device=dev)
-        d_cnt = torch.empty((J,), dtype=torch.int32, device=dev)
-        d_max = torch.empty((J,), dtype=torch.int32, device=dev)
-        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
-        if world > 1:
-            d_mp = torch.empty((J,), dtype=torch.float64, device=dev)
-            g_idx = torch.empty((world, J, k), dtype=torch.int32, device=dev)
-            g_cnt = torch.empty((world, J), dtype=torch.int32, device=dev)
-            g_max = torch.empty((world, J), dtype=torch.int32, device=dev)
-            g_mp = torch.empty((world, J), dtype=torch.float64, device=dev)
-            sizes = torch.tensor([table.n_rows], dtype=torch.int64, device=dev)
-            all_sizes = torch.empty((world,), dtype=torch.int64, device=dev)
-            dist.all_gather_into_tensor(all_sizes, sizes)
-            base = torch.cumsum(all_sizes, 0) - all_sizes
-            o_idx = torch.empty((J, k), dtype=torch.int64, device=dev)
-            o_cnt = torch.empty((J,), dtype=torch.int64, device=dev)
-            o_max = torch.empty((J,), dtype=torch.int64, device=dev)
-            o_mp = torch.empty((J,), dtype=torch.float64, device=dev)
-
-        def step_resident():
-            native.check(lib.dsm_match_topk_dev(h, dt.handle, C.byref(lay), d_rec.data_ptr(), J, k,
-                                                d_idx.data_ptr(), d_cnt.data_ptr(), d_max.data_ptr()))
-            if world > 1:
-                native.check(lib.dsm_gather_price_dev(h, dt.handle, d_max.data_ptr(), J, d_mp.data_ptr()))
-                dist.all_gather_into_tensor(g_idx, d_idx)
-                dist.all_gather_into_tensor(g_cnt, d_cnt)
-                dist.all_gather_into_tensor(g_max, d_max)
-                dist.all_gather_into_tensor(g_mp, d_mp)
-                native.check(lib.dsm_merge_shards_dev(h, world, J, k, g_idx.data_ptr(), g_cnt.data_ptr(),
-                                                      g_max.data_ptr(), g_mp.data_ptr(), base.data_ptr(),
-                                                      o_idx.data_ptr(), o_cnt.data_ptr(), o_max.data_ptr(),
-                                                      o_mp.data_ptr()))
-
         t_pin = torch.from_numpy(pin_rec.array.view(np.int32))
-        t_pidx = torch.from_numpy(pin_idx.array.view(np.int32))
-        t_pcnt = torch.from_numpy(pin_cnt.array.view(np.int32))
-        t_pmax = torch.from_numpy(pin_max.array.view(np.int32))
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
         if world > 1:
             pin_oidx = torch.empty((J, k), dtype=torch.int64).pin_memory()
             pin_ocnt = torch.empty((J,), dtype=torch.int64).pin_memory()
@@ -346,15 +290,15 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         def step_e2e():
             """Host buffers in, host buffers out."""
             if world == 1:
-                native.check(lib.dsm_match_topk(h, dt.handle, C.byref(lay), pin_rec.array.ctypes.data, J, k,
-                                                pin_idx.array.ctypes.data, pin_cnt.array.ctypes.data,
+                native.check(lib.dsm_match_topk(h, sm.device_table.handle, C.byref(b["lay"]), pin_rec.array.ctypes.data,
+                                                J, k, pin_idx.array.ctypes.data, pin_cnt.array.ctypes.data,
                                                 pin_max.array.ctypes.data))
             else:
-                d_rec.copy_(t_pin, non_blocking=True)
-                step_resident()
-                pin_oidx.copy_(o_idx, non_blocking=True)
-                pin_ocnt.copy_(o_cnt, non_blocking=True)
-                pin_omp.copy_(o_mp, non_blocking=True)
+                b["rec"].copy_(t_pin, non_blocking=True)
+                sm.step()
+                pin_oidx.copy_(b["o_idx"], non_blocking=True)
+                pin_ocnt.copy_(b["o_cnt"], non_blocking=True)
+                pin_omp.copy_(b["o_mp"], non_blocking=True)
                 stream.synchronize()
 
         def barrier():
@@ -362,8 +306,9 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
                 dist.barrier()
             torch.cuda.synchronize(dev)
 
-        for _ in range(max(3, args.warmup)):
-            step_resident()
+        warm = max(3, args.warmup)
+        for _ in range(warm):
+            sm.step()
             flush.zero_()
         barrier()
 
@@ -373,14 +318,14 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         launches0 = m.launch_count()
         evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
         barrier()
-        for a, b in evs:
-            a.record(stream)
-            step_resident()
-            b.record(stream)
+        for e0, e1 in evs:
+            e0.record(stream)
+            sm.step()
+            e1.record(stream)
             flush.zero_()  # evict the table from L2; outside the event pair
         barrier()
         launches = m.launch_count() - launches0
-        step_ms = [a.elapsed_time(b) for a, b in evs]
+        step_ms = [e0.elapsed_time(e1) for e0, e1 in evs]
         km = C.c_double()
         kn = C.c_uint32()
         native.check(lib.dsm_timing_read(h, C.byref(km), C.byref(kn)))
@@ -404,35 +349,18 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
 
         mean_ms = statistics.mean(step_ms)
         e2e_mean = statistics.mean(e2e_s)
+        e2e_p50 = statistics.median(e2e_s)
         if world > 1:
-            t = torch.tensor([mean_ms, e2e_mean, statistics.median(e2e_s)], dtype=torch.float64, device=dev)
+            t = torch.tensor([mean_ms, e2e_mean, e2e_p50], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             mean_ms, e2e_mean, e2e_p50 = (float(x) for x in t.cpu())
-        else:
-            e2e_p50 = statistics.median(e2e_s)
 
         # ---- parity at full size (outside the timed regions)
+        sm.step()
+        src, cnt, mp_ = sm.result_in_source_space()
         if world == 1:
-            idx = d_idx.cpu().numpy().view(np.uint32)
-            src = np.where(idx == NO_ROW, -1, table.perm[np.minimum(idx, table.n_rows - 1)])
-            cnt = d_cnt.cpu().numpy().view(np.uint32).astype(np.int64)
-            mx = d_max.cpu().numpy().view(np.uint32)
-            mp_ = np.where(mx == NO_ROW, np.nan, table.price[np.minimum(mx, table.n_rows - 1)])
-            assert np.array_equal(idx, pin_idx.array) and np.array_equal(cnt, pin_cnt.array.astype(np.int64)), \
-                "host-buffer path and resident path disagree"
-        else:
-            # global physical row -> source position through the owning shard's perm
-            perms = [None] * world
-            dist.all_gather_object(perms, (mine, table.perm))
-            bases = base.cpu().numpy()
-            gi = o_idx.cpu().numpy()
-            src = np.full(gi.shape, -1, np.int64)
-            for s, (mine_s, perm_s) in enumerate(perms):
-                sel = (gi >= bases[s]) & (gi < bases[s] + len(perm_s)) & (gi >= 0)
-                local = perm_s[(gi[sel] - bases[s]).astype(np.int64)]
-                src[sel] = mine_s[local]
-            cnt = o_cnt.cpu().numpy()
-            mp_ = o_mp.cpu().numpy()
+            assert np.array_equal(b["idx"].cpu().numpy().view(np.uint32), pin_idx.array) and \
+                np.array_equal(cnt, pin_cnt.array.astype(np.int64)), "host-buffer path and resident path disagree"
         verified = 0
         if rank == 0:
             verified = verify(full, sj, k, src, cnt, mp_, np.random.default_rng(0),
@@ -446,12 +374,10 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
 
     evals = float(J) * float(N)
     value = evals / (mean_ms * 1e-3)
-    peaks = {}
     peaks_src = "fallback 6650 GB/s (B200_PROFILING.md)"
     hbm_peak = 6650.0
     try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        hbm_peak = float(peaks["hbm_gbs"])
+        hbm_peak = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"])
         peaks_src = "MEASURED_PEAKS.json hbm_gbs"
     except Exception:
         pass
@@ -460,13 +386,14 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
     alg_bytes = groups * table.n_rows * row_bytes + J * rec_words * 4 + J * (k + 2) * 4
     achieved = alg_bytes / (match_ms * 1e-3) / 1e9
     out = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
         "ms_per_step": mean_ms, "higher_is_better": True, "scaling": "strong" if world > 1 else "weak",
         "vs_baseline": None, "dtype": "u16 codes / u32 bit-sliced words", "data": "synthetic",
         "config": {"workload": wl["workload"], "jobs": J, "offers": N, "k": k, "jobs_per_pass": 128,
                    "row_bytes": row_bytes, "rows_per_gpu": int(table.n_rows),
                    "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
-                   "parallelism": f"catalog sharded x{world} in rank order" if world > 1 else "1 GPU"},
+                   "parallelism": f"catalog sharded x{world} in result order, NCCL all_gather of per-shard top-k"
+                   if world > 1 else "1 GPU"},
         "e2e": {"value": evals / e2e_mean, "unit": UNIT, "h2d_bytes_per_step": int(J * rec_words * 4),
                 "d2h_bytes_per_step": int(J * (k + 2) * 4 if world == 1 else J * (k * 8 + 16)),
                 "p50_batch_latency_ms": 1e3 * e2e_p50,
@@ -476,16 +403,15 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         "clocks": clock_info,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": None, "kernel": "k_match",
-                     "kernel_ms": match_ms, "kernel_share_of_step": match_ms / (statistics.mean(step_ms)),
+                     "kernel_ms": match_ms, "kernel_share_of_step": match_ms / statistics.mean(step_ms),
                      "algorithmic_bytes_per_launch": int(alg_bytes), "peak_source": peaks_src,
-                     "note": "k_match is bound by shared-memory gathers and instruction issue, not HBM "
-                             "(128 jobs share every 16-byte row read); see DESIGN.md"},
+                     "note": "k_match is bound by instruction issue and the LSU/shared-memory pipe, not HBM: "
+                             "128 jobs share every 16-byte row read (DESIGN.md section 3)"},
         "parity": {"verified_jobs_vs_oracle": int(verified), "properties_all_jobs": True},
         "setup_seconds": setup_s,
     }
     if world == 1 and not args.no_cpu_baseline:
-        cb = cpu_baseline(wl, os.cpu_count() or 1)
-        out["cpu_baseline"] = {k_: cb[k_] for k_ in ("value", "unit", "cores", "kind", "sample")}
+        out["cpu_baseline"] = cpu_baseline(wl, os.cpu_count() or 1)
     print(json.dumps(out))
     if dist is not None:
         dist.barrier()

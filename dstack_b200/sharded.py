@@ -1,0 +1,158 @@
+"""Catalog sharded over the GPUs of one node: one process per GPU, NCCL for the one exchange.
+
+Rank r holds a contiguous range of the global result order (stable sort of the source list by
+``(not available, price)``, the order ``server/services/backends/__init__.py:449-451``
+produces) as its own device table with its own dictionaries; job records are replicated.  A
+step is: local ``dsm_match_topk_dev`` -> ``dsm_gather_price_dev`` -> ``all_gather`` of the
+per-shard first-k rows, counts, max rows and their prices -> ``dsm_merge_shards_dev``.  Because
+shards are in result order the merge is a concatenation and the total order is the *global
+physical row* ``shard_base[s] + local row``.
+
+The helpers at the top are pure numpy (used by the CPU ``gloo`` tests as well); the device path
+is :class:`ShardedMatcher`.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+import dataclasses
+from typing import Any, List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from .encode import NO_ROW, EncodedTable, JobColumns, OfferColumns, PackedJobs, encode_table, pack_jobs
+
+
+def rank_order(oc: OfferColumns) -> np.ndarray:
+    """Source positions in result order."""
+    return np.lexsort((np.asarray(oc.price, dtype=np.float64), ~np.asarray(oc.available, dtype=bool)))
+
+
+def shard_positions(order: np.ndarray, rank: int, world: int) -> np.ndarray:
+    """Source positions (ascending) of the offers rank ``rank`` owns: the ``rank``-th of ``world``
+    equal contiguous ranges of the result order."""
+    n = len(order)
+    lo, hi = rank * n // world, (rank + 1) * n // world
+    return np.sort(order[lo:hi])
+
+
+def subset_columns(oc: OfferColumns, idx: np.ndarray) -> OfferColumns:
+    """Rows ``idx`` of ``oc``; dictionaries (shapes, regions, instance types) stay shared, so job
+    filters packed against one shard's id space are valid for every shard."""
+    return dataclasses.replace(
+        oc, shape_id=oc.shape_id[idx], price=oc.price[idx], spot=oc.spot[idx], available=oc.available[idx],
+        backend=oc.backend[idx], src_backend=oc.src_backend[idx], region_id=oc.region_id[idx],
+        itype_id=oc.itype_id[idx])
+
+
+def shard_bases(n_rows_per_shard: Sequence[int]) -> np.ndarray:
+    sizes = np.asarray(n_rows_per_shard, dtype=np.int64)
+    return np.cumsum(sizes) - sizes
+
+
+def global_rows_to_source(global_rows: np.ndarray, bases: np.ndarray, perms: Sequence[np.ndarray],
+                          positions: Sequence[np.ndarray]) -> np.ndarray:
+    """Global physical rows (``shard_base + local row``, ``-1``/``2^64-1`` = none) -> positions in
+    the full source list, through the owning shard's ``perm`` and its source positions."""
+    g = np.asarray(global_rows).astype(np.int64)
+    out = np.full(g.shape, -1, dtype=np.int64)
+    for s, (perm, pos) in enumerate(zip(perms, positions)):
+        sel = (g >= bases[s]) & (g < bases[s] + len(perm))
+        local = perm[g[sel] - bases[s]]
+        out[sel] = np.asarray(pos)[local]
+    return out
+
+
+class ShardedMatcher:
+    """Device path.  ``torch`` supplies device memory, the stream and the process group only."""
+
+    def __init__(self, full: OfferColumns, *, rank: int, world: int, device: int, order: Optional[np.ndarray] = None):
+        import torch
+        import torch.distributed as dist
+
+        from . import native
+        from .engine import Matcher
+
+        self.torch, self.dist, self.native = torch, dist, native
+        self.rank, self.world = rank, world
+        self.dev = torch.device("cuda", device)
+        self.order = rank_order(full) if order is None else order
+        self.positions = shard_positions(self.order, rank, world) if world > 1 else None
+        cols = subset_columns(full, self.positions) if world > 1 else full
+        self.table: EncodedTable = encode_table(cols)
+        self.stream = torch.cuda.Stream(device=self.dev)
+        with torch.cuda.stream(self.stream):
+            self.matcher = Matcher(device, stream=self.stream.cuda_stream)
+            self.device_table = self.matcher.upload(self.table)
+            if world > 1:
+                sizes = torch.tensor([self.table.n_rows], dtype=torch.int64, device=self.dev)
+                all_sizes = torch.empty((world,), dtype=torch.int64, device=self.dev)
+                dist.all_gather_into_tensor(all_sizes, sizes)
+                self.base = torch.cumsum(all_sizes, 0) - all_sizes
+        self._bufs = None
+
+    def pack(self, jobs: JobColumns) -> PackedJobs:
+        return pack_jobs(self.table, jobs)
+
+    def prepare(self, packed: PackedJobs, k: int):
+        """Allocate the device buffers of a batch shape once (records stay resident)."""
+        torch = self.torch
+        j = len(packed.records)
+        dev = self.dev
+        b = dict(j=j, k=k, lay=self.matcher._layout(packed))
+        b["rec"] = torch.from_numpy(np.ascontiguousarray(packed.records).view(np.int32)).to(dev)
+        b["idx"] = torch.empty((j, k), dtype=torch.int32, device=dev)
+        b["cnt"] = torch.empty((j,), dtype=torch.int32, device=dev)
+        b["max"] = torch.empty((j,), dtype=torch.int32, device=dev)
+        if self.world > 1:
+            w = self.world
+            b["mp"] = torch.empty((j,), dtype=torch.float64, device=dev)
+            b["g_idx"] = torch.empty((w, j, k), dtype=torch.int32, device=dev)
+            b["g_cnt"] = torch.empty((w, j), dtype=torch.int32, device=dev)
+            b["g_max"] = torch.empty((w, j), dtype=torch.int32, device=dev)
+            b["g_mp"] = torch.empty((w, j), dtype=torch.float64, device=dev)
+            b["o_idx"] = torch.empty((j, k), dtype=torch.int64, device=dev)
+            b["o_cnt"] = torch.empty((j,), dtype=torch.int64, device=dev)
+            b["o_max"] = torch.empty((j,), dtype=torch.int64, device=dev)
+            b["o_mp"] = torch.empty((j,), dtype=torch.float64, device=dev)
+        self._bufs = b
+        return b
+
+    def step(self) -> None:
+        """One batch on the resident buffers; asynchronous on ``self.stream`` (call under it)."""
+        b, lib, h = self._bufs, self.native.lib(), self.matcher.handle
+        check = self.native.check
+        check(lib.dsm_match_topk_dev(h, self.device_table.handle, C.byref(b["lay"]), b["rec"].data_ptr(), b["j"], b["k"],
+                                     b["idx"].data_ptr(), b["cnt"].data_ptr(), b["max"].data_ptr()))
+        if self.world > 1:
+            dist = self.dist
+            check(lib.dsm_gather_price_dev(h, self.device_table.handle, b["max"].data_ptr(), b["j"], b["mp"].data_ptr()))
+            dist.all_gather_into_tensor(b["g_idx"], b["idx"])
+            dist.all_gather_into_tensor(b["g_cnt"], b["cnt"])
+            dist.all_gather_into_tensor(b["g_max"], b["max"])
+            dist.all_gather_into_tensor(b["g_mp"], b["mp"])
+            check(lib.dsm_merge_shards_dev(h, self.world, b["j"], b["k"], b["g_idx"].data_ptr(), b["g_cnt"].data_ptr(),
+                                           b["g_max"].data_ptr(), b["g_mp"].data_ptr(), self.base.data_ptr(),
+                                           b["o_idx"].data_ptr(), b["o_cnt"].data_ptr(), b["o_max"].data_ptr(),
+                                           b["o_mp"].data_ptr()))
+
+    def result_in_source_space(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
+        """(index [J,k] source positions, count [J], max_price [J]) of the last step, on every rank."""
+        b, t = self._bufs, self.table
+        self.stream.synchronize()
+        if self.world == 1:
+            idx = b["idx"].cpu().numpy().view(np.uint32)
+            src = np.where(idx == NO_ROW, -1, t.perm[np.minimum(idx, t.n_rows - 1)]).astype(np.int64)
+            cnt = b["cnt"].cpu().numpy().view(np.uint32).astype(np.int64)
+            mx = b["max"].cpu().numpy().view(np.uint32)
+            price = np.where(mx == NO_ROW, np.nan, t.price[np.minimum(mx, t.n_rows - 1)])
+            return src, cnt, price
+        gathered: List[Any] = [None] * self.world
+        self.dist.all_gather_object(gathered, (self.positions, t.perm))
+        bases = self.base.cpu().numpy()
+        src = global_rows_to_source(b["o_idx"].cpu().numpy(), bases, [g[1] for g in gathered], [g[0] for g in gathered])
+        return src, b["o_cnt"].cpu().numpy(), b["o_mp"].cpu().numpy()
+
+    def close(self) -> None:
+        self.device_table.close()
+        self.matcher.close()

@@ -102,3 +102,30 @@ def topk(table: EncodedTable, packed: PackedJobs, k: int):
                 best = b[-1]
             mx[i] = best
     return idx, cnt, mx
+
+
+def merge_shards(idx_all, cnt_all, max_all, maxprice_all, bases, k):
+    """What k_merge_shards computes: shards are in table order, so the first k matches are the
+    concatenation of the per-shard first-k lists; counts add up; the max row is the one with the
+    highest price (earlier shard wins ties).  Rows come out as global physical rows, -1 = none."""
+    n_shards, j = cnt_all.shape
+    idx_out = np.full((j, k), -1, dtype=np.int64)
+    cnt_out = np.zeros(j, dtype=np.int64)
+    max_out = np.full(j, -1, dtype=np.int64)
+    mp_out = np.full(j, np.nan)
+    for job in range(j):
+        have = 0
+        for s in range(n_shards):
+            c = int(cnt_all[s, job])
+            if c == 0:
+                continue
+            take = min(c, k, k - have)
+            idx_out[job, have:have + take] = bases[s] + idx_all[s, job, :take].astype(np.int64)
+            have += take
+            cnt_out[job] += c
+            m = int(max_all[s, job])
+            if m != NO_ROW:
+                pr = float(maxprice_all[s, job])
+                if max_out[job] < 0 or pr > mp_out[job]:
+                    max_out[job], mp_out[job] = bases[s] + m, pr
+    return idx_out, cnt_out, max_out, mp_out
