@@ -305,6 +305,14 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     gp.k = k;
     gp.slots = pl.slots;
     gp.slots_a = pl.pc.pa * MATCH_WARPS;
+    gp.rows16 = reinterpret_cast<const uint16_t*>(t->rows);
+    gp.tabs = mp.tabs;
+    gp.recs = d_jobs;
+    for (uint32_t c = 0; c < DSM_MAX_COLS; ++c) { gp.lut[c] = mp.lut[c]; gp.base[c] = mp.base[c]; }
+    gp.n_cols = t->desc.n_cols;
+    gp.n_used = L->n_used;
+    gp.n_entries = pl.lay.n_entries;
+    gp.rec_words = L->rec_words;
     gp.out_idx = d_idx;
     gp.out_cnt = d_cnt;
     gp.out_max = d_max;

@@ -170,7 +170,7 @@ struct MatchParams {
   uint32_t slots;        // slots per job = pieces per group * 8
   uint32_t* work_counter;
   uint32_t* part_cnt;    // [jobs_pad][slots]
-  uint32_t* part_last;   // [jobs_pad][slots]
+  uint32_t* part_last;   // [jobs_pad][slots]: last 32-row block with a match (DSM_NO_ROW: none)
   uint2* part_log;       // [jobs_pad][slots][k] x (block, match word)
   uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
 };
@@ -181,6 +181,14 @@ struct MergeParams {
   const uint2* part_log;
   const double* price;
   uint32_t n_jobs, k, slots, slots_a;  // slots below slots_a belong to the first segment
+  // to find the last matching row inside the last block with a match, that one block is
+  // evaluated again for the job from the global copies of rows and tables
+  const uint16_t* rows16;
+  const uint4* tabs;
+  const uint32_t* recs;
+  const uint16_t* lut[DSM_MAX_COLS];
+  uint32_t base[DSM_MAX_COLS];
+  uint32_t n_cols, n_used, n_entries, rec_words;
   uint32_t* out_idx;
   uint32_t* out_cnt;
   uint32_t* out_max;
@@ -307,11 +315,12 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   XposeCtl xc;
   transpose_setup(xc, lane);
 
+  // Gather address of column c for a row = tab0 + (base[c] << shift)   (warp-uniform)
+  //                                      + ((code << shift) | lane_off)  (per lane, 2 ALU ops)
   const uint32_t code_shift = 4u + rep_shift;
-  uint32_t taddr[NC];  // shared-memory byte address of this lane's copy of each column's entry 0
-#pragma unroll
-  for (int c = 0; c < NC; ++c)
-    taddr[c] = smem_u32(s_tab) + (p.base[c] << code_shift) + ((lane & ((1u << rep_shift) - 1u)) << 4);
+  const uint32_t code_mask = 0xFFFFu << code_shift;
+  const uint32_t lane_off = (lane & ((1u << rep_shift) - 1u)) << 4;  // this lane's copy of an entry
+  const uint32_t tab0 = smem_u32(s_tab);
 
   if (tid == 0) {
     mbar_init(&s_bar, 1);
@@ -378,18 +387,14 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     // Rows below a job's cut-off pass its price / availability test.  full[t] holds the jobs
     // of tile t that pass on every row of the current block; it only changes at an "event"
     // block, the block a cut-off falls into, where the per-row comparison is done.
-    uint32_t cutv[TPG];  // lane j: cut-off row of job 32t+j in this segment
-#pragma unroll
-    for (int t = 0; t < TPG; ++t) cutv[t] = s_cut[(pos >= pc.pa ? JPG : 0u) + t * 32 + lane];
+    const uint32_t* cut_lane = s_cut + (pos >= pc.pa ? JPG : 0u) + lane;  // + 32t: job 32t+lane's cut-off
     uint32_t full[TPG];
     uint32_t next_evt = b0;  // forces the classification on the first block
 
-    uint32_t cnt[TPG], ent[TPG], last_word[TPG], last_blk[TPG];
+    // per job (lane j, tile t): matches, log entries written, last block with a match
+    uint32_t cnt[TPG], ent[TPG], last_blk[TPG];
 #pragma unroll
-    for (int t = 0; t < TPG; ++t) { cnt[t] = 0; ent[t] = 0; last_word[t] = 0; last_blk[t] = 0; full[t] = 0; }
-    // first-k log of (job = 32t + lane, this slot): [jobs_pad][slots][k] entries of 8 bytes
-    uint2* log_lane = p.part_log + ((size_t)(group * JPG + lane) * p.slots + slot) * kk;
-    const size_t log_tile_stride = (size_t)32 * p.slots * kk;
+    for (int t = 0; t < TPG; ++t) { cnt[t] = 0; ent[t] = 0; last_blk[t] = DSM_NO_ROW; full[t] = 0; }
 
     // rows are prefetched two blocks ahead (L2 latency is longer than one block of work)
     RowCodes<NC> rc0, rc1;
@@ -415,14 +420,15 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         uint32_t nxt = 0xFFFFFFFFu;
 #pragma unroll
         for (int t = 0; t < TPG; ++t) {
-          full[t] = __ballot_sync(0xFFFFFFFFu, cutv[t] >= row_end);
-          uint32_t part = __ballot_sync(0xFFFFFFFFu, cutv[t] > blk * 32u && cutv[t] < row_end);
+          const uint32_t cutv = cut_lane[t * 32];  // lane j: cut-off row of job 32t+j
+          full[t] = __ballot_sync(0xFFFFFFFFu, cutv >= row_end);
+          uint32_t part = __ballot_sync(0xFFFFFFFFu, cutv > blk * 32u && cutv < row_end);
           while (part) {
             const uint32_t j = __ffs(part) - 1;
             part &= part - 1;
-            pw[t] |= (row < __shfl_sync(0xFFFFFFFFu, cutv[t], j)) ? (1u << j) : 0u;
+            pw[t] |= (row < __shfl_sync(0xFFFFFFFFu, cutv, j)) ? (1u << j) : 0u;
           }
-          if (cutv[t] >= row_end) nxt = min(nxt, cutv[t] >> 5);  // block where this job leaves `full`
+          if (cutv >= row_end) nxt = min(nxt, cutv >> 5);  // block where this job leaves `full`
         }
         next_evt = __reduce_min_sync(0xFFFFFFFFu, nxt);
         m = make_uint4(full[0] | pw[0], full[1] | pw[1], full[2] | pw[2], full[3] | pw[3]);
@@ -433,11 +439,17 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       // gather one 128-bit word group per column and AND them
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
-        uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
+        uint32_t off;  // (code << code_shift) | lane_off
         if constexpr (HAS_LUT) {
+          uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
           if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+          off = (code << code_shift) | lane_off;
+        } else {
+          const uint32_t w = cur.w[c >> 1];
+          const uint32_t sh = (c & 1) ? (w >> (16u - code_shift)) : (w << code_shift);
+          off = (sh & code_mask) | lane_off;
         }
-        const uint4 a = lds128(taddr[c] + (code << code_shift));
+        const uint4 a = lds128(tab0 + (p.base[c] << code_shift) + off);
         m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
       }
 
@@ -469,16 +481,17 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         for (int t = 0; t < TPG; ++t) {
           const bool hit = T[t] != 0u;
           want = want || (hit && cnt[t] < kk);
-          last_word[t] = hit ? T[t] : last_word[t];
           last_blk[t] = hit ? blk : last_blk[t];
         }
         if (__any_sync(0xFFFFFFFFu, want)) {
           // a job that still lacks k matches logs (block, match word); k_merge expands the
           // words to rows.  At most k entries per (job, slot): every entry has >= 1 match.
+          // Log of (job, slot): part_log[(job * slots + slot) * k ...], 8-byte entries.
 #pragma unroll
           for (int t = 0; t < TPG; ++t) {
             if (T[t] != 0u && cnt[t] < kk) {
-              log_lane[(size_t)t * log_tile_stride + ent[t]] = make_uint2(blk, T[t]);
+              const size_t at = ((size_t)(group * JPG + t * 32 + lane) * p.slots + slot) * kk + ent[t];
+              p.part_log[at] = make_uint2(blk, T[t]);
               ent[t] += 1;
             }
           }
@@ -493,7 +506,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       for (int t = 0; t < TPG; ++t) {
         const size_t o = (size_t)(group * JPG + t * 32 + lane) * p.slots + slot;
         p.part_cnt[o] = cnt[t];
-        p.part_last[o] = last_word[t] ? last_blk[t] * 32u + 31u - __clz(last_word[t]) : DSM_NO_ROW;
+        p.part_last[o] = last_blk[t];  // k_merge finds the row inside the block
       }
     }
   }
@@ -554,7 +567,7 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
     const bool seg_b = s >= p.slots_a;
     const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c != 0 && !seg_b);
     const uint32_t hit_b = __ballot_sync(0xFFFFFFFFu, c != 0 && seg_b);
-    const uint32_t l = c ? lst[s] : DSM_NO_ROW;
+    const uint32_t l = c ? lst[s] : DSM_NO_ROW;  // last block with a match in this slot
     if (hit_a) last_a = __shfl_sync(0xFFFFFFFFu, l, 31 - __clz(hit_a));
     if (hit_b) last_b = __shfl_sync(0xFFFFFFFFu, l, 31 - __clz(hit_b));
     const uint32_t sum = __shfl_sync(0xFFFFFFFFu, incl, 31);
@@ -562,6 +575,30 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
     have = min(p.k, have + sum);  // saturating: only used against k
   }
   for (uint32_t i = have + lane; i < p.k; i += 32) out[i] = DSM_NO_ROW;
+
+  // last_a / last_b are blocks: evaluate the 32 rows of each (lane = row) to get the last row
+  {
+    const uint32_t tile = (job % JPG) / 32u, bit = job & 31u;
+    const uint32_t* tab = reinterpret_cast<const uint32_t*>(p.tabs + (size_t)(job / JPG) * p.n_entries);
+    const uint32_t cut_a = p.recs[(size_t)job * p.rec_words + 0];
+    const uint32_t cut_b = p.recs[(size_t)job * p.rec_words + 1];
+    uint32_t* last[2] = {&last_a, &last_b};
+    const uint32_t cut[2] = {cut_a, cut_b};
+    for (int seg = 0; seg < 2; ++seg) {
+      const uint32_t blk = *last[seg];
+      if (blk == DSM_NO_ROW) continue;  // warp-uniform
+      const uint32_t row = blk * 32u + lane;
+      bool ok = row < cut[seg];
+      const uint16_t* codes = p.rows16 + (size_t)row * p.n_cols;
+      for (uint32_t c = 0; c < p.n_used; ++c) {
+        uint32_t code = codes[c];
+        if (p.lut[c] != nullptr) code = p.lut[c][code];
+        ok = ok && ((tab[(size_t)(p.base[c] + code) * 4u + tile] >> bit) & 1u);
+      }
+      const uint32_t hits = __ballot_sync(0xFFFFFFFFu, ok);
+      *last[seg] = hits ? blk * 32u + 31u - __clz(hits) : DSM_NO_ROW;
+    }
+  }
   if (lane == 0) {
     p.out_cnt[job] = total;
     uint32_t best = last_a;
