@@ -145,7 +145,7 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     const uint32_t need = base * 16u * ((1u << rs) + 1u) + cuts;
     if (need <= MAX_SMEM_BYTES / MATCH_CTAS_PER_SM) { pl.rep_shift = rs; break; }
   }
-  if (force_rep) pl.rep_shift = (uint32_t)atoi(force_rep) & 3u;
+  if (force_rep) pl.rep_shift = atoi(force_rep) >= 3 ? 3u : 0u;
   pl.smem = base * 16u * (pl.rep_shift ? (1u << pl.rep_shift) + 1u : 1u) + cuts;
   if (pl.smem > MAX_SMEM_BYTES) { pl.rep_shift = 0; pl.smem = base * 16u + cuts; }
   pl.n_groups = (n_jobs + JPG - 1) / JPG;
@@ -183,20 +183,23 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   return 0;
 }
 
+template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT, bool REP8>
+static cudaError_t launch_match_v(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
+  cudaError_t e = cudaFuncSetAttribute(k_match<NC, ROW32, BITMAP, HAS_LUT, REP8>,
+                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  k_match<NC, ROW32, BITMAP, HAS_LUT, REP8><<<grid, MATCH_THREADS, smem, st>>>(mp);
+  return cudaGetLastError();
+}
+
 template <int NC, bool ROW32, bool BITMAP>
 static cudaError_t launch_match_nc(const MatchParams& mp, bool has_lut, uint32_t grid, uint32_t smem,
                                    cudaStream_t st) {
-  cudaError_t e;
-  if (has_lut) {
-    e = cudaFuncSetAttribute(k_match<NC, ROW32, BITMAP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    k_match<NC, ROW32, BITMAP, true><<<grid, MATCH_THREADS, smem, st>>>(mp);
-  } else {
-    e = cudaFuncSetAttribute(k_match<NC, ROW32, BITMAP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    k_match<NC, ROW32, BITMAP, false><<<grid, MATCH_THREADS, smem, st>>>(mp);
-  }
-  return cudaGetLastError();
+  const bool rep8 = mp.rep_shift == 3u;
+  if (has_lut) return rep8 ? launch_match_v<NC, ROW32, BITMAP, true, true>(mp, grid, smem, st)
+                           : launch_match_v<NC, ROW32, BITMAP, true, false>(mp, grid, smem, st);
+  return rep8 ? launch_match_v<NC, ROW32, BITMAP, false, true>(mp, grid, smem, st)
+              : launch_match_v<NC, ROW32, BITMAP, false, false>(mp, grid, smem, st);
 }
 
 template <bool BITMAP>
@@ -229,6 +232,8 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   int rc = make_plan(ctx, t, L, n_jobs, pl);
   if (rc) return rc;
   if (!bitmap && (k == 0 || k > 4096)) return fail(DSM_E_ARG, "k must be in 1..4096");
+  if (!bitmap && (unsigned long long)pl.n_groups * JPG * pl.slots * k > 0xFFFFFFFFull)
+    return fail(DSM_E_TOO_LARGE, "first-k log of this batch exceeds 2^32 entries; use fewer jobs per call or a smaller k");
   const bool row32 = t->desc.n_cols == 16;
   if (row32 && L->n_used < 5) return fail(DSM_E_ARG, "16-column tables need n_used >= 5");
   CK(cudaSetDevice(ctx->device));

@@ -294,7 +294,7 @@ __device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCod
   }
 }
 
-template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT>
+template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT, bool REP8>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
   // shared memory: [staging: E entries][table: E entries x R copies][cut-offs: 2 x 128]
   // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
@@ -302,7 +302,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   // quarter-warp phase of a 128-bit gather hit 8 different bank groups: no bank conflicts
   // whatever the codes are.  R < 8 (large dictionaries) only reduces them.
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const uint32_t rep_shift = p.rep_shift;
+  constexpr uint32_t rep_shift = REP8 ? 3u : 0u;
   uint4* s_stage = reinterpret_cast<uint4*>(smem_raw);
   uint4* s_tab = rep_shift ? s_stage + p.n_entries : s_stage;
   uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + ((size_t)p.n_entries << rep_shift));  // [2][128]
@@ -315,12 +315,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   XposeCtl xc;
   transpose_setup(xc, lane);
 
-  // Gather address of column c for a row = tab0 + (base[c] << shift)   (warp-uniform)
-  //                                      + ((code << shift) | lane_off)  (per lane, 2 ALU ops)
-  const uint32_t code_shift = 4u + rep_shift;
-  const uint32_t code_mask = 0xFFFFu << code_shift;
-  const uint32_t lane_off = (lane & ((1u << rep_shift) - 1u)) << 4;  // this lane's copy of an entry
-  const uint32_t tab0 = smem_u32(s_tab);
+  // Gather address of column c for a row: lane_base (table start + this lane's copy)
+  //                                      + (code << SHIFT) + (base[c] << SHIFT, warp-uniform)
+  constexpr uint32_t SHIFT = 4u + rep_shift;
+  const uint32_t lane_base = smem_u32(s_tab) + ((lane & ((1u << rep_shift) - 1u)) << 4);
 
   if (tid == 0) {
     mbar_init(&s_bar, 1);
@@ -391,27 +389,18 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     uint32_t full[TPG];
     uint32_t next_evt = b0;  // forces the classification on the first block
 
-    // per job (lane j, tile t): matches, log entries written, last block with a match
-    uint32_t cnt[TPG], ent[TPG], last_blk[TPG];
+    // per job (lane j, tile t): matches, last block with a match, next free element of the
+    // job's first-k log in this slot (index into part_log; the host checks it fits 32 bits)
+    uint32_t cnt[TPG], last_blk[TPG], lidx[TPG];
 #pragma unroll
-    for (int t = 0; t < TPG; ++t) { cnt[t] = 0; ent[t] = 0; last_blk[t] = DSM_NO_ROW; full[t] = 0; }
+    for (int t = 0; t < TPG; ++t) {
+      cnt[t] = 0;
+      last_blk[t] = DSM_NO_ROW;
+      full[t] = 0;
+      lidx[t] = ((group * JPG + t * 32 + lane) * p.slots + slot) * kk;
+    }
 
-    // rows are prefetched two blocks ahead (L2 latency is longer than one block of work)
-    RowCodes<NC> rc0, rc1;
-    if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, rc0);
-    if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rc1);
-#pragma unroll
-    for (uint32_t a = 2; a < PREFETCH_BLOCKS; ++a)
-      if (b0 + a < b1) prefetch_l1(rows_lane + (size_t)(b0 + a) * (ROW32 ? 64u : 32u));
-
-#pragma unroll 1
-    for (uint32_t blk = b0; blk < b1; ++blk) {
-      const RowCodes<NC> cur = rc0;
-      rc0 = rc1;
-      if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, rc1);
-      if (blk + PREFETCH_BLOCKS < b1)
-        prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
-
+    auto process = [&](const uint32_t blk, const RowCodes<NC>& cur) {
       uint4 m;
       if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
         const uint32_t row = blk * 32u + lane;
@@ -439,17 +428,11 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       // gather one 128-bit word group per column and AND them
 #pragma unroll
       for (int c = 0; c < NC; ++c) {
-        uint32_t off;  // (code << code_shift) | lane_off
+        uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
         if constexpr (HAS_LUT) {
-          uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
           if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-          off = (code << code_shift) | lane_off;
-        } else {
-          const uint32_t w = cur.w[c >> 1];
-          const uint32_t sh = (c & 1) ? (w >> (16u - code_shift)) : (w << code_shift);
-          off = (sh & code_mask) | lane_off;
         }
-        const uint4 a = lds128(tab0 + (p.base[c] << code_shift) + off);
+        const uint4 a = lds128(lane_base + (code << SHIFT) + (p.base[c] << SHIFT));
         m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
       }
 
@@ -486,20 +469,41 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         if (__any_sync(0xFFFFFFFFu, want)) {
           // a job that still lacks k matches logs (block, match word); k_merge expands the
           // words to rows.  At most k entries per (job, slot): every entry has >= 1 match.
-          // Log of (job, slot): part_log[(job * slots + slot) * k ...], 8-byte entries.
 #pragma unroll
           for (int t = 0; t < TPG; ++t) {
             if (T[t] != 0u && cnt[t] < kk) {
-              const size_t at = ((size_t)(group * JPG + t * 32 + lane) * p.slots + slot) * kk + ent[t];
-              p.part_log[at] = make_uint2(blk, T[t]);
-              ent[t] += 1;
+              p.part_log[lidx[t]] = make_uint2(blk, T[t]);
+              lidx[t] += 1;
             }
           }
         }
 #pragma unroll
         for (int t = 0; t < TPG; ++t) cnt[t] += __popc(T[t]);
       }
+    };
+
+    // two row buffers used alternately (no register rotation); the rows themselves were
+    // requested PREFETCH_BLOCKS blocks ahead into L1
+    RowCodes<NC> ra, rb;
+    if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, ra);
+    if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rb);
+#pragma unroll
+    for (uint32_t a = 2; a < PREFETCH_BLOCKS; ++a)
+      if (b0 + a < b1) prefetch_l1(rows_lane + (size_t)(b0 + a) * (ROW32 ? 64u : 32u));
+
+    uint32_t blk = b0;
+#pragma unroll 1
+    for (; blk + 1 < b1; blk += 2) {
+      if (blk + PREFETCH_BLOCKS < b1)
+        prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
+      process(blk, ra);
+      if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, ra);
+      if (blk + 1 + PREFETCH_BLOCKS < b1)
+        prefetch_l1(rows_lane + (size_t)(blk + 1 + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
+      process(blk + 1, rb);
+      if (blk + 3 < b1) load_row<NC, ROW32>(rows_lane, (blk + 3) * 32u, rb);
     }
+    if (blk < b1) process(blk, ra);
 
     if constexpr (!BITMAP) {
 #pragma unroll
