@@ -22,8 +22,10 @@
 
 #define JPG DSM_JOBS_PER_GROUP  // 128 jobs per group
 #define TPG 4                   // 32-job tiles per group
-#define MATCH_THREADS 256
+#ifndef MATCH_WARPS
 #define MATCH_WARPS 8
+#endif
+#define MATCH_THREADS (32 * MATCH_WARPS)
 #ifndef MATCH_CTAS_PER_SM
 #define MATCH_CTAS_PER_SM 3
 #endif
@@ -491,19 +493,22 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     for (uint32_t a = 2; a < PREFETCH_BLOCKS; ++a)
       if (b0 + a < b1) prefetch_l1(rows_lane + (size_t)(b0 + a) * (ROW32 ? 64u : 32u));
 
+    // a block's codes are copied out of its buffer first and the buffer is reloaded at once,
+    // so every load has two blocks of work to land
+    auto step = [&](const uint32_t blk, RowCodes<NC>& buf) {
+      const RowCodes<NC> cur = buf;
+      if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, buf);
+      if (blk + PREFETCH_BLOCKS < b1)
+        prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
+      process(blk, cur);
+    };
     uint32_t blk = b0;
 #pragma unroll 1
     for (; blk + 1 < b1; blk += 2) {
-      if (blk + PREFETCH_BLOCKS < b1)
-        prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
-      process(blk, ra);
-      if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, ra);
-      if (blk + 1 + PREFETCH_BLOCKS < b1)
-        prefetch_l1(rows_lane + (size_t)(blk + 1 + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
-      process(blk + 1, rb);
-      if (blk + 3 < b1) load_row<NC, ROW32>(rows_lane, (blk + 3) * 32u, rb);
+      step(blk, ra);
+      step(blk + 1, rb);
     }
-    if (blk < b1) process(blk, ra);
+    if (blk < b1) step(blk, ra);
 
     if constexpr (!BITMAP) {
 #pragma unroll
