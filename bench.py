@@ -41,13 +41,13 @@ UNIT = "evals/s"
 def workload(n_gpus: int, override: str = ""):
     name = override or ("cfg3" if n_gpus == 1 else "cfg4")
     if name == "cfg3":
-        return dict(workload="cfg3: 4096 jobs x 1048576 offers, top-16, seed 3", jobs=4096, offers=1 << 20,
+        return dict(name="cfg3", workload="cfg3: 4096 jobs x 1048576 offers, top-16, seed 3", jobs=4096, offers=1 << 20,
                     k=16, seed=3, shapes=4096)
     if name == "cfg4":
-        return dict(workload="cfg4: 16384 jobs x 67108864 offers sharded over the GPUs, top-16, seed 4",
+        return dict(name="cfg4", workload="cfg4: 16384 jobs x 67108864 offers sharded over the GPUs, top-16, seed 4",
                     jobs=16384, offers=1 << 26, k=16, seed=4, shapes=4096)
     if name == "tiny":  # CPU-side plumbing tests
-        return dict(workload="tiny: 256 jobs x 65536 offers, top-16, seed 3", jobs=256, offers=1 << 16, k=16,
+        return dict(name="tiny", workload="tiny: 256 jobs x 65536 offers, top-16, seed 3", jobs=256, offers=1 << 16, k=16,
                     seed=3, shapes=512)
     raise SystemExit(f"unknown workload {name}")
 
@@ -381,6 +381,13 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         peaks_src = "MEASURED_PEAKS.json hbm_gbs"
     except Exception:
         pass
+    traffic = None
+    try:  # per-launch DRAM bytes of k_match from the committed ncu capture of this workload
+        t = json.load(open(os.path.join(ROOT, "profiles", "k_match_traffic.json"))).get(wl["name"])
+        if t and world == 1:
+            traffic = int(t["dram_read_bytes"]) + int(t["dram_write_bytes"])
+    except Exception:
+        pass
     groups = (J + 127) // 128
     row_bytes = table.n_cols * 2
     alg_bytes = groups * table.n_rows * row_bytes + J * rec_words * 4 + J * (k + 2) * 4
@@ -402,7 +409,7 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         "gpu_launches": int(launches),
         "clocks": clock_info,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": None, "kernel": "k_match",
+                     "frac": achieved / hbm_peak, "traffic": traffic, "kernel": "k_match",
                      "kernel_ms": match_ms, "kernel_share_of_step": match_ms / statistics.mean(step_ms),
                      "algorithmic_bytes_per_launch": int(alg_bytes), "peak_source": peaks_src,
                      "note": "k_match is bound by instruction issue and the LSU/shared-memory pipe, not HBM: "
