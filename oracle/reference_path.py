@@ -362,3 +362,55 @@ def plan_slice(offers: Sequence[Any], k: int):
     server/background/tasks/process_submitted_jobs.py:450."""
     prices = [o.price for o in offers]
     return list(offers[:k]), len(offers), (max(prices) if prices else None)
+
+
+# --------------------------------------------------------------------------- callers (SURVEY §8f rows 1, 3)
+
+
+def assign_job_to_pool_instance(pool_instances: Sequence[Any], profile, requirements, *, fleet_model=None,
+                                multinode=False, master_job_provisioning_data=None, volumes=None):
+    """server/background/tasks/process_submitted_jobs.py:347-400 without the DB session: pick the
+    cheapest candidate (unshared IDLE instances first, then shared ones with enough idle blocks),
+    mark it BUSY and grow its busy_blocks.  Returns ``(instance, offer)`` or ``None``."""
+    unshared = filter_pool_instances(pool_instances, profile, requirements=requirements, status=M.InstanceStatus.IDLE,
+                                     fleet_model=fleet_model, multinode=multinode,
+                                     master_job_provisioning_data=master_job_provisioning_data, volumes=volumes,
+                                     shared=False)
+    candidates = [(inst, M.InstanceOfferWithAvailability.parse_raw(inst.offer)) for inst in unshared]
+    if not multinode:
+        candidates.extend(get_shared_pool_instances_with_offers(pool_instances, profile, requirements, idle_only=True,
+                                                                fleet_model=fleet_model, volumes=volumes))
+    if not candidates:
+        return None
+    candidates.sort(key=lambda pair: pair[0].price or 0)
+    inst, offer = candidates[0]
+    inst.status = M.InstanceStatus.BUSY
+    inst.busy_blocks += offer.blocks
+    return inst, offer
+
+
+def get_plan_offers(pool_offers: Sequence[Any], offers: Sequence[Tuple[Any, Any]], k: int = 50):
+    """server/services/runs.py:336-349: pool offers, then backend offers, stable sort on
+    availability, first ``k``, total, max price."""
+    job_offers = list(pool_offers)
+    job_offers.extend(o for _, o in offers)
+    job_offers.sort(key=lambda o: not o.availability.is_available())
+    return job_offers[:k], len(job_offers), max((o.price for o in job_offers), default=None)
+
+
+def get_pool_offers(pool_instances: Sequence[Any], profile, requirements, *, multinode=False, volumes=None):
+    """server/services/runs.py:674-715 without the DB: shared offers first, then unshared
+    instances (IDLE / BUSY by status), sorted by price."""
+    pool_offers = []
+    if not multinode:
+        for _, offer in get_shared_pool_instances_with_offers(pool_instances, profile, requirements, volumes=volumes):
+            pool_offers.append(offer)
+    for inst in filter_pool_instances(pool_instances, profile, requirements=requirements, multinode=multinode,
+                                      volumes=volumes, shared=False):
+        if inst.offer is None:
+            continue
+        offer = M.InstanceOfferWithAvailability.parse_raw(inst.offer)
+        offer.availability = M.InstanceAvailability.IDLE if inst.status == M.InstanceStatus.IDLE else M.InstanceAvailability.BUSY
+        pool_offers.append(offer)
+    pool_offers.sort(key=lambda o: o.price)
+    return pool_offers
