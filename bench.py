@@ -40,12 +40,16 @@ UNIT = "evals/s"
 
 def workload(n_gpus: int, override: str = ""):
     name = override or ("cfg3" if n_gpus == 1 else "cfg4")
-    if name == "cfg3":
-        return dict(name="cfg3", workload="cfg3: 4096 jobs x 1048576 offers, top-16, seed 3", jobs=4096, offers=1 << 20,
-                    k=16, seed=3, shapes=4096)
+    if name == "cfg3" or name.startswith("cfg3:k"):  # cfg3:k50 etc. = config 3 with another k
+        k = int(name.split(":k")[1]) if ":k" in name else 16
+        return dict(name=name, workload=f"cfg3: 4096 jobs x 1048576 offers, top-{k}, seed 3", jobs=4096,
+                    offers=1 << 20, k=k, seed=3, shapes=4096)
     if name == "cfg4":
         return dict(name="cfg4", workload="cfg4: 16384 jobs x 67108864 offers sharded over the GPUs, top-16, seed 4",
                     jobs=16384, offers=1 << 26, k=16, seed=4, shapes=4096)
+    if name.startswith("custom:"):  # tuning: custom:<jobs>x<offers>
+        j, n = (int(x) for x in name.split(":", 1)[1].split("x"))
+        return dict(name=name, workload=f"{name}, top-16, seed 4", jobs=j, offers=n, k=16, seed=4, shapes=4096)
     if name == "tiny":  # CPU-side plumbing tests
         return dict(name="tiny", workload="tiny: 256 jobs x 65536 offers, top-16, seed 3", jobs=256, offers=1 << 16, k=16,
                     seed=3, shapes=512)

@@ -508,11 +508,11 @@ int dsm_match_bitmap(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
   return 0;
 }
 
-int dsm_merge_shards_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
-                         const uint32_t* d_idx_all, const uint32_t* d_cnt_all,
-                         const uint32_t* d_max_all, const double* d_maxprice_all,
-                         const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
-                         uint64_t* d_max_out, double* d_maxprice_out) {
+static int merge_shards(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                        const uint32_t* d_idx_all, const uint32_t* d_cnt_all, const uint32_t* d_max_all,
+                        const double* d_maxprice_all, size_t shard_stride_bytes,
+                        const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
+                        uint64_t* d_max_out, double* d_maxprice_out) {
   if (!ctx || !d_idx_all || !d_cnt_all || !d_max_all || !d_maxprice_all || !d_shard_base ||
       !d_idx_out || !d_cnt_out || !d_max_out || !d_maxprice_out)
     return fail(DSM_E_ARG, "NULL argument");
@@ -520,11 +520,30 @@ int dsm_merge_shards_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint3
   std::lock_guard<std::mutex> g(ctx->mu);
   CK(cudaSetDevice(ctx->device));
   k_merge_shards<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
-      n_shards, n_jobs, k, d_idx_all, d_cnt_all, d_max_all, d_maxprice_all, d_shard_base, d_idx_out,
-      d_cnt_out, d_max_out, d_maxprice_out);
+      n_shards, n_jobs, k, d_idx_all, d_cnt_all, d_max_all, d_maxprice_all, shard_stride_bytes,
+      d_shard_base, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
   CK(cudaGetLastError());
   ctx->launches++;
   return 0;
+}
+
+int dsm_merge_shards_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                         const uint32_t* d_idx_all, const uint32_t* d_cnt_all,
+                         const uint32_t* d_max_all, const double* d_maxprice_all,
+                         const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
+                         uint64_t* d_max_out, double* d_maxprice_out) {
+  return merge_shards(ctx, n_shards, n_jobs, k, d_idx_all, d_cnt_all, d_max_all, d_maxprice_all, 0,
+                      d_shard_base, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
+}
+
+int dsm_merge_shards_strided_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                                 const uint32_t* d_idx0, const uint32_t* d_cnt0, const uint32_t* d_max0,
+                                 const double* d_maxprice0, size_t shard_stride_bytes,
+                                 const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
+                                 uint64_t* d_max_out, double* d_maxprice_out) {
+  if (shard_stride_bytes == 0 || shard_stride_bytes % 8) return fail(DSM_E_ARG, "shard stride must be a non-zero multiple of 8");
+  return merge_shards(ctx, n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
+                      d_shard_base, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
 }
 
 int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_rows, uint32_t n,

@@ -631,10 +631,13 @@ __global__ void k_gather_price(const double* price, const uint32_t* rows, uint32
 }
 
 // Shards are in table order: concatenate per-shard first-k lists, sum counts, keep the
-// highest-priced max row.  One thread per job.
+// highest-priced max row.  One thread per job.  With shard_stride_bytes == 0 the four inputs are
+// dense [n_shards][...] arrays; otherwise every pointer addresses shard 0's field and shard s's
+// field lies s * shard_stride_bytes further on (all fields of a shard in one all-gathered record).
 __global__ void k_merge_shards(uint32_t n_shards, uint32_t n_jobs, uint32_t k,
                                const uint32_t* idx_all, const uint32_t* cnt_all,
                                const uint32_t* max_all, const double* maxprice_all,
+                               size_t shard_stride_bytes,
                                const uint64_t* shard_base, uint64_t* idx_out, uint64_t* cnt_out,
                                uint64_t* max_out, double* maxprice_out) {
   const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
@@ -644,17 +647,30 @@ __global__ void k_merge_shards(uint32_t n_shards, uint32_t n_jobs, uint32_t k,
   uint64_t best = ~0ull;
   double best_price = 0.0;
   for (uint32_t s = 0; s < n_shards; ++s) {
-    const size_t o = (size_t)s * n_jobs + job;
-    const uint32_t c = cnt_all[o];
+    const uint32_t *idx_s, *cnt_s, *max_s;
+    const double* mp_s;
+    if (shard_stride_bytes) {
+      const size_t off = (size_t)s * shard_stride_bytes;
+      idx_s = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(idx_all) + off);
+      cnt_s = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(cnt_all) + off);
+      max_s = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(max_all) + off);
+      mp_s = reinterpret_cast<const double*>(reinterpret_cast<const char*>(maxprice_all) + off);
+    } else {
+      idx_s = idx_all + (size_t)s * n_jobs * k;
+      cnt_s = cnt_all + (size_t)s * n_jobs;
+      max_s = max_all + (size_t)s * n_jobs;
+      mp_s = maxprice_all + (size_t)s * n_jobs;
+    }
+    const uint32_t c = cnt_s[job];
     if (c == 0) continue;
     const uint32_t take = min(min(c, k), k - have);
     for (uint32_t i = 0; i < take; ++i)
-      idx_out[(size_t)job * k + have + i] = shard_base[s] + idx_all[o * k + i];
+      idx_out[(size_t)job * k + have + i] = shard_base[s] + idx_s[(size_t)job * k + i];
     have += take;
     total += c;
-    const uint32_t m = max_all[o];
+    const uint32_t m = max_s[job];
     if (m != DSM_NO_ROW) {
-      const double pr = maxprice_all[o];
+      const double pr = mp_s[job];
       if (best == ~0ull || pr > best_price) { best = shard_base[s] + m; best_price = pr; }
     }
   }

@@ -3,8 +3,8 @@
 Rank r holds a contiguous range of the global result order (stable sort of the source list by
 ``(not available, price)``, the order ``server/services/backends/__init__.py:449-451``
 produces) as its own device table with its own dictionaries; job records are replicated.  A
-step is: local ``dsm_match_topk_dev`` -> ``dsm_gather_price_dev`` -> ``all_gather`` of the
-per-shard first-k rows, counts, max rows and their prices -> ``dsm_merge_shards_dev``.  Because
+step is: local ``dsm_match_topk_dev`` -> ``dsm_gather_price_dev`` -> ONE ``all_gather`` of a per-shard
+record (first-k rows, counts, max rows and their prices) -> ``dsm_merge_shards_strided_dev``.  Because
 shards are in result order the merge is a concatenation and the total order is the *global
 physical row* ``shard_base[s] + local row``.
 
@@ -101,16 +101,21 @@ class ShardedMatcher:
         dev = self.dev
         b = dict(j=j, k=k, lay=self.matcher._layout(packed))
         b["rec"] = torch.from_numpy(np.ascontiguousarray(packed.records).view(np.int32)).to(dev)
-        b["idx"] = torch.empty((j, k), dtype=torch.int32, device=dev)
-        b["cnt"] = torch.empty((j,), dtype=torch.int32, device=dev)
-        b["max"] = torch.empty((j,), dtype=torch.int32, device=dev)
+        # one record per shard: [idx J*k | cnt J | max J | (pad) | max price J f64], so that a
+        # single all_gather moves everything
+        w_idx, w_cnt = j * k, j
+        w_head = (w_idx + 2 * w_cnt + 1) // 2 * 2          # keep the f64 part 8-byte aligned
+        words = w_head + 2 * j
+        b["words"] = words
+        rec_out = torch.empty((words,), dtype=torch.int32, device=dev)
+        b["out"] = rec_out
+        b["idx"] = rec_out[:w_idx].view(j, k)
+        b["cnt"] = rec_out[w_idx:w_idx + w_cnt]
+        b["max"] = rec_out[w_idx + w_cnt:w_idx + 2 * w_cnt]
+        b["mp"] = rec_out[w_head:].view(torch.float64)
         if self.world > 1:
             w = self.world
-            b["mp"] = torch.empty((j,), dtype=torch.float64, device=dev)
-            b["g_idx"] = torch.empty((w, j, k), dtype=torch.int32, device=dev)
-            b["g_cnt"] = torch.empty((w, j), dtype=torch.int32, device=dev)
-            b["g_max"] = torch.empty((w, j), dtype=torch.int32, device=dev)
-            b["g_mp"] = torch.empty((w, j), dtype=torch.float64, device=dev)
+            b["g_out"] = torch.empty((w, words), dtype=torch.int32, device=dev)
             b["o_idx"] = torch.empty((j, k), dtype=torch.int64, device=dev)
             b["o_cnt"] = torch.empty((j,), dtype=torch.int64, device=dev)
             b["o_max"] = torch.empty((j,), dtype=torch.int64, device=dev)
@@ -127,14 +132,14 @@ class ShardedMatcher:
         if self.world > 1:
             dist = self.dist
             check(lib.dsm_gather_price_dev(h, self.device_table.handle, b["max"].data_ptr(), b["j"], b["mp"].data_ptr()))
-            dist.all_gather_into_tensor(b["g_idx"], b["idx"])
-            dist.all_gather_into_tensor(b["g_cnt"], b["cnt"])
-            dist.all_gather_into_tensor(b["g_max"], b["max"])
-            dist.all_gather_into_tensor(b["g_mp"], b["mp"])
-            check(lib.dsm_merge_shards_dev(h, self.world, b["j"], b["k"], b["g_idx"].data_ptr(), b["g_cnt"].data_ptr(),
-                                           b["g_max"].data_ptr(), b["g_mp"].data_ptr(), self.base.data_ptr(),
-                                           b["o_idx"].data_ptr(), b["o_cnt"].data_ptr(), b["o_max"].data_ptr(),
-                                           b["o_mp"].data_ptr()))
+            dist.all_gather_into_tensor(b["g_out"], b["out"])  # the one exchange of the step
+            g = b["g_out"]
+            w_idx, w_cnt = b["j"] * b["k"], b["j"]
+            base_ptr = g.data_ptr()
+            check(lib.dsm_merge_shards_strided_dev(
+                h, self.world, b["j"], b["k"], base_ptr, base_ptr + 4 * w_idx, base_ptr + 4 * (w_idx + w_cnt),
+                base_ptr + 4 * (b["words"] - 2 * b["j"]), 4 * b["words"], self.base.data_ptr(),
+                b["o_idx"].data_ptr(), b["o_cnt"].data_ptr(), b["o_max"].data_ptr(), b["o_mp"].data_ptr()))
 
     def result_in_source_space(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
         """(index [J,k] source positions, count [J], max_price [J]) of the last step, on every rank."""

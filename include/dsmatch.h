@@ -207,6 +207,15 @@ int dsm_merge_shards_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint3
                          const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
                          uint64_t* d_max_out, double* d_maxprice_out);
 
+/* Same merge when each shard's four result arrays travel in ONE all-gathered record (one
+ * collective per step instead of four): the pointers address shard 0's arrays and shard s's
+ * lie s * shard_stride_bytes further on. */
+int dsm_merge_shards_strided_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                                 const uint32_t* d_idx0, const uint32_t* d_cnt0, const uint32_t* d_max0,
+                                 const double* d_maxprice0, size_t shard_stride_bytes,
+                                 const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
+                                 uint64_t* d_max_out, double* d_maxprice_out);
+
 /* Gather price[row] for rows produced by dsm_match_topk_dev (DSM_NO_ROW -> NaN). */
 int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_rows, uint32_t n,
                          double* d_out);
