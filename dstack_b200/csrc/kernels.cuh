@@ -247,6 +247,8 @@ __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
         if (gflags & DSM_GPUF_CC_BOUNDED)                                      // item 10
           ok = ok && cc != 0xFFFFu && cc >= cc_min;
         ok = ok && tot >= (r2 & 0xFFFFu) && tot <= (r2 >> 16);                 // item 11
+        const uint32_t blocks = r4 >> 16, gpus_for_blocks = e2 >> 25;          // offers.py:102-118
+        if (blocks) ok = ok && (gpus_for_blocks % blocks == 0u);
       } else if (kind == DSM_COL_BK) {
         const uint32_t* ent = p.bk_entries + (size_t)e * DSM_BK_ENTRY_WORDS;
         const uint32_t e0 = ent[0], fl = ent[1];

@@ -241,7 +241,11 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True) -> Enc
     e_name = np.where(guniq[:, 3] >= 0, guniq[:, 3], 0xFFFF)
     gpu_entries[:, 0] = (guniq[:, 0] | (guniq[:, 1] << 16)).astype(np.uint32)
     gpu_entries[:, 1] = (tot_ord[rep] | (cc_ord[rep] << 16)).astype(np.uint32)
-    gpu_entries[:, 2] = (e_name | (guniq[:, 2] << 16) | (guniq[:, 4] << 24)).astype(np.uint32)
+    # bits 25..31: GPUs that count for block splitting (a TPU slice counts as one,
+    # server/services/offers.py:110-112), saturated at 127
+    e_count = cnt_vals[guniq[:, 0]].astype(np.int64)
+    e_eff = np.minimum(np.where(guniq[:, 2] == VENDOR_CODES["google"], np.minimum(e_count, 1), e_count), 127)
+    gpu_entries[:, 2] = (e_name | (guniq[:, 2] << 16) | (guniq[:, 4] << 24) | (e_eff << 25)).astype(np.uint32)
 
     # ---- backend / spot / status / flags dictionary (entry 0 = dead)
     sid = np.asarray(oc.shape_id, dtype=np.int64)
@@ -364,6 +368,8 @@ class JobColumns:
     zone_any: Optional[np.ndarray] = None
     zone_ptr: Optional[np.ndarray] = None
     zone_ids: Optional[np.ndarray] = None
+    # explicit block count per job: 0 = none, b > 1 = rows must split into b blocks, -1 = invalid count
+    blocks: Optional[np.ndarray] = None
 
 
 def _range_words(vals: np.ndarray, bounds: np.ndarray) -> np.ndarray:
@@ -456,7 +462,27 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
         trivial[-1] = bool(any_mask.all())
 
     c = t.col
-    add(_range_words(t.columns[c("cpu")].values, jc.cpu), KIND_RANGE, t.columns[c("cpu")].card)
+    # explicit block counts (offers.py:102-118): b > 1 keeps rows with cpu % b == 0 and gpus % b == 0,
+    # b < 0 stands for an invalid count (nothing is divisible); 0 = no block filter
+    blocks = np.zeros(j, dtype=np.int64) if jc.blocks is None else np.asarray(jc.blocks, dtype=np.int64)
+    if (blocks > 0xFFFF).any():
+        raise ValueError("block counts above 65535 are not supported")
+    if (blocks > 1).any() and len(t.gpu_entries) and int((t.gpu_entries[:, 2] >> 25).max()) >= 127:
+        raise ValueError("an instance with more than 126 GPUs cannot be matched against an explicit block count")
+    cpu_col = t.columns[c("cpu")]
+    if (blocks != 0).any():
+        # the cpu test becomes "in range and divisible": an irregular set, sent as a bitset
+        w = _range_words(cpu_col.values, jc.cpu)
+        e = np.arange(cpu_col.card, dtype=np.uint32)[None, :]
+        ok = (e >= (w & 0xFFFF)[:, None]) & (e <= (w >> 16)[:, None])
+        vals = cpu_col.values.astype(np.int64)[None, :]
+        ok &= np.where(blocks[:, None] > 1, vals % np.maximum(blocks, 1)[:, None] == 0, blocks[:, None] == 0)
+        bits = np.zeros((j, (cpu_col.card + 31) // 32), dtype=np.uint32)
+        jj, ee = np.nonzero(ok)
+        np.bitwise_or.at(bits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
+        add(bits, KIND_BITSET, cpu_col.card)
+    else:
+        add(_range_words(cpu_col.values, jc.cpu), KIND_RANGE, cpu_col.card)
     add(_range_words(t.columns[c("memory")].values, jc.memory), KIND_RANGE, t.columns[c("memory")].card)
     dcol = t.columns[c("disk")]
     add(_range_words(dcol.values, jc.disk), KIND_RANGE, dcol.card, COLF_NULL_PASSES)
@@ -480,7 +506,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
         _range_words(gd["memory"], gm)[:, None],
         _range_words(gd["total"], jc.gpu_total)[:, None],
         (np.minimum(cc_ord, 0xFFFE) | (gflags << np.uint32(16)))[:, None],
-        vmask[:, None],
+        (vmask | (np.where(blocks > 1, blocks, 0).astype(np.uint32) << np.uint32(16)))[:, None],
         name_bits,
     ], axis=1)
     add(gwords, KIND_GPU, t.columns[c("gpu")].card, ax=nwn)

@@ -191,6 +191,7 @@ class JobFilter:
     instance_types: Optional[Sequence[str]] = None
     exclude_not_available: bool = False
     require_auto_divisible: bool = False            # blocks="auto" (offers.py:102-118)
+    blocks: int = 0                                 # explicit block count: 0 none, b > 1, -1 invalid
     # pool rows
     status: Optional[Any] = None
     fleet_id: Any = None
@@ -222,6 +223,7 @@ def job_columns(table: EncodedTable, filters: Sequence[JobFilter]) -> JobColumns
     excl = np.zeros(j, bool)
     flag_req = np.zeros(j, np.uint16)
     flag_forbid = np.zeros(j, np.uint16)
+    blocks = np.zeros(j, np.int64)
     status_mask = np.full(j, 0xFF, np.uint8)
     fleet_any = np.ones(j, bool)
     fleet_ids = np.full(j, -1, np.int64)
@@ -279,6 +281,7 @@ def job_columns(table: EncodedTable, filters: Sequence[JobFilter]) -> JobColumns
         itype.put(i, f.instance_types)
         if f.require_auto_divisible:
             flag_req[i] |= FLAG_AUTO_DIVISIBLE
+        blocks[i] = f.blocks
         if f.shared is not None:  # pool filter (pools.py:460,484-488)
             flag_forbid[i] |= FLAG_UNREACHABLE | FLAG_BLOCKS_UNKNOWN
             if f.shared:
@@ -309,7 +312,7 @@ def job_columns(table: EncodedTable, filters: Sequence[JobFilter]) -> JobColumns
         gpu_name_ids=gn_ids, src_backend_mask=src_mask, off_backend_mask=off_mask,
         exclude_not_available=excl, region_any=r_any, region_ptr=r_ptr, region_ids=r_ids,
         itype_any=t_any, itype_ptr=t_ptr, itype_ids=t_ids, flag_req=flag_req, flag_forbid=flag_forbid,
-        status_mask=status_mask,
+        status_mask=status_mask, blocks=blocks if blocks.any() else None,
     )
     if table.is_pool:
         z_any, z_ptr, z_ids = zone.arrays()

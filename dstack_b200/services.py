@@ -200,12 +200,15 @@ def job_filter(profile: Any, requirements: Any, *, backend_types_of_project: Opt
     backend_types, regions = derive_backend_types_and_regions(
         p, multinode=multinode, master_job_provisioning_data=master_job_provisioning_data, volumes=volumes,
         privileged=privileged, instance_mounts=instance_mounts)
-    if blocks not in (1, "auto"):
-        raise NotImplementedError("explicit block counts are evaluated on the host path "
-                                  "(get_offers_by_requirements); the batched path takes 1 or 'auto'")
+    # blocks == 1 filters nothing; "auto" needs min(cpu, gpu) to divide both (a per-row flag);
+    # an explicit count b needs cpu % b == 0 and gpu % b == 0; b < 1 is never divisible
+    explicit = 0
+    if blocks != "auto" and blocks != 1:
+        explicit = int(blocks) if int(blocks) > 1 else -1
     return JobFilter(query=requirements_to_query_filter(requirements), backend_types=backend_types,
                      keep_dstack_backend=True, regions=regions, instance_types=profile.instance_types,
-                     exclude_not_available=exclude_not_available, require_auto_divisible=(blocks == "auto"))
+                     exclude_not_available=exclude_not_available, require_auto_divisible=(blocks == "auto"),
+                     blocks=explicit)
 
 
 class OfferCatalog:
@@ -246,9 +249,9 @@ class OfferCatalog:
         out = []
         for f, rows in zip(filters, hits):
             pairs = [(self.backends[i], self.offers[i]) for i in rows]
-            if f.require_auto_divisible:
+            if f.require_auto_divisible or f.blocks > 1:  # offers.py:116 writes the count back
                 for _, o in pairs:
-                    o.total_blocks = _blocks_of_offer(o, "auto")[1]
+                    o.total_blocks = _blocks_of_offer(o, "auto" if f.require_auto_divisible else f.blocks)[1]
             out.append(pairs)
         return out
 

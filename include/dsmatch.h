@@ -64,8 +64,9 @@ enum dsm_col_kind {
   DSM_COL_BITSET = 2,
   /* accelerator configuration dictionary, record = 5 + aux words:
    *   w0 count lo|hi<<16   w1 memory lo|hi<<16   w2 total-memory lo|hi<<16
-   *   w3 cc_min | flags<<16 (DSM_GPUF_*)   w4 vendor mask (bit = vendor code)
-   *   w5.. GPU-name bitset (aux words).  App. A.1 items 6-11. */
+   *   w3 cc_min | flags<<16 (DSM_GPUF_*)   w4 vendor mask (bit = vendor code) | blocks<<16
+   *   w5.. GPU-name bitset (aux words).  App. A.1 items 6-11; blocks != 0 also requires the
+   *   entry's GPU count to be divisible by it (server/services/offers.py:102-118). */
   DSM_COL_GPU = 3,
   /* backend/spot/status/flags dictionary, record = 4 words:
    *   w0 serving-backend mask  w1 offer-backend mask  w2 spot mask | status mask<<8
@@ -83,7 +84,8 @@ enum dsm_col_kind {
 /* Dictionary entry of a DSM_COL_GPU column (3 words, built by the host encoder):
  *   w0 count ordinal | memory ordinal<<16
  *   w1 total-memory ordinal | compute-capability ordinal<<16 (0xFFFF unknown)
- *   w2 name id (0xFFFF none) | vendor code<<16 | has_gpu<<24
+ *   w2 name id (0xFFFF none) | vendor code<<16 | has_gpu<<24 | GPUs counted for block
+ *      splitting<<25 (7 bits, saturated)
  * Dictionary entry of a DSM_COL_BK column (2 words):
  *   w0 serving backend | offer backend<<8 | spot<<16 | status<<24      w1 flags
  * Entry 0 of the DSM_COL_BK column is reserved as the dead entry: rows that carry it never

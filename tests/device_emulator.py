@@ -51,6 +51,8 @@ def acceptance(table: EncodedTable, packed: PackedJobs):
             cc_ok = (cc != 0xFFFF) & (cc >= cc_min)
             ok &= np.where((gflags & GPUF_CC_BOUNDED) != 0, cc_ok, True)
             ok &= (tot >= (r2 & 0xFFFF)) & (tot <= (r2 >> 16))
+            blocks, eff = (r4 >> 16).astype(np.int64), (ent[:, 2] >> 25).astype(np.int64)[None, :]
+            ok &= np.where(blocks > 0, eff % np.maximum(blocks, 1) == 0, True)
         elif kind == KIND_BK:
             ent = table.bk_entries.astype(np.uint64)
             src, offb = (ent[:, 0] & 0xFF)[None, :], ((ent[:, 0] >> 8) & 0xFF)[None, :]

@@ -51,3 +51,31 @@ def test_unsorted_backend_list_is_rejected():
     cat.columns.price[:2] = cat.columns.price[:2][::-1] + np.array([1.0, 0.0])
     with pytest.raises(ValueError, match="not sorted by price"):
         encode_table(cat.columns)
+
+
+@pytest.mark.parametrize("blocks", [2, 4, 3, 8, 0, "auto"])
+def test_block_counts_equal_reference(blocks):
+    """`blocks` of get_offers_by_requirements (server/services/offers.py:102-118): explicit counts
+    become a cpu bitset + a GPU-count divisibility test, "auto" a per-row flag."""
+    from dstack_b200 import models as M
+    from oracle import reference_path as ref
+
+    cat = synth.make_catalog(1500, seed=23, n_shapes=160)
+    per_backend = synth.catalog_objects(cat, filter_fn=ref.match_requirements)
+    backends = [b for b, _ in per_backend]
+    offers = [o for _, lst in per_backend for o in lst]
+    src = [b.TYPE for b, lst in per_backend for _ in lst]
+    table = encode_table(columns_from_offers(offers, src))
+    reqs = [M.Requirements(resources=M.ResourcesSpec(), max_price=None, spot=None),
+            M.Requirements(resources=M.ResourcesSpec(gpu="1..8"), max_price=None, spot=None),
+            M.Requirements(resources=M.ResourcesSpec(gpu="tpu:0..8", cpu="1.."), max_price=None, spot=None)]
+    filters = [job_filter(M.Profile(name="p"), r, blocks=blocks) for r in reqs]
+    m = emu.match_matrix(table, pack_jobs(table, job_columns(table, filters)))
+    pos = {id(o): i for i, o in enumerate(offers)}
+    seen = 0
+    for j, r in enumerate(reqs):
+        want = ref.get_offers_by_requirements(backends, M.Profile(name="p"), r, blocks=blocks)
+        got = [int(table.perm[row]) for row in np.flatnonzero(m[j])]
+        assert got == [pos[id(o)] for _, o in want], (blocks, j)
+        seen += len(want)
+    assert (seen > 0) == (blocks != 0)

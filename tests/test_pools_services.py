@@ -267,6 +267,8 @@ def test_gpu_offer_catalog_equals_oracle(matcher):
         dict(profile=M.Profile(name="p", reservation="cr-1"), requirements=DEFAULT_REQ),
         dict(profile=M.Profile(name="p"), requirements=DEFAULT_REQ, volumes=[[volume(BT.AWS, per_backend[0][1][0].region)]]),
         dict(profile=M.Profile(name="p"), requirements=gpu_req, blocks="auto"),
+        dict(profile=M.Profile(name="p"), requirements=gpu_req, blocks=2),
+        dict(profile=M.Profile(name="p"), requirements=DEFAULT_REQ, blocks=4),
         dict(profile=M.Profile(name="p", backends=[BT.DSTACK]), requirements=DEFAULT_REQ),
     ]
     try:
