@@ -154,6 +154,12 @@ class GpuCatalog:
             self._owner.append(pid)
         self._invalidate()
 
+    def add_csv(self, provider: str, text: str) -> None:
+        """One provider's CSV from gpuhunt's ``catalog.zip`` (see :mod:`dstack_b200.catalog_csv`)."""
+        from .catalog_csv import catalog_items_from_csv
+
+        self.add_items(provider, catalog_items_from_csv(text, provider))
+
     def _invalidate(self) -> None:
         if self._dt is not None:
             self._dt.close()
