@@ -386,10 +386,17 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
     except Exception:
         pass
     traffic = None
+    issue_fraction = None
     try:  # per-launch DRAM bytes of k_match from the committed ncu capture of this workload
         t = json.load(open(os.path.join(ROOT, "profiles", "k_match_traffic.json"))).get(wl["name"])
         if t and world == 1:
             traffic = int(t["dram_read_bytes"]) + int(t["dram_write_bytes"])
+            # warp instructions of one launch (same capture) against what the
+            # 4 schedulers of every SM can issue in the live launch time at the sampled clock
+            sm_mhz = (clock_info or {}).get("sm_mhz")
+            if t.get("warp_instructions") and sm_mhz:
+                sms = torch.cuda.get_device_properties(dev).multi_processor_count
+                issue_fraction = float(t["warp_instructions"]) / (match_ms * 1e-3 * sms * 4 * sm_mhz * 1e6)
     except Exception:
         pass
     groups = (J + 127) // 128
@@ -414,6 +421,7 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         "clocks": clock_info,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "kernel": "k_match",
+                     "hbm_fraction": achieved / hbm_peak, "issue_fraction": issue_fraction, "jobs_per_tile": 128,
                      "kernel_ms": match_ms, "kernel_share_of_step": match_ms / statistics.mean(step_ms),
                      "algorithmic_bytes_per_launch": int(alg_bytes), "peak_source": peaks_src,
                      "note": "k_match is bound by instruction issue and the LSU/shared-memory pipe, not HBM: "

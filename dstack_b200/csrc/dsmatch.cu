@@ -107,8 +107,9 @@ struct Plan {
   uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, grid;
 };
 
+// k = 0: bitmap mode (no per-slot logs, so nothing limits the number of pieces).
 static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, uint32_t n_jobs,
-                     Plan& pl) {
+                     uint32_t k, Plan& pl) {
   if (!L || L->n_used < 1 || L->n_used > t->desc.n_cols)
     return fail(DSM_E_ARG, "layout.n_used out of range");
   if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
@@ -163,6 +164,14 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   const uint32_t units_per_cta = env_units ? (uint32_t)atoi(env_units) : 4u;
   uint32_t want = (resident * (units_per_cta ? units_per_cta : 1u) + pl.n_groups - 1) / pl.n_groups;
   if (want < 1) want = 1;
+  if (k) {
+    // every (job, slot) owns k log entries of 8 bytes: keep the log of one call near 2 GiB by
+    // cutting the rows into fewer pieces when k or the batch is large
+    const unsigned long long per_slot = (unsigned long long)pl.n_groups * JPG * k * 8ull;
+    const unsigned long long max_slots = (2ull << 30) / per_slot;
+    const uint32_t cap = (uint32_t)(max_slots / MATCH_WARPS > 1 ? max_slots / MATCH_WARPS : 1);
+    if (want > cap) want = cap;
+  }
   const uint32_t a_blocks = pl.split_block, b_blocks = pl.n_blocks - pl.split_block;
   const uint32_t min_piece = MATCH_WARPS * 2u;
   auto pieces_for = [&](uint32_t blocks) -> uint32_t {
@@ -228,10 +237,10 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
                      uint32_t n_jobs, uint32_t k, bool bitmap, uint32_t* d_idx, uint32_t* d_cnt,
                      uint32_t* d_max, uint32_t* d_bits) {
   if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
-  Plan pl;
-  int rc = make_plan(ctx, t, L, n_jobs, pl);
-  if (rc) return rc;
   if (!bitmap && (k == 0 || k > 4096)) return fail(DSM_E_ARG, "k must be in 1..4096");
+  Plan pl;
+  int rc = make_plan(ctx, t, L, n_jobs, bitmap ? 0u : k, pl);
+  if (rc) return rc;
   if (!bitmap && (unsigned long long)pl.n_groups * JPG * pl.slots * k > 0xFFFFFFFFull)
     return fail(DSM_E_TOO_LARGE, "first-k log of this batch exceeds 2^32 entries; use fewer jobs per call or a smaller k");
   const bool row32 = t->desc.n_cols == 16;
@@ -321,7 +330,10 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     gp.out_idx = d_idx;
     gp.out_cnt = d_cnt;
     gp.out_max = d_max;
-    k_merge<<<(n_jobs + 7) / 8, 256, 0, ctx->stream>>>(gp);
+    // few slots per job: a warp per job; thousands (small batches): a CTA per job
+    const uint32_t chunk_bytes = (pl.slots + 31u) / 32u * 4u;
+    if (pl.slots >= 1024u) k_merge<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
+    else k_merge<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
     CK(cudaGetLastError());
     ctx->launches++;
   }
@@ -646,7 +658,7 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
   std::lock_guard<std::mutex> g(ctx->mu);
   Plan pl;
-  int rc = make_plan(ctx, t, layout, n_jobs, pl);  // pure arithmetic, allocates nothing
+  int rc = make_plan(ctx, t, layout, n_jobs, 0u, pl);  // pure arithmetic, allocates nothing
   if (rc) return rc;
   const bool row32 = t->desc.n_cols == 16;
   if (row32 && layout->n_used < 5) return fail(DSM_E_ARG, "16-column tables need n_used >= 5");
@@ -714,10 +726,10 @@ int dsm_debug_cta_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_ctas) 
 #endif
 
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, uint32_t n_jobs,
-                   uint32_t out[8]) {
+                   uint32_t k, uint32_t out[8]) {
   if (!ctx || !t || !layout || !out) return fail(DSM_E_ARG, "NULL argument");
   Plan pl;
-  int rc = make_plan(ctx, t, layout, n_jobs, pl);
+  int rc = make_plan(ctx, t, layout, n_jobs, k, pl);
   if (rc) return rc;
   out[0] = pl.grid;
   out[1] = pl.pc.count();

@@ -535,55 +535,115 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 }
 
 // ------------------------------------------------------------------------------------------
-// k_merge: one warp per job walks the job's slots in row order, 32 slots at a time.
+// k_merge: WPJ warps per job (1 when a job has few slots, 8 when a small batch was cut into
+// thousands of pieces).  Pass 1 sums the per-slot counts 32 slots ("a chunk") at a time, all
+// loads independent; pass 2 (one warp) prefix-sums the chunk totals and opens only the chunks
+// that hold some of the job's first k matches.
 // ------------------------------------------------------------------------------------------
 
+template <int WPJ>
 __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
+  constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
+  extern __shared__ uint32_t chunk_sums[];  // [JPC][n_chunks]
+  __shared__ uint32_t red_total[8];
+  __shared__ int red_last_a[8], red_last_b[8];
   const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t job = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (job >= p.n_jobs) return;
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t jl = warp / WPJ, wj = warp % WPJ;
+  const uint32_t job = blockIdx.x * JPC + jl;
+  const bool live = job < p.n_jobs;
   const uint32_t n_slots = p.slots;
-  const uint32_t* cnt = p.part_cnt + (size_t)job * p.slots;
-  const uint32_t* lst = p.part_last + (size_t)job * p.slots;
+  const uint32_t n_chunks = (n_slots + 31u) / 32u;
+  const uint32_t* cnt = p.part_cnt + (size_t)(live ? job : 0u) * p.slots;
+  const uint32_t* lst = p.part_last + (size_t)(live ? job : 0u) * p.slots;
+  uint32_t* csum = chunk_sums + jl * n_chunks;
+
+  {  // pass 1
+    uint32_t tot = 0;
+    int ls_a = -1, ls_b = -1;  // last slot with a match, per segment
+    for (uint32_t ch0 = wj; ch0 < n_chunks; ch0 += 4u * WPJ) {
+      uint32_t c[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t s = (ch0 + u * WPJ) * 32u + lane;
+        c[u] = (live && s < n_slots) ? cnt[s] : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t ch = ch0 + u * WPJ;
+        if (ch >= n_chunks) break;  // warp-uniform
+        const uint32_t s = ch * 32u + lane;
+        const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, c[u]);
+        const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c[u] != 0 && s < p.slots_a);
+        const uint32_t hit_b = __ballot_sync(0xFFFFFFFFu, c[u] != 0 && s >= p.slots_a);
+        if (hit_a) ls_a = (int)(ch * 32u + 31u - __clz(hit_a));
+        if (hit_b) ls_b = (int)(ch * 32u + 31u - __clz(hit_b));
+        if (lane == 0) csum[ch] = sum;
+        tot += sum;
+      }
+    }
+    if (lane == 0) { red_total[warp] = tot; red_last_a[warp] = ls_a; red_last_b[warp] = ls_b; }
+  }
+  __syncthreads();
+  if (!live || wj != 0) return;
+
   const uint2* log = p.part_log + (size_t)job * p.slots * p.k;
   uint32_t* out = p.out_idx + (size_t)job * p.k;
-
   uint32_t total = 0, have = 0;
   uint32_t last_a = DSM_NO_ROW, last_b = DSM_NO_ROW;
-  for (uint32_t s0 = 0; s0 < n_slots; s0 += 32) {
-    const uint32_t s = s0 + lane;
-    const uint32_t c = s < n_slots ? cnt[s] : 0u;
-    uint32_t incl = c;  // inclusive prefix sum over the 32 slots
+  {
+    int ls_a = -1, ls_b = -1;
+#pragma unroll
+    for (int w = 0; w < WPJ; ++w) {
+      total += red_total[jl * WPJ + w];
+      ls_a = max(ls_a, red_last_a[jl * WPJ + w]);
+      ls_b = max(ls_b, red_last_b[jl * WPJ + w]);
+    }
+    if (ls_a >= 0) last_a = lst[ls_a];  // last block with a match in that slot
+    if (ls_b >= 0) last_b = lst[ls_b];
+  }
+  // pass 2
+  for (uint32_t c0 = 0; c0 < n_chunks && have < p.k; c0 += 32) {
+    const uint32_t cs = c0 + lane < n_chunks ? csum[c0 + lane] : 0u;
+    uint32_t cincl = cs;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-      if (lane >= (uint32_t)d) incl += v;
+      const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, cincl, d);
+      if (lane >= (uint32_t)d) cincl += v;
     }
-    const uint32_t before = have + (incl - c);  // matches that precede this slot
-    if (c && before < p.k) {
-      // expand the slot's log of (block, match word) entries into rows, ascending
-      uint32_t take = min(c, p.k - before);
-      const uint2* src = log + (size_t)s * p.k;
-      uint32_t o = before;
-      for (uint32_t i = 0; take; ++i) {
-        const uint2 e = src[i];
-        uint32_t w = e.y;
-        while (w && take) {
-          out[o++] = e.x * 32u + (__ffs(w) - 1);
-          w &= w - 1;
-          --take;
+    const uint32_t cbefore = have + (cincl - cs);
+    uint32_t open = __ballot_sync(0xFFFFFFFFu, cs != 0 && cbefore < p.k);
+    while (open) {  // warp-uniform
+      const int src_lane = __ffs(open) - 1;
+      open &= open - 1;
+      const uint32_t base_have = __shfl_sync(0xFFFFFFFFu, cbefore, src_lane);
+      const uint32_t s = (c0 + src_lane) * 32u + lane;
+      const uint32_t c = s < n_slots ? cnt[s] : 0u;
+      uint32_t incl = c;  // inclusive prefix sum over the chunk's 32 slots
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+        if (lane >= (uint32_t)d) incl += v;
+      }
+      const uint32_t before = base_have + (incl - c);  // matches that precede this slot
+      if (c && before < p.k) {
+        // expand the slot's log of (block, match word) entries into rows, ascending
+        uint32_t take = min(c, p.k - before);
+        const uint2* src = log + (size_t)s * p.k;
+        uint32_t o = before;
+        for (uint32_t i = 0; take; ++i) {
+          const uint2 e = src[i];
+          uint32_t w = e.y;
+          while (w && take) {
+            out[o++] = e.x * 32u + (__ffs(w) - 1);
+            w &= w - 1;
+            --take;
+          }
         }
       }
     }
-    const bool seg_b = s >= p.slots_a;
-    const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c != 0 && !seg_b);
-    const uint32_t hit_b = __ballot_sync(0xFFFFFFFFu, c != 0 && seg_b);
-    const uint32_t l = c ? lst[s] : DSM_NO_ROW;  // last block with a match in this slot
-    if (hit_a) last_a = __shfl_sync(0xFFFFFFFFu, l, 31 - __clz(hit_a));
-    if (hit_b) last_b = __shfl_sync(0xFFFFFFFFu, l, 31 - __clz(hit_b));
-    const uint32_t sum = __shfl_sync(0xFFFFFFFFu, incl, 31);
-    total += sum;
-    have = min(p.k, have + sum);  // saturating: only used against k
+    const uint32_t sum = __shfl_sync(0xFFFFFFFFu, cincl, 31);
+    have = (sum >= p.k - have) ? p.k : have + sum;  // saturating: only used against k
   }
   for (uint32_t i = have + lane; i < p.k; i += 32) out[i] = DSM_NO_ROW;
 

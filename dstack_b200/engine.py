@@ -76,10 +76,12 @@ class Matcher:
             lut_ptrs[col] = out.value
         return native.make_layout(packed.layout, lut_ptrs)
 
-    def plan(self, dt: "DeviceTable", packed: PackedJobs) -> Dict[str, int]:
+    def plan(self, dt: "DeviceTable", packed: PackedJobs, k: int = 16) -> Dict[str, int]:
+        """Launch geometry the library would pick for this batch (``k=0``: bitmap mode)."""
         out = (C.c_uint32 * 8)()
         lay = native.make_layout(packed.layout)
-        native.check(self._lib.dsm_plan_query(self.handle, dt.handle, C.byref(lay), len(packed.records), C.byref(out)))
+        native.check(self._lib.dsm_plan_query(self.handle, dt.handle, C.byref(lay), len(packed.records), k,
+                                              C.byref(out)))
         keys = ["grid", "units", "pieces_a", "pieces_b", "slots", "smem", "entries", "groups"]
         return dict(zip(keys, [int(x) for x in out]))
 

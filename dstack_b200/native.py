@@ -84,7 +84,7 @@ def lib() -> C.CDLL:
     L.dsm_host_free.argtypes = [vp]
     L.dsm_timing_enable.argtypes = [vp, C.c_int]
     L.dsm_timing_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
-    L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, C.POINTER(u32 * 8)]
+    L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, u32, C.POINTER(u32 * 8)]
     for name in EXPORTS:
         fn = getattr(L, name)
         if name not in ("dsm_last_error", "dsm_build_info", "dsm_launch_count"):

@@ -235,9 +235,10 @@ uint64_t dsm_launch_count(const dsm_ctx* ctx);
  * the number of launches since the last read, and resets the counter. */
 int dsm_timing_enable(dsm_ctx* ctx, int on);
 int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches);
-/* Launch geometry chosen for a call: grid CTAs, work items, row ranges per job group, slots. */
+/* Launch geometry chosen for a call (k = 0: bitmap mode): grid CTAs, work items, row ranges per
+ * job group in the two segments, slots, shared memory, dictionary entries, job groups. */
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
-                   uint32_t n_jobs, uint32_t out[8]);
+                   uint32_t n_jobs, uint32_t k, uint32_t out[8]);
 
 #ifdef __cplusplus
 }

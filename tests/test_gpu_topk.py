@@ -41,6 +41,41 @@ def test_topk_ragged_sizes(matcher, n_offers, n_jobs):
     _check(matcher, cat, sj, 16)
 
 
+@pytest.mark.parametrize("n_jobs", [1, 5, 130])
+def test_small_batch_over_many_pieces(matcher, n_jobs):
+    """A scheduler tick: a handful of jobs against a large table is cut into thousands of row
+    pieces, which k_merge then walks with a whole CTA per job."""
+    cat = synth.make_catalog(400_000, seed=31, n_shapes=1024)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, n_jobs, seed=32)
+    dt = matcher.upload(table)
+    try:
+        assert matcher.plan(dt, pack_jobs(table, sj.columns), 50)["slots"] >= 1024
+    finally:
+        dt.close()
+    got = _check(matcher, cat, sj, 50)
+    if n_jobs >= 5:
+        assert ((got.count > 0) & (got.count < 50)).any() or (got.count >= 50).any()
+
+
+def test_large_k_uses_fewer_pieces_and_stays_exact(matcher):
+    """k = 2048 over 1024 jobs: the per-slot logs would not fit in 2 GiB with the usual number of
+    row pieces, so the plan cuts fewer; results stay those of the oracle."""
+    cat = synth.make_catalog(60_000, seed=41, n_shapes=256)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, 1024, seed=42)
+    dt = matcher.upload(table)
+    try:
+        packed = pack_jobs(table, sj.columns)
+        small, large = matcher.plan(dt, packed, 16), matcher.plan(dt, packed, 2048)
+        assert large["slots"] < small["slots"]
+        assert 1024 * large["slots"] * 2048 * 8 <= (2 << 30) + 2 * 8 * 1024 * 2048 * 8
+    finally:
+        dt.close()
+    got = _check(matcher, cat, sj, 2048)
+    assert (got.count > 2048).any()
+
+
 def test_bitmap_equals_oracle_matrix(matcher):
     cat = synth.make_catalog(20_000, seed=8, n_shapes=512)
     table = encode_table(cat.columns)
