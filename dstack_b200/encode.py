@@ -378,8 +378,9 @@ def _range_words(vals: np.ndarray, bounds: np.ndarray) -> np.ndarray:
     lo = first i with vals[i] >= min, hi = last i with vals[i] <= max: exactly the set the
     reference's ``not (v < min) and not (v > max)`` keeps.  Empty -> (1, 0)."""
     lo_b, hi_b = bounds[:, 0], bounds[:, 1]
-    lo = np.where(np.isnan(lo_b), 0, np.searchsorted(vals, np.nan_to_num(lo_b), side="left"))
-    hi = np.where(np.isnan(hi_b), len(vals) - 1, np.searchsorted(vals, np.nan_to_num(hi_b), side="right") - 1)
+    no_lo, no_hi = np.isnan(lo_b), np.isnan(hi_b)  # NaN = bound not set
+    lo = np.where(no_lo, 0, np.searchsorted(vals, np.where(no_lo, 0.0, lo_b), side="left"))
+    hi = np.where(no_hi, len(vals) - 1, np.searchsorted(vals, np.where(no_hi, 0.0, hi_b), side="right") - 1)
     empty = (lo > hi) | (len(vals) == 0)
     lo = np.where(empty, 1, lo).astype(np.uint32)
     hi = np.where(empty, 0, hi).astype(np.uint32)
@@ -422,8 +423,10 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
 
     # words 0,1: row cut-offs (max_price and exclude_not_available)
     mp = np.asarray(jc.max_price, dtype=np.float64)
-    cut_a = np.where(np.isnan(mp), t.split_row, np.searchsorted(t.price_a, np.nan_to_num(mp), side="right"))
-    cut_b = np.where(np.isnan(mp), t.n_rows, t.split_row + np.searchsorted(t.price_b, np.nan_to_num(mp), side="right"))
+    no_mp = np.isnan(mp)
+    mp0 = np.where(no_mp, 0.0, mp)
+    cut_a = np.where(no_mp, t.split_row, np.searchsorted(t.price_a, mp0, side="right"))
+    cut_b = np.where(no_mp, t.n_rows, t.split_row + np.searchsorted(t.price_b, mp0, side="right"))
     cut_b = np.where(np.asarray(jc.exclude_not_available, dtype=bool), t.split_row, cut_b)
     parts.append(np.stack([cut_a, cut_b], axis=1).astype(np.uint32))
     pos = 2
