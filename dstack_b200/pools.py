@@ -17,7 +17,7 @@ import numpy as np
 from . import models as M
 from .encode import EncodedTable, encode_table
 from .engine import DeviceTable, Matcher, default_matcher
-from .ingest import JobFilter, columns_from_pool_instances, job_columns
+from .ingest import JobFilter, PoolParseCache, columns_from_pool_instances, job_columns
 from .offers import requirements_to_query_filter
 from .services import generate_shared_offer
 
@@ -54,13 +54,16 @@ class PoolIndex:
     """Pool rows resident on the GPU.  Build once per scheduler tick, query for many jobs."""
 
     def __init__(self, pool_instances: Sequence[Any], *, matcher: Optional[Matcher] = None,
-                 offers: Optional[Sequence[Any]] = None):
+                 offers: Optional[Sequence[Any]] = None, parse_cache: Optional[PoolParseCache] = None):
+        """``parse_cache``: a :class:`~dstack_b200.ingest.PoolParseCache` kept by the caller across
+        ticks, so that only rows whose stored JSON changed are parsed again."""
         self.matcher = matcher or default_matcher()
         self.instances = list(pool_instances)
         self.table: Optional[EncodedTable] = None
         self.device_table: Optional[DeviceTable] = None
         if self.instances:
-            self.table = encode_table(columns_from_pool_instances(self.instances, offers=offers))
+            self.table = encode_table(columns_from_pool_instances(self.instances, offers=offers,
+                                                                  parse_cache=parse_cache))
             self.device_table = self.matcher.upload(self.table)
 
     def close(self) -> None:
@@ -97,9 +100,10 @@ def filter_pool_instances(
     volumes: Optional[List[List[Any]]] = None,
     shared: bool = False,
     matcher: Optional[Matcher] = None,
+    parse_cache: Optional[PoolParseCache] = None,
 ) -> List[Any]:
     """``server/services/pools.py:409-503``: matching rows, same objects, input order."""
-    index = PoolIndex(pool_instances, matcher=matcher)
+    index = PoolIndex(pool_instances, matcher=matcher, parse_cache=parse_cache)
     try:
         return index.filter(profile, requirements=requirements, status=status, fleet_model=fleet_model,
                             multinode=multinode, master_job_provisioning_data=master_job_provisioning_data,

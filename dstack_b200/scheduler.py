@@ -47,15 +47,17 @@ class Assignment:
 
 
 def assign_jobs_to_pool(pool_instances: Sequence[Any], jobs: Sequence[JobRequest], *,
-                        matcher: Optional[Matcher] = None, mutate: bool = True) -> List[Assignment]:
+                        matcher: Optional[Matcher] = None, mutate: bool = True,
+                        parse_cache: Optional[Any] = None) -> List[Assignment]:
     """Assign ``jobs`` (in order) to pool instances as the reference's per-job loop would.
 
     With ``mutate`` the chosen rows get ``status = BUSY`` and ``busy_blocks += blocks`` like
-    ``process_submitted_jobs.py:398-399``."""
+    ``process_submitted_jobs.py:398-399``.  ``parse_cache`` (a ``PoolParseCache`` kept by the
+    scheduler between ticks) spares re-parsing the stored JSON of unchanged instances."""
     rows = list(pool_instances)
     if not jobs:
         return []
-    unshared = PoolIndex(rows, matcher=matcher)
+    unshared = PoolIndex(rows, matcher=matcher, parse_cache=parse_cache)
     shared = SharedPoolIndex(rows, matcher=matcher)
     try:
         f_unshared = [_pool_filter(j.profile, requirements=j.requirements, status=M.InstanceStatus.IDLE,

@@ -257,3 +257,51 @@ class OfferCatalog:
 
     def pairs(self, index_row: np.ndarray) -> List[Tuple[Any, Any]]:
         return [(self.backends[i], self.offers[i]) for i in index_row if i >= 0]
+
+
+class OfferCatalogCache:
+    """An :class:`OfferCatalog` with the life time of the reference's offers cache.
+
+    The reference keeps each backend's offers for 30 s (``TTLCache(maxsize=10, ttl=30)`` around
+    ``get_offers_cached``, ``core/backends/base/compute.py:46-48,201-209``); the resident table
+    follows the same clock: ``get()`` returns the current catalog and rebuilds it from
+    ``fetch()`` -- ``[(backend, price-sorted offers), ...]`` -- on the first use after ``ttl``
+    seconds.  The previous table is freed once the new one is up.  Calls may come from several
+    threads (the reference fetches offers from a thread pool); a lock serialises rebuilds."""
+
+    def __init__(self, fetch, *, ttl: float = 30.0, matcher: Optional[Matcher] = None,
+                 clock=None, build=None):
+        import threading
+        import time
+
+        self._fetch = fetch
+        self.ttl = ttl
+        self._matcher = matcher
+        self._clock = clock or time.monotonic
+        self._build = build or (lambda offers_by_backend: OfferCatalog(offers_by_backend, matcher=self._matcher))
+        self._lock = threading.Lock()
+        self._catalog: Optional[Any] = None
+        self._born = 0.0
+        self.rebuilds = 0
+
+    def get(self) -> Any:
+        with self._lock:
+            now = self._clock()
+            if self._catalog is None or now - self._born >= self.ttl:
+                fresh = self._build(self._fetch())
+                old, self._catalog, self._born = self._catalog, fresh, now
+                self.rebuilds += 1
+                if old is not None:
+                    old.close()
+            return self._catalog
+
+    def invalidate(self) -> None:
+        """Force a rebuild on the next ``get()`` (e.g. after a backend was added or removed)."""
+        with self._lock:
+            self._born = -float("inf")
+
+    def close(self) -> None:
+        with self._lock:
+            if self._catalog is not None:
+                self._catalog.close()
+                self._catalog = None
