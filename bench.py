@@ -358,6 +358,11 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
             t = torch.tensor([mean_ms, e2e_mean, e2e_p50], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             mean_ms, e2e_mean, e2e_p50 = (float(x) for x in t.cpu())
+            per_rank = [torch.zeros(1, dtype=torch.float64, device=dev) for _ in range(world)]
+            dist.all_gather(per_rank, torch.tensor([match_ms], dtype=torch.float64, device=dev))
+            per_rank_match_ms = [float(x.item()) for x in per_rank]
+        else:
+            per_rank_match_ms = [match_ms]
 
         # ---- parity at full size (outside the timed regions)
         sm.step()
@@ -410,19 +415,21 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
         "config": {"workload": wl["workload"], "jobs": J, "offers": N, "k": k, "jobs_per_pass": 128,
                    "row_bytes": row_bytes, "rows_per_gpu": int(table.n_rows),
                    "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
-                   "parallelism": f"catalog sharded x{world} in result order, NCCL all_gather of per-shard top-k"
+                   "parallelism": f"catalog sharded x{world} (result order dealt out in 1024-row chunks), "
+                                  "one NCCL all_gather of per-shard top-k + k-way merge kernel"
                    if world > 1 else "1 GPU"},
         "e2e": {"value": evals / e2e_mean, "unit": UNIT, "h2d_bytes_per_step": int(J * rec_words * 4),
                 "d2h_bytes_per_step": int(J * (k + 2) * 4 if world == 1 else J * (k * 8 + 16)),
                 "p50_batch_latency_ms": 1e3 * e2e_p50,
                 "path": "dsm_match_topk (C ABI, pinned host buffers)" if world == 1 else
-                        "pinned H2D + dsm_match_topk_dev + NCCL all_gather + dsm_merge_shards_dev + D2H"},
+                        "pinned H2D + dsm_match_topk_dev + NCCL all_gather + dsm_merge_shards_interleaved_dev + D2H"},
         "gpu_launches": int(launches),
         "clocks": clock_info,
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "kernel": "k_match",
                      "hbm_fraction": achieved / hbm_peak, "issue_fraction": issue_fraction, "jobs_per_tile": 128,
                      "kernel_ms": match_ms, "kernel_share_of_step": match_ms / statistics.mean(step_ms),
+                     "kernel_ms_per_rank": per_rank_match_ms,
                      "algorithmic_bytes_per_launch": int(alg_bytes), "peak_source": peaks_src,
                      "note": "k_match is bound by instruction issue and the LSU/shared-memory pipe, not HBM: "
                              "128 jobs share every 16-byte row read (DESIGN.md section 3)"},

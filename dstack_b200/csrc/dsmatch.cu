@@ -558,6 +558,29 @@ int dsm_merge_shards_strided_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_job
                       d_shard_base, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
 }
 
+int dsm_merge_shards_interleaved_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                                     const uint32_t* d_idx0, const uint32_t* d_cnt0, const uint32_t* d_max0,
+                                     const double* d_maxprice0, size_t shard_stride_bytes,
+                                     const uint32_t* d_shard_geom, uint32_t chunk_rows,
+                                     uint64_t* d_idx_out, uint64_t* d_cnt_out, uint64_t* d_max_out,
+                                     double* d_maxprice_out) {
+  if (!ctx || !d_idx0 || !d_cnt0 || !d_max0 || !d_maxprice0 || !d_shard_geom || !d_idx_out || !d_cnt_out ||
+      !d_max_out || !d_maxprice_out)
+    return fail(DSM_E_ARG, "NULL argument");
+  if (n_shards == 0 || n_shards > 32) return fail(DSM_E_ARG, "interleaved merge takes 1..32 shards");
+  if (n_jobs == 0 || k == 0 || k > 255) return fail(DSM_E_ARG, "interleaved merge needs n_jobs > 0 and k in 1..255");
+  if (chunk_rows == 0) return fail(DSM_E_ARG, "chunk_rows must be > 0");
+  if (shard_stride_bytes == 0 || shard_stride_bytes % 8) return fail(DSM_E_ARG, "shard stride must be a non-zero multiple of 8");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  CK(cudaSetDevice(ctx->device));
+  k_merge_shards_interleaved<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
+      n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
+      reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
+  CK(cudaGetLastError());
+  ctx->launches++;
+  return 0;
+}
+
 int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_rows, uint32_t n,
                          double* d_out) {
   if (!ctx || !t || !d_rows || !d_out || n == 0) return fail(DSM_E_ARG, "bad argument");

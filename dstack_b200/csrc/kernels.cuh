@@ -741,3 +741,57 @@ __global__ void k_merge_shards(uint32_t n_shards, uint32_t n_jobs, uint32_t k,
   max_out[job] = best;
   maxprice_out[job] = (best == ~0ull) ? __longlong_as_double(0x7FF8000000000000LL) : best_price;
 }
+
+// Interleaved shards: the result order was dealt out to the shards in chunks of chunk_rows
+// positions (chunk c to shard c % n_shards), so a shard's first-k list is ascending in the
+// global order but the lists interleave.  geom[s] = (split_row, n_avail) of shard s turns a
+// physical row of that shard's table into its position in the shard's own order, and from there
+// into the global position; the merge keeps the k smallest positions.  Always strided input
+// (every pointer addresses shard 0's field).  One thread per job; n_shards <= 32.
+__global__ void k_merge_shards_interleaved(uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                                           const uint32_t* idx_all, const uint32_t* cnt_all,
+                                           const uint32_t* max_all, const double* maxprice_all,
+                                           size_t shard_stride_bytes, const uint2* geom,
+                                           uint32_t chunk_rows, uint64_t* idx_out, uint64_t* cnt_out,
+                                           uint64_t* max_out, double* maxprice_out) {
+  const uint32_t job = blockIdx.x * blockDim.x + threadIdx.x;
+  if (job >= n_jobs) return;
+  auto field = [&](const void* base, uint32_t s) {
+    return reinterpret_cast<const char*>(base) + (size_t)s * shard_stride_bytes;
+  };
+  auto position = [&](uint32_t s, uint32_t row) -> uint64_t {
+    const uint2 g = geom[s];
+    const uint64_t q = row < g.x ? row : (uint64_t)g.y + (row - g.x);
+    return ((q / chunk_rows) * n_shards + s) * chunk_rows + q % chunk_rows;
+  };
+  uint64_t head[32];  // global position of each shard's next unread entry, ~0 = exhausted
+  uint8_t used[32];
+  uint64_t total = 0, best = ~0ull;
+  double best_price = 0.0;
+  for (uint32_t s = 0; s < n_shards; ++s) {
+    const uint32_t* idx_s = reinterpret_cast<const uint32_t*>(field(idx_all, s)) + (size_t)job * k;
+    const uint32_t c = reinterpret_cast<const uint32_t*>(field(cnt_all, s))[job];
+    total += c;
+    used[s] = 0;
+    head[s] = (c != 0 && idx_s[0] != DSM_NO_ROW) ? position(s, idx_s[0]) : ~0ull;
+    const uint32_t m = reinterpret_cast<const uint32_t*>(field(max_all, s))[job];
+    if (m != DSM_NO_ROW) {
+      const double pr = reinterpret_cast<const double*>(field(maxprice_all, s))[job];
+      if (best == ~0ull || pr > best_price) { best = position(s, m); best_price = pr; }
+    }
+  }
+  for (uint32_t i = 0; i < k; ++i) {
+    uint32_t win = 0;
+    uint64_t lo = ~0ull;
+    for (uint32_t s = 0; s < n_shards; ++s)
+      if (head[s] < lo) { lo = head[s]; win = s; }
+    idx_out[(size_t)job * k + i] = lo;
+    if (lo == ~0ull) continue;
+    const uint32_t* idx_w = reinterpret_cast<const uint32_t*>(field(idx_all, win)) + (size_t)job * k;
+    const uint32_t nxt = ++used[win];
+    head[win] = (nxt < k && idx_w[nxt] != DSM_NO_ROW) ? position(win, idx_w[nxt]) : ~0ull;
+  }
+  cnt_out[job] = total;
+  max_out[job] = best;
+  maxprice_out[job] = (best == ~0ull) ? __longlong_as_double(0x7FF8000000000000LL) : best_price;
+}

@@ -25,6 +25,7 @@ EXPORTS = [
     "dsm_match_topk_dev", "dsm_match_bitmap_dev", "dsm_merge_shards_dev", "dsm_gather_price_dev",
     "dsm_sync", "dsm_host_alloc", "dsm_host_free", "dsm_launch_count", "dsm_plan_query",
     "dsm_timing_enable", "dsm_timing_read", "dsm_match_bitmap_static", "dsm_merge_shards_strided_dev",
+    "dsm_merge_shards_interleaved_dev",
 ]
 STATIC_SCRATCH_BYTES = 2 << 20  # DSM_STATIC_SCRATCH_BYTES
 
@@ -78,6 +79,8 @@ def lib() -> C.CDLL:
     L.dsm_match_bitmap_static.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp]
     L.dsm_merge_shards_dev.argtypes = [vp, u32, u32, u32, vp, vp, vp, vp, vp, vp, vp, vp, vp]
     L.dsm_merge_shards_strided_dev.argtypes = [vp, u32, u32, u32, vp, vp, vp, vp, C.c_size_t, vp, vp, vp, vp, vp]
+    L.dsm_merge_shards_interleaved_dev.argtypes = [vp, u32, u32, u32, vp, vp, vp, vp, C.c_size_t, vp, u32,
+                                                   vp, vp, vp, vp]
     L.dsm_gather_price_dev.argtypes = [vp, vp, vp, u32, vp]
     L.dsm_sync.argtypes = [vp]
     L.dsm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]

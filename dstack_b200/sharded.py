@@ -4,9 +4,11 @@ Rank r holds a contiguous range of the global result order (stable sort of the s
 ``(not available, price)``, the order ``server/services/backends/__init__.py:449-451``
 produces) as its own device table with its own dictionaries; job records are replicated.  A
 step is: local ``dsm_match_topk_dev`` -> ``dsm_gather_price_dev`` -> ONE ``all_gather`` of a per-shard
-record (first-k rows, counts, max rows and their prices) -> ``dsm_merge_shards_strided_dev``.  Because
-shards are in result order the merge is a concatenation and the total order is the *global
-physical row* ``shard_base[s] + local row``.
+record (first-k rows, counts, max rows and their prices) -> a merge kernel.  By default the result
+order is dealt out to the ranks in chunks of 1024 positions (``dsm_merge_shards_interleaved_dev`` keeps
+the k smallest global positions), which balances the ranks; with ``chunk_rows=0`` every rank holds
+one contiguous range, the merge is a concatenation (``dsm_merge_shards_strided_dev``) and the total
+order is the *global physical row* ``shard_base[s] + local row``.
 
 The helpers at the top are pure numpy (used by the CPU ``gloo`` tests as well); the device path
 is :class:`ShardedMatcher`.
@@ -28,12 +30,32 @@ def rank_order(oc: OfferColumns) -> np.ndarray:
     return np.lexsort((np.asarray(oc.price, dtype=np.float64), ~np.asarray(oc.available, dtype=bool)))
 
 
-def shard_positions(order: np.ndarray, rank: int, world: int) -> np.ndarray:
-    """Source positions (ascending) of the offers rank ``rank`` owns: the ``rank``-th of ``world``
-    equal contiguous ranges of the result order."""
+def shard_positions(order: np.ndarray, rank: int, world: int, chunk_rows: int = 0) -> np.ndarray:
+    """Source positions (ascending) of the offers rank ``rank`` owns.
+
+    ``chunk_rows == 0``: the ``rank``-th of ``world`` equal contiguous ranges of the result order.
+    ``chunk_rows > 0``: the result order is dealt out in chunks of that many positions, chunk ``c``
+    to rank ``c % world``, so every shard sees the same mix of cheap and expensive rows and the
+    ranks finish together (a contiguous split left one rank of four 7 % behind the others)."""
     n = len(order)
+    if chunk_rows > 0:
+        p = np.arange(n)
+        return np.sort(order[(p // chunk_rows) % world == rank])
     lo, hi = rank * n // world, (rank + 1) * n // world
     return np.sort(order[lo:hi])
+
+
+def local_rows_to_positions(rows: np.ndarray, split_row: int, n_avail: int, rank: int, world: int,
+                            chunk_rows: int) -> np.ndarray:
+    """Physical rows of an interleaved shard's table -> positions in the global result order
+    (``NO_ROW`` / negative stay "none" = -1).  A shard's table keeps its rows in result order with
+    the first segment padded to ``split_row``; its ``q``-th row is the global position
+    ``((q // chunk) * world + rank) * chunk + q % chunk``."""
+    r = np.asarray(rows).astype(np.int64)
+    none = (r < 0) | (r == NO_ROW)
+    q = np.where(r < split_row, r, n_avail + (r - split_row))
+    p = ((q // chunk_rows) * world + rank) * chunk_rows + q % chunk_rows
+    return np.where(none, -1, p)
 
 
 def subset_columns(oc: OfferColumns, idx: np.ndarray) -> OfferColumns:
@@ -66,7 +88,10 @@ def global_rows_to_source(global_rows: np.ndarray, bases: np.ndarray, perms: Seq
 class ShardedMatcher:
     """Device path.  ``torch`` supplies device memory, the stream and the process group only."""
 
-    def __init__(self, full: OfferColumns, *, rank: int, world: int, device: int, order: Optional[np.ndarray] = None):
+    def __init__(self, full: OfferColumns, *, rank: int, world: int, device: int, order: Optional[np.ndarray] = None,
+                 chunk_rows: int = 1024):
+        """``chunk_rows > 0`` deals the result order out in chunks (balanced shards, the default);
+        ``0`` gives every rank one contiguous range."""
         import torch
         import torch.distributed as dist
 
@@ -77,7 +102,8 @@ class ShardedMatcher:
         self.rank, self.world = rank, world
         self.dev = torch.device("cuda", device)
         self.order = rank_order(full) if order is None else order
-        self.positions = shard_positions(self.order, rank, world) if world > 1 else None
+        self.chunk_rows = chunk_rows
+        self.positions = shard_positions(self.order, rank, world, chunk_rows) if world > 1 else None
         cols = subset_columns(full, self.positions) if world > 1 else full
         self.table: EncodedTable = encode_table(cols)
         self.stream = torch.cuda.Stream(device=self.dev)
@@ -89,6 +115,9 @@ class ShardedMatcher:
                 all_sizes = torch.empty((world,), dtype=torch.int64, device=self.dev)
                 dist.all_gather_into_tensor(all_sizes, sizes)
                 self.base = torch.cumsum(all_sizes, 0) - all_sizes
+                geom = torch.tensor([self.table.split_row, self.table.n_avail], dtype=torch.int32, device=self.dev)
+                self.geom = torch.empty((world, 2), dtype=torch.int32, device=self.dev)
+                dist.all_gather_into_tensor(self.geom, geom)
         self._bufs = None
 
     def pack(self, jobs: JobColumns) -> PackedJobs:
@@ -136,10 +165,15 @@ class ShardedMatcher:
             g = b["g_out"]
             w_idx, w_cnt = b["j"] * b["k"], b["j"]
             base_ptr = g.data_ptr()
-            check(lib.dsm_merge_shards_strided_dev(
-                h, self.world, b["j"], b["k"], base_ptr, base_ptr + 4 * w_idx, base_ptr + 4 * (w_idx + w_cnt),
-                base_ptr + 4 * (b["words"] - 2 * b["j"]), 4 * b["words"], self.base.data_ptr(),
-                b["o_idx"].data_ptr(), b["o_cnt"].data_ptr(), b["o_max"].data_ptr(), b["o_mp"].data_ptr()))
+            fields = (base_ptr, base_ptr + 4 * w_idx, base_ptr + 4 * (w_idx + w_cnt),
+                      base_ptr + 4 * (b["words"] - 2 * b["j"]), 4 * b["words"])
+            outs = (b["o_idx"].data_ptr(), b["o_cnt"].data_ptr(), b["o_max"].data_ptr(), b["o_mp"].data_ptr())
+            if self.chunk_rows > 0:
+                check(lib.dsm_merge_shards_interleaved_dev(h, self.world, b["j"], b["k"], *fields,
+                                                           self.geom.data_ptr(), self.chunk_rows, *outs))
+            else:
+                check(lib.dsm_merge_shards_strided_dev(h, self.world, b["j"], b["k"], *fields,
+                                                       self.base.data_ptr(), *outs))
 
     def result_in_source_space(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
         """(index [J,k] source positions, count [J], max_price [J]) of the last step, on every rank."""
@@ -152,6 +186,10 @@ class ShardedMatcher:
             mx = b["max"].cpu().numpy().view(np.uint32)
             price = np.where(mx == NO_ROW, np.nan, t.price[np.minimum(mx, t.n_rows - 1)])
             return src, cnt, price
+        if self.chunk_rows > 0:  # merged indices are positions in the global result order
+            pos = b["o_idx"].cpu().numpy()
+            src = np.where(pos < 0, -1, self.order[np.clip(pos, 0, len(self.order) - 1)]).astype(np.int64)
+            return src, b["o_cnt"].cpu().numpy(), b["o_mp"].cpu().numpy()
         gathered: List[Any] = [None] * self.world
         self.dist.all_gather_object(gathered, (self.positions, t.perm))
         bases = self.base.cpu().numpy()

@@ -218,6 +218,19 @@ int dsm_merge_shards_strided_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_job
                                  const uint64_t* d_shard_base, uint64_t* d_idx_out, uint64_t* d_cnt_out,
                                  uint64_t* d_max_out, double* d_maxprice_out);
 
+/* Merge for shards that were dealt the result order in chunks: position p of the global order
+ * belongs to shard (p / chunk_rows) % n_shards, so all shards see the same price mix and finish
+ * together.  d_shard_geom = [n_shards][2] u32: split_row and number of live first-segment rows
+ * (n_avail) of every shard's table.  Outputs are positions in the global result order (not
+ * physical rows): the k smallest over all shards, ~0 = none.  Strided input as above;
+ * n_shards <= 32, k <= 255.  Like the other merges this has no counterpart in the reference. */
+int dsm_merge_shards_interleaved_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32_t k,
+                                     const uint32_t* d_idx0, const uint32_t* d_cnt0, const uint32_t* d_max0,
+                                     const double* d_maxprice0, size_t shard_stride_bytes,
+                                     const uint32_t* d_shard_geom, uint32_t chunk_rows,
+                                     uint64_t* d_idx_out, uint64_t* d_cnt_out, uint64_t* d_max_out,
+                                     double* d_maxprice_out);
+
 /* Gather price[row] for rows produced by dsm_match_topk_dev (DSM_NO_ROW -> NaN). */
 int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_rows, uint32_t n,
                          double* d_out);

@@ -131,3 +131,31 @@ def merge_shards(idx_all, cnt_all, max_all, maxprice_all, bases, k):
                 if max_out[job] < 0 or pr > mp_out[job]:
                     max_out[job], mp_out[job] = bases[s] + m, pr
     return idx_out, cnt_out, max_out, mp_out
+
+
+def merge_shards_interleaved(idx_all, cnt_all, max_all, maxprice_all, geom, chunk_rows, k):
+    """What k_merge_shards_interleaved computes: shard s was dealt chunks s, s+G, ... of the
+    result order; geom[s] = (split_row, n_avail) turns its physical rows into global positions;
+    the k smallest positions over all shards are kept.  Positions out, -1 = none."""
+    from dstack_b200.sharded import local_rows_to_positions
+
+    n_shards, j = cnt_all.shape
+    idx_out = np.full((j, k), -1, dtype=np.int64)
+    cnt_out = cnt_all.astype(np.int64).sum(axis=0)
+    max_out = np.full(j, -1, dtype=np.int64)
+    mp_out = np.full(j, np.nan)
+    pos = np.stack([local_rows_to_positions(idx_all[s], int(geom[s][0]), int(geom[s][1]), s, n_shards, chunk_rows)
+                    for s in range(n_shards)])  # [G, J, k]
+    for job in range(j):
+        cand = pos[:, job, :].reshape(-1)
+        cand = np.sort(cand[cand >= 0])[:k]
+        idx_out[job, :len(cand)] = cand
+        for s in range(n_shards):
+            m = int(max_all[s, job])
+            if m != NO_ROW and m >= 0:
+                pr = float(maxprice_all[s, job])
+                if max_out[job] < 0 or pr > mp_out[job]:
+                    max_out[job] = local_rows_to_positions(np.array([m]), int(geom[s][0]), int(geom[s][1]), s,
+                                                           n_shards, chunk_rows)[0]
+                    mp_out[job] = pr
+    return idx_out, cnt_out, max_out, mp_out

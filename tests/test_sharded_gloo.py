@@ -2,7 +2,7 @@
 
 The device steps (dsm_match_topk_dev, dsm_merge_shards_dev) are replaced by their numpy
 emulation from tests/device_emulator.py; what is exercised for real is everything around them:
-the split of the result order into contiguous shards, per-shard tables with their own
+the split of the result order into contiguous or chunk-interleaved shards, per-shard tables with their own
 dictionaries, job packing per shard, the all-gather, shard bases and the mapping of global rows
 back to source positions.  The merged answer must equal the oracle's on the unsharded catalog.
 """
@@ -20,7 +20,7 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _worker(rank, world, port, n_offers, n_jobs, k, out):
+def _worker(rank, world, port, n_offers, n_jobs, k, chunk_rows, out):
     import sys
 
     here = os.path.dirname(os.path.abspath(__file__))
@@ -42,7 +42,7 @@ def _worker(rank, world, port, n_offers, n_jobs, k, out):
         cat = synth.make_catalog(n_offers, seed=17, n_shapes=128)
         full = cat.columns
         order = sharded.rank_order(full)
-        mine = sharded.shard_positions(order, rank, world)
+        mine = sharded.shard_positions(order, rank, world, chunk_rows)
         table = encode_table(sharded.subset_columns(full, mine))
         sj = synth.make_jobs(cat, table, n_jobs, seed=18)      # ids are valid for every shard
         idx, cnt, mx = emu.topk(table, pack_jobs(table, sj.columns), k)
@@ -60,8 +60,13 @@ def _worker(rank, world, port, n_offers, n_jobs, k, out):
         bases = sharded.shard_bases(sizes)
         meta = [None] * world
         dist.all_gather_object(meta, (mine, table.perm))
-        o_idx, o_cnt, o_max, o_mp = emu.merge_shards(g_idx, g_cnt, g_max, g_mp, bases, k)
-        src = sharded.global_rows_to_source(o_idx, bases, [m[1] for m in meta], [m[0] for m in meta])
+        if chunk_rows:
+            geom = gather(np.array([table.split_row, table.n_avail], dtype=np.int64))
+            o_idx, o_cnt, o_max, o_mp = emu.merge_shards_interleaved(g_idx, g_cnt, g_max, g_mp, geom, chunk_rows, k)
+            src = np.where(o_idx < 0, -1, order[np.maximum(o_idx, 0)])
+        else:
+            o_idx, o_cnt, o_max, o_mp = emu.merge_shards(g_idx, g_cnt, g_max, g_mp, bases, k)
+            src = sharded.global_rows_to_source(o_idx, bases, [m[1] for m in meta], [m[0] for m in meta])
 
         want = columnar.topk(full, sj.columns, k, order=order)
         assert np.array_equal(o_cnt, want.count)
@@ -71,20 +76,23 @@ def _worker(rank, world, port, n_offers, n_jobs, k, out):
         assert sum(len(m[0]) for m in meta) == n_offers
         rank_of = np.empty(n_offers, np.int64)
         rank_of[order] = np.arange(n_offers)
-        if rank + 1 < world:
+        if chunk_rows:  # chunk c of the result order belongs to rank c % world
+            assert ((rank_of[mine] // chunk_rows) % world == rank).all()
+        elif rank + 1 < world:
             assert rank_of[meta[rank][0]].max() < rank_of[meta[rank + 1][0]].min()
         out[rank] = int(want.count.sum())
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("n_offers,n_jobs,k", [(3000, 40, 16), (257, 9, 50)])
-def test_two_rank_sharded_merge_equals_unsharded_oracle(n_offers, n_jobs, k):
+@pytest.mark.parametrize("n_offers,n_jobs,k,chunk_rows", [(3000, 40, 16, 0), (257, 9, 50, 0),
+                                                          (3000, 40, 16, 64), (1000, 9, 50, 7), (257, 5, 16, 1024)])
+def test_two_rank_sharded_merge_equals_unsharded_oracle(n_offers, n_jobs, k, chunk_rows):
     import torch.multiprocessing as mp
 
     world = 2
     port = _free_port()
     with mp.Manager() as manager:
         out = manager.dict()
-        mp.spawn(_worker, args=(world, port, n_offers, n_jobs, k, out), nprocs=world, join=True)
+        mp.spawn(_worker, args=(world, port, n_offers, n_jobs, k, chunk_rows, out), nprocs=world, join=True)
         assert len(out) == world and out[0] == out[1] and out[0] > 0
