@@ -82,7 +82,7 @@ struct dsm_ctx {
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
   size_t timing_used = 0;
-  DevBuf tabs, counter, part_cnt, part_last, part_log, d_jobs, d_idx, d_cnt, d_max, d_bits;
+  DevBuf tabs, counter, part_cnt, part_last, part_log, win_rows, d_jobs, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
 };
 
@@ -192,29 +192,35 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   return 0;
 }
 
-template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT, bool REP8>
+template <int NC, bool ROW32, int MODE, bool HAS_LUT, bool REP8>
 static cudaError_t launch_match_v(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(k_match<NC, ROW32, BITMAP, HAS_LUT, REP8>,
+  cudaError_t e = cudaFuncSetAttribute(k_match<NC, ROW32, MODE, HAS_LUT, REP8>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  k_match<NC, ROW32, BITMAP, HAS_LUT, REP8><<<grid, MATCH_THREADS, smem, st>>>(mp);
+  k_match<NC, ROW32, MODE, HAS_LUT, REP8><<<grid, MATCH_THREADS, smem, st>>>(mp);
   return cudaGetLastError();
 }
 
-template <int NC, bool ROW32, bool BITMAP>
+template <int NC, bool ROW32, int MODE>
 static cudaError_t launch_match_nc(const MatchParams& mp, bool has_lut, uint32_t grid, uint32_t smem,
                                    cudaStream_t st) {
   const bool rep8 = mp.rep_shift == 3u;
-  if (has_lut) return rep8 ? launch_match_v<NC, ROW32, BITMAP, true, true>(mp, grid, smem, st)
-                           : launch_match_v<NC, ROW32, BITMAP, true, false>(mp, grid, smem, st);
-  return rep8 ? launch_match_v<NC, ROW32, BITMAP, false, true>(mp, grid, smem, st)
-              : launch_match_v<NC, ROW32, BITMAP, false, false>(mp, grid, smem, st);
+  if (has_lut) return rep8 ? launch_match_v<NC, ROW32, MODE, true, true>(mp, grid, smem, st)
+                           : launch_match_v<NC, ROW32, MODE, true, false>(mp, grid, smem, st);
+  return rep8 ? launch_match_v<NC, ROW32, MODE, false, true>(mp, grid, smem, st)
+              : launch_match_v<NC, ROW32, MODE, false, false>(mp, grid, smem, st);
 }
 
-template <bool BITMAP>
+template <int MODE>
 static cudaError_t launch_match(uint32_t nc, bool row32, const MatchParams& mp, bool has_lut,
                                 uint32_t grid, uint32_t smem, cudaStream_t st) {
-#define CASE_NC(n, r) case n: return launch_match_nc<n, r, BITMAP>(mp, has_lut, grid, smem, st);
+#define CASE_NC(n, r) case n: return launch_match_nc<n, r, MODE>(mp, has_lut, grid, smem, st);
+#ifdef DSM_FAST_BUILD  // experiments: only the shapes the benchmark uses
+  if (!row32) {
+    switch (nc) { CASE_NC(5, false) CASE_NC(6, false) }
+  }
+  return cudaErrorInvalidValue;
+#endif
   if (!row32) {
     switch (nc) {
       CASE_NC(1, false) CASE_NC(2, false) CASE_NC(3, false) CASE_NC(4, false)
@@ -303,14 +309,32 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     tev = &ctx->timing_events[ctx->timing_used++];
     CK(cudaEventRecord(tev->first, ctx->stream));
   }
-  cudaError_t e = bitmap ? launch_match<true>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
-                         : launch_match<false>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  const bool count_mode = !bitmap && getenv("DSM_LOG_MODE") == nullptr;  // DSM_LOG_MODE: the older path, for A/B
+  if (count_mode) {
+    // windows per slot: the longest warp range of any piece, in windows
+    uint32_t longest = 0;
+    for (uint32_t pos = 0; pos < pl.pc.per_group(); ++pos) {
+      uint32_t lo, hi;
+      pl.pc.blocks_of(pos, lo, hi);
+      const uint32_t per_warp = (hi - lo + MATCH_WARPS - 1) / MATCH_WARPS + 1;
+      if (per_warp > longest) longest = per_warp;
+    }
+    mp.wps = (longest + WIN_BLOCKS - 1) / WIN_BLOCKS;
+    if ((rc = ensure(ctx->win_rows, (size_t)pl.n_groups * pl.slots * mp.wps * JPG * 4))) return rc;
+    mp.win_rows = (uint32_t*)ctx->win_rows.p;
+  }
+  cudaError_t e = bitmap ? launch_match<MODE_BITMAP>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
+                  : count_mode ? launch_match<MODE_COUNT>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
+                         : launch_match<MODE_LOG>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   if (tev) CK(cudaEventRecord(tev->second, ctx->stream));
   ctx->launches++;
 
   if (!bitmap) {
     MergeParams gp;
+    gp.pc = pl.pc;
+    gp.win_rows = mp.win_rows;
+    gp.wps = mp.wps;
     gp.part_cnt = mp.part_cnt;
     gp.part_last = mp.part_last;
     gp.part_log = mp.part_log;
@@ -332,7 +356,10 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     gp.out_max = d_max;
     // few slots per job: a warp per job; thousands (small batches): a CTA per job
     const uint32_t chunk_bytes = (pl.slots + 31u) / 32u * 4u;
-    if (pl.slots >= 1024u) k_merge<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
+    if (count_mode) {
+      if (pl.slots >= 1024u) k_extract<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
+      else k_extract<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
+    } else if (pl.slots >= 1024u) k_merge<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
     else k_merge<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
     CK(cudaGetLastError());
     ctx->launches++;
@@ -377,7 +404,7 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->part_last, &ctx->part_log, &ctx->d_jobs,
+  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->part_last, &ctx->part_log, &ctx->win_rows, &ctx->d_jobs,
                     &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);
@@ -732,7 +759,7 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   mp.slots = pl.slots;
   mp.work_counter = bp.work_counter;
   mp.bits = d_bits;
-  cudaError_t e = launch_match<true>(layout->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  cudaError_t e = launch_match<MODE_BITMAP>(layout->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   ctx->launches++;
   return 0;

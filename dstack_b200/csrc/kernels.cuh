@@ -175,7 +175,19 @@ struct MatchParams {
   uint32_t* part_last;   // [jobs_pad][slots]: last 32-row block with a match (DSM_NO_ROW: none)
   uint2* part_log;       // [jobs_pad][slots][k] x (block, match word)
   uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
+  uint32_t* win_rows;    // count mode: [groups][slots][wps][128]: per window of WIN_BLOCKS blocks and job,
+                         // the row lanes (row mod 32) with at least one match
+  uint32_t wps;          // count mode: windows reserved per slot
 };
+
+// k_match modes
+#define MODE_LOG 0     // count + first-k log + last block per slot (k_merge finishes the job)
+#define MODE_BITMAP 1  // every match word, job-major
+#define MODE_COUNT 2   // counts per window only; k_extract re-evaluates the few windows it needs
+// count mode: a 4-bit vertical counter per (row lane, job bit) holds up to 15 blocks
+#define WIN_PLANES 4
+#define WIN_BLOCKS 15
+#define EXTRACT_BATCH 5  // blocks k_extract evaluates at a time (their loads overlap)
 
 struct MergeParams {
   const uint32_t* part_cnt;
@@ -194,6 +206,10 @@ struct MergeParams {
   uint32_t* out_idx;
   uint32_t* out_cnt;
   uint32_t* out_max;
+  // k_extract: the pieces k_match worked on (slot -> block range) and its per-window counts
+  Pieces pc;
+  const uint32_t* win_rows;
+  uint32_t wps;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -298,8 +314,10 @@ __device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCod
   }
 }
 
-template <int NC, bool ROW32, bool BITMAP, bool HAS_LUT, bool REP8>
+template <int NC, bool ROW32, int MODE, bool HAS_LUT, bool REP8>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
+  constexpr bool BITMAP = MODE == MODE_BITMAP;
+  constexpr bool COUNT = MODE == MODE_COUNT;
   // shared memory: [staging: E entries][table: E entries x R copies][cut-offs: 2 x 128]
   // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
   // R = 8 copy r lies in bank group r (4 banks), lane l reads copy l%8, and the 8 lanes of every
@@ -404,6 +422,29 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       lidx[t] = ((group * JPG + t * 32 + lane) * p.slots + slot) * kk;
     }
 
+    // count mode: vertical match counters of the current window and the window's number
+    uint32_t pln[TPG][WIN_PLANES];
+    uint32_t in_win = 0, widx = 0;
+#pragma unroll
+    for (int t = 0; t < TPG; ++t)
+#pragma unroll
+      for (int b = 0; b < WIN_PLANES; ++b) pln[t][b] = 0;
+
+    // four independent 32x32 bit transposes, interleaved step by step so the shuffles overlap
+    auto xpose4 = [&](uint32_t (&T)[TPG]) {
+#pragma unroll
+      for (int i = 0; i < 5; ++i) {
+        uint32_t y[TPG];
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(0xFFFFFFFFu, T[t], 16u >> i);
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
+          T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
+        }
+      }
+    };
+
     auto process = [&](const uint32_t blk, const RowCodes<NC>& cur) {
       uint4 m;
       if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
@@ -440,20 +481,53 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
       }
 
+      if constexpr (COUNT) {
+        // add this block's match bits into the vertical counters: pln[t][b] is bit b of a
+        // counter kept per (row lane, job bit); no cross-lane traffic until the window ends
+        const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+        for (int t = 0; t < TPG; ++t) {
+          uint32_t carry = mm[t];
+#pragma unroll
+          for (int b = 0; b < WIN_PLANES; ++b) {
+            const uint32_t up = pln[t][b] & carry;
+            pln[t][b] ^= carry;
+            carry = up;
+          }
+        }
+        if (++in_win == WIN_BLOCKS || blk + 1 == b1) {  // warp-uniform: the window is complete
+          // after the transposes lane j holds, per plane, which row lanes have that counter bit
+          // set for job 32t+j: popcounts give the window's matches, the OR of the planes the
+          // row lanes (row mod 32) that matched at all -- k_extract looks only at those rows
+          uint32_t c[TPG] = {0, 0, 0, 0}, any[TPG] = {0, 0, 0, 0};
+#pragma unroll
+          for (int b = 0; b < WIN_PLANES; ++b) {
+            uint32_t T[TPG];
+#pragma unroll
+            for (int t = 0; t < TPG; ++t) { T[t] = pln[t][b]; pln[t][b] = 0; }
+            xpose4(T);
+#pragma unroll
+            for (int t = 0; t < TPG; ++t) {
+              c[t] += (uint32_t)__popc(T[t]) << b;
+              any[t] |= T[t];
+            }
+          }
+          uint32_t* w = p.win_rows + (((size_t)group * p.slots + slot) * p.wps + widx) * JPG + lane;
+#pragma unroll
+          for (int t = 0; t < TPG; ++t) {
+            w[t * 32] = any[t];
+            cnt[t] += c[t];
+          }
+          ++widx;
+          in_win = 0;
+        }
+        return;
+      }
+
       // four independent 32x32 transposes, interleaved step by step so the shuffles overlap:
       // afterwards lane j holds in T[t] the rows of this block that match job 32t+j
       uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
-#pragma unroll
-      for (int i = 0; i < 5; ++i) {
-        uint32_t y[TPG];
-#pragma unroll
-        for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(0xFFFFFFFFu, T[t], 16u >> i);
-#pragma unroll
-        for (int t = 0; t < TPG; ++t) {
-          const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
-          T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
-        }
-      }
+      xpose4(T);
 
       if constexpr (BITMAP) {
 #pragma unroll
@@ -670,6 +744,201 @@ __global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
       *last[seg] = hits ? blk * 32u + 31u - __clz(hits) : DSM_NO_ROW;
     }
   }
+  if (lane == 0) {
+    p.out_cnt[job] = total;
+    uint32_t best = last_a;
+    if (last_b != DSM_NO_ROW) {
+      if (best == DSM_NO_ROW) best = last_b;
+      else if (p.price != nullptr && p.price[last_b] > p.price[last_a]) best = last_b;
+    }
+    p.out_max[job] = best;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// k_extract: finishes a count-mode k_match.  Per job the per-slot and per-window counts say where
+// the first k matches and the last match of each segment lie; only those windows (15 blocks)
+// are evaluated again for this one job, lane = row, straight from the global rows and tables.
+// A job needs at most k + 2 windows, usually one to three.  WPJ as in k_merge.
+// ------------------------------------------------------------------------------------------
+
+template <int WPJ>
+__global__ void __launch_bounds__(256) k_extract(const MergeParams p) {
+  constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
+  constexpr uint32_t FULL = 0xFFFFFFFFu;
+  extern __shared__ uint32_t chunk_sums[];  // [JPC][n_chunks]
+  __shared__ uint32_t red_total[8];
+  __shared__ int red_last_a[8], red_last_b[8];
+  const uint32_t lane = threadIdx.x & 31u;
+  const uint32_t warp = threadIdx.x >> 5;
+  const uint32_t jl = warp / WPJ, wj = warp % WPJ;
+  const uint32_t job = blockIdx.x * JPC + jl;
+  const bool live = job < p.n_jobs;
+  const uint32_t n_slots = p.slots;
+  const uint32_t n_chunks = (n_slots + 31u) / 32u;
+  const uint32_t* cnt = p.part_cnt + (size_t)(live ? job : 0u) * p.slots;
+  uint32_t* csum = chunk_sums + jl * n_chunks;
+
+  {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
+    uint32_t tot = 0;
+    int ls_a = -1, ls_b = -1;
+    for (uint32_t ch0 = wj; ch0 < n_chunks; ch0 += 4u * WPJ) {
+      uint32_t c[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t s = (ch0 + u * WPJ) * 32u + lane;
+        c[u] = (live && s < n_slots) ? cnt[s] : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint32_t ch = ch0 + u * WPJ;
+        if (ch >= n_chunks) break;  // warp-uniform
+        const uint32_t s = ch * 32u + lane;
+        const uint32_t sum = __reduce_add_sync(FULL, c[u]);
+        const uint32_t hit_a = __ballot_sync(FULL, c[u] != 0 && s < p.slots_a);
+        const uint32_t hit_b = __ballot_sync(FULL, c[u] != 0 && s >= p.slots_a);
+        if (hit_a) ls_a = (int)(ch * 32u + 31u - __clz(hit_a));
+        if (hit_b) ls_b = (int)(ch * 32u + 31u - __clz(hit_b));
+        if (lane == 0) csum[ch] = sum;
+        tot += sum;
+      }
+    }
+    if (lane == 0) { red_total[warp] = tot; red_last_a[warp] = ls_a; red_last_b[warp] = ls_b; }
+  }
+  __syncthreads();
+  if (!live || wj != 0) return;
+
+  uint32_t total = 0;
+  int ls_a = -1, ls_b = -1;
+#pragma unroll
+  for (int w = 0; w < WPJ; ++w) {
+    total += red_total[jl * WPJ + w];
+    ls_a = max(ls_a, red_last_a[jl * WPJ + w]);
+    ls_b = max(ls_b, red_last_b[jl * WPJ + w]);
+  }
+
+  // ---- what it takes to evaluate this job on one row per lane
+  const uint32_t group = job / JPG, tile = (job % JPG) / 32u, bit = job & 31u;
+  const uint32_t* tab = reinterpret_cast<const uint32_t*>(p.tabs + (size_t)group * p.n_entries) + tile;
+  const uint32_t cut_a = p.recs[(size_t)job * p.rec_words + 0];
+  const uint32_t cut_b = p.recs[(size_t)job * p.rec_words + 1];
+  const uint32_t row_u4 = p.n_cols >> 3;  // uint4 per row: 1 or 2
+  const uint4* rows4 = reinterpret_cast<const uint4*>(p.rows16);
+  auto eval_row = [&](const uint32_t row, const uint32_t cut) -> uint32_t {
+    const uint4* rp = rows4 + (size_t)row * row_u4;
+    const uint4 v0 = __ldg(rp);
+    const uint4 v1 = row_u4 == 2u ? __ldg(rp + 1) : make_uint4(0, 0, 0, 0);
+    const uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    uint32_t ok = row < cut ? 1u : 0u;
+#pragma unroll
+    for (int c = 0; c < DSM_MAX_COLS; ++c) {
+      if ((uint32_t)c < p.n_used) {  // warp-uniform
+        uint32_t code = (c & 1) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
+        if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+        ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
+      }
+    }
+    return ok & 1u;
+  };
+  // block range, cut-off and window records of a slot (same arithmetic as k_match)
+  struct SlotGeom { uint32_t b0, b1, cut, n_win; const uint32_t* wr; };
+  auto geom_of = [&](const uint32_t sl) -> SlotGeom {
+    SlotGeom g;
+    const uint32_t pos = sl / MATCH_WARPS, wq = sl % MATCH_WARPS;
+    uint32_t lo, hi;
+    p.pc.blocks_of(pos, lo, hi);
+    const uint32_t len = hi - lo;
+    g.b0 = lo + (uint32_t)(((unsigned long long)len * wq) / MATCH_WARPS);
+    g.b1 = lo + (uint32_t)(((unsigned long long)len * (wq + 1)) / MATCH_WARPS);
+    g.cut = pos >= p.pc.pa ? cut_b : cut_a;
+    g.n_win = (g.b1 - g.b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+    g.wr = p.win_rows + (((size_t)group * p.slots + sl) * p.wps) * JPG + (job % JPG);
+    return g;
+  };
+  // A window's record is the set R of row lanes (row mod 32) with a match somewhere in its
+  // blocks, so its candidate rows are {32 * blk + l : blk in window, l in R}; candidate i (in
+  // row order) is block i / |R|, the (i mod |R|)-th lane of R.  A sparse job has |R| = 1 or 2
+  // and the whole window is one warp-wide evaluation.
+  auto candidate = [&](const uint32_t i, const uint32_t bs, const uint32_t R, const uint32_t nR) -> uint32_t {
+    const uint32_t b = i / nR;
+    return (bs + b) * 32u + __fns(R, 0u, (int)(i - b * nR) + 1);
+  };
+
+  // ---- first k matches: walk slots and windows in row order, skipping empty ones
+  uint32_t* out = p.out_idx + (size_t)job * p.k;
+  const uint32_t k = p.k;
+  uint32_t have = 0;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  for (uint32_t c0 = 0; c0 < n_chunks && have < k; c0 += 32) {
+    const uint32_t cs = c0 + lane < n_chunks ? csum[c0 + lane] : 0u;
+    uint32_t open_ch = __ballot_sync(FULL, cs != 0);
+    while (open_ch && have < k) {  // all loops below are warp-uniform
+      const uint32_t ch = c0 + __ffs(open_ch) - 1;
+      open_ch &= open_ch - 1;
+      const uint32_t s = ch * 32u + lane;
+      const uint32_t c = s < n_slots ? cnt[s] : 0u;
+      uint32_t open_sl = __ballot_sync(FULL, c != 0);
+      while (open_sl && have < k) {
+        const uint32_t sl = ch * 32u + __ffs(open_sl) - 1;
+        open_sl &= open_sl - 1;
+        const SlotGeom g = geom_of(sl);
+        for (uint32_t w0 = 0; w0 < g.n_win && have < k; w0 += 32) {
+          const uint32_t wv = w0 + lane < g.n_win ? g.wr[(size_t)(w0 + lane) * JPG] : 0u;
+          uint32_t open_w = __ballot_sync(FULL, wv != 0);
+          while (open_w && have < k) {
+            const uint32_t w = w0 + __ffs(open_w) - 1;
+            open_w &= open_w - 1;
+            const uint32_t R = __shfl_sync(FULL, wv, w - w0), nR = __popc(R);
+            const uint32_t bs = g.b0 + w * WIN_BLOCKS, be = min(bs + WIN_BLOCKS, g.b1);
+            const uint32_t n_cand = (be - bs) * nR;
+            for (uint32_t i0 = 0; i0 < n_cand && have < k; i0 += 32) {
+              const uint32_t i = i0 + lane;
+              uint32_t row = 0, ok = 0;
+              if (i < n_cand) {
+                row = candidate(i, bs, R, nR);
+                ok = eval_row(row, g.cut);
+              }
+              const uint32_t hits = __ballot_sync(FULL, ok);
+              const uint32_t rank = have + __popc(hits & lt_mask);
+              if (ok && rank < k) out[rank] = row;
+              have = min(k, have + (uint32_t)__popc(hits));
+            }
+          }
+        }
+      }
+    }
+  }
+  for (uint32_t i = have + lane; i < k; i += 32) out[i] = DSM_NO_ROW;
+
+  // ---- last match of each segment: last non-empty slot -> its last non-empty window ->
+  // candidates from the end
+  auto last_row_of = [&](const int sl) -> uint32_t {
+    if (sl < 0) return DSM_NO_ROW;
+    const SlotGeom g = geom_of((uint32_t)sl);
+    for (int w0 = (int)((g.n_win - 1) / 32u * 32u); w0 >= 0; w0 -= 32) {
+      const uint32_t wv = (uint32_t)w0 + lane < g.n_win ? g.wr[(size_t)(w0 + lane) * JPG] : 0u;
+      const uint32_t nz = __ballot_sync(FULL, wv != 0);
+      if (!nz) continue;
+      const uint32_t wl = 31u - __clz(nz);
+      const uint32_t w = (uint32_t)w0 + wl;
+      const uint32_t R = __shfl_sync(FULL, wv, wl), nR = __popc(R);
+      const uint32_t bs = g.b0 + w * WIN_BLOCKS, be = min(bs + WIN_BLOCKS, g.b1);
+      const uint32_t n_cand = (be - bs) * nR;
+      for (uint32_t hi = n_cand; hi > 0; hi -= min(hi, 32u)) {  // lane 0 takes the last candidate
+        uint32_t row = 0, ok = 0;
+        if (lane < hi) {
+          row = candidate(hi - 1u - lane, bs, R, nR);
+          ok = eval_row(row, g.cut);
+        }
+        const uint32_t hits = __ballot_sync(FULL, ok);
+        if (hits) return __shfl_sync(FULL, row, __ffs(hits) - 1);
+      }
+      break;
+    }
+    return DSM_NO_ROW;
+  };
+  const uint32_t last_a = last_row_of(ls_a);
+  const uint32_t last_b = last_row_of(ls_b);
   if (lane == 0) {
     p.out_cnt[job] = total;
     uint32_t best = last_a;
