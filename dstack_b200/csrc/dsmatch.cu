@@ -3,17 +3,20 @@
 // Data flow of one call (J jobs against a table of N rows, J_t = 128 jobs per group):
 //
 //   records [J][rec_words] u32 --k_build_tables--> tabs [groups][E][4] u32        (scratch)
-//   rows [N][n_cols] u16 + tabs --k_match--> per-slot partials                     (scratch)
-//        part_cnt [J][S], part_last [J][S], part_log [J][S][k] x (block, match word)
-//   partials + price --k_merge--> idx [J][k], cnt [J], max [J]
+//   rows [N][n_cols] u16 + tabs --k_match--> counts                                (scratch)
+//        part_cnt [J][S] matches per slot, win_rows [groups][S][W][128] matching row lanes per
+//        15-block window (S slots per job, W windows per slot)
+//   counts + rows + tabs + price --k_extract--> idx [J][k], cnt [J], max [J]
+//   (bitmap calls: k_match writes every 32-row match word, job-major, and nothing follows)
 //
 // k_match is the hot kernel.  One thread owns one row (a single 128-bit load of its 8 codes,
 // or two for 16-code rows) and, for each column, gathers a 128-bit word group from the
 // shared-memory acceptance table: bit j of word t says whether job 32t+j of the group accepts
-// this dictionary entry.  ANDing the gathered groups evaluates 128 jobs against the row; a
-// 32x32 bit transpose across the warp then gives lane j the 32-row match word of job j, from
-// which count / first-k / last-match are kept per job in registers.  No tensor cores: there is
-// no contraction here, the work is integer gathers and bit logic.
+// this dictionary entry.  ANDing the gathered groups evaluates 128 jobs against the row.  In a
+// top-k call the match bits are summed in per-lane bit-sliced counters and transposed across
+// the warp once per 15-block window; in a bitmap call every block is transposed so that lane j
+// holds the 32-row match word of job j.  No tensor cores: there is no contraction here, the
+// work is integer gathers and bit logic.
 //
 // Reference being replaced: gpuhunt.matches per (job, offer) at
 // core/backends/base/offers.py:154-157 and server/services/pools.py:496-502,533-543, and the
@@ -82,7 +85,7 @@ struct dsm_ctx {
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
   size_t timing_used = 0;
-  DevBuf tabs, counter, part_cnt, part_last, part_log, win_rows, d_jobs, d_idx, d_cnt, d_max, d_bits;
+  DevBuf tabs, counter, part_cnt, win_rows, d_jobs, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
 };
 
@@ -164,14 +167,7 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   const uint32_t units_per_cta = env_units ? (uint32_t)atoi(env_units) : 4u;
   uint32_t want = (resident * (units_per_cta ? units_per_cta : 1u) + pl.n_groups - 1) / pl.n_groups;
   if (want < 1) want = 1;
-  if (k) {
-    // every (job, slot) owns k log entries of 8 bytes: keep the log of one call near 2 GiB by
-    // cutting the rows into fewer pieces when k or the batch is large
-    const unsigned long long per_slot = (unsigned long long)pl.n_groups * JPG * k * 8ull;
-    const unsigned long long max_slots = (2ull << 30) / per_slot;
-    const uint32_t cap = (uint32_t)(max_slots / MATCH_WARPS > 1 ? max_slots / MATCH_WARPS : 1);
-    if (want > cap) want = cap;
-  }
+  (void)k;  // the scratch of a top-k call (counts per slot and window) does not depend on k
   const uint32_t a_blocks = pl.split_block, b_blocks = pl.n_blocks - pl.split_block;
   const uint32_t min_piece = MATCH_WARPS * 2u;
   auto pieces_for = [&](uint32_t blocks) -> uint32_t {
@@ -247,8 +243,6 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   Plan pl;
   int rc = make_plan(ctx, t, L, n_jobs, bitmap ? 0u : k, pl);
   if (rc) return rc;
-  if (!bitmap && (unsigned long long)pl.n_groups * JPG * pl.slots * k > 0xFFFFFFFFull)
-    return fail(DSM_E_TOO_LARGE, "first-k log of this batch exceeds 2^32 entries; use fewer jobs per call or a smaller k");
   const bool row32 = t->desc.n_cols == 16;
   if (row32 && L->n_used < 5) return fail(DSM_E_ARG, "16-column tables need n_used >= 5");
   CK(cudaSetDevice(ctx->device));
@@ -256,10 +250,19 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   const size_t jobs_pad = (size_t)pl.n_groups * JPG;
   if ((rc = ensure(ctx->tabs, (size_t)pl.n_groups * pl.lay.n_entries * 16))) return rc;
   if ((rc = ensure(ctx->counter, 256))) return rc;
+  uint32_t wps = 0;
   if (!bitmap) {
+    // windows per slot: the longest warp range of any piece, in windows of WIN_BLOCKS blocks
+    uint32_t longest = 0;
+    for (uint32_t pos = 0; pos < pl.pc.per_group(); ++pos) {
+      uint32_t lo, hi;
+      pl.pc.blocks_of(pos, lo, hi);
+      const uint32_t per_warp = (hi - lo + MATCH_WARPS - 1) / MATCH_WARPS + 1;
+      if (per_warp > longest) longest = per_warp;
+    }
+    wps = (longest + WIN_BLOCKS - 1) / WIN_BLOCKS;
     if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
-    if ((rc = ensure(ctx->part_last, jobs_pad * pl.slots * 4))) return rc;
-    if ((rc = ensure(ctx->part_log, jobs_pad * pl.slots * k * 8))) return rc;  // (block, word) entries
+    if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * wps * 4))) return rc;
   }
 
   BuildParams bp;
@@ -290,12 +293,11 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   mp.n_entries = pl.lay.n_entries;
   mp.rep_shift = pl.rep_shift;
   mp.n_jobs = n_jobs;
-  mp.k = k;
   mp.slots = pl.slots;
   mp.work_counter = (uint32_t*)ctx->counter.p;
   mp.part_cnt = (uint32_t*)ctx->part_cnt.p;
-  mp.part_last = (uint32_t*)ctx->part_last.p;
-  mp.part_log = (uint2*)ctx->part_log.p;
+  mp.win_rows = (uint32_t*)ctx->win_rows.p;
+  mp.wps = wps;
   mp.bits = d_bits;
 
   std::pair<cudaEvent_t, cudaEvent_t>* tev = nullptr;
@@ -309,35 +311,18 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     tev = &ctx->timing_events[ctx->timing_used++];
     CK(cudaEventRecord(tev->first, ctx->stream));
   }
-  const bool count_mode = !bitmap && getenv("DSM_LOG_MODE") == nullptr;  // DSM_LOG_MODE: the older path, for A/B
-  if (count_mode) {
-    // windows per slot: the longest warp range of any piece, in windows
-    uint32_t longest = 0;
-    for (uint32_t pos = 0; pos < pl.pc.per_group(); ++pos) {
-      uint32_t lo, hi;
-      pl.pc.blocks_of(pos, lo, hi);
-      const uint32_t per_warp = (hi - lo + MATCH_WARPS - 1) / MATCH_WARPS + 1;
-      if (per_warp > longest) longest = per_warp;
-    }
-    mp.wps = (longest + WIN_BLOCKS - 1) / WIN_BLOCKS;
-    if ((rc = ensure(ctx->win_rows, (size_t)pl.n_groups * pl.slots * mp.wps * JPG * 4))) return rc;
-    mp.win_rows = (uint32_t*)ctx->win_rows.p;
-  }
   cudaError_t e = bitmap ? launch_match<MODE_BITMAP>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
-                  : count_mode ? launch_match<MODE_COUNT>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
-                         : launch_match<MODE_LOG>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+                         : launch_match<MODE_COUNT>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   if (tev) CK(cudaEventRecord(tev->second, ctx->stream));
   ctx->launches++;
 
   if (!bitmap) {
-    MergeParams gp;
+    ExtractParams gp;
     gp.pc = pl.pc;
     gp.win_rows = mp.win_rows;
     gp.wps = mp.wps;
     gp.part_cnt = mp.part_cnt;
-    gp.part_last = mp.part_last;
-    gp.part_log = mp.part_log;
     gp.price = t->price;
     gp.n_jobs = n_jobs;
     gp.k = k;
@@ -356,11 +341,8 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     gp.out_max = d_max;
     // few slots per job: a warp per job; thousands (small batches): a CTA per job
     const uint32_t chunk_bytes = (pl.slots + 31u) / 32u * 4u;
-    if (count_mode) {
-      if (pl.slots >= 1024u) k_extract<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
-      else k_extract<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
-    } else if (pl.slots >= 1024u) k_merge<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
-    else k_merge<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
+    if (pl.slots >= 1024u) k_extract<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
+    else k_extract<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
     CK(cudaGetLastError());
     ctx->launches++;
   }
@@ -404,7 +386,7 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->part_last, &ctx->part_log, &ctx->win_rows, &ctx->d_jobs,
+  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->win_rows, &ctx->d_jobs,
                     &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);
@@ -755,7 +737,6 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   mp.n_entries = pl.lay.n_entries;
   mp.rep_shift = pl.rep_shift;
   mp.n_jobs = n_jobs;
-  mp.k = 1;
   mp.slots = pl.slots;
   mp.work_counter = bp.work_counter;
   mp.bits = d_bits;

@@ -1,9 +1,10 @@
 // kernels.cuh -- device code of libdsmatch (sm_100a).  Included by dsmatch.cu only.
 //
 //   k_build_tables  job records -> bit-sliced acceptance tables (one u32 per 32 jobs per entry)
-//   k_match         rows x job groups -> per-slot partial results (count, first-k log, last match)
-//   k_merge         per-job ordered merge of the partials
-//   k_merge_shards  per-job merge of all-gathered per-GPU results
+//   k_match         rows x job groups -> match counts per slot and per 15-block window (top-k
+//                   calls), or every match word job-major (bitmap calls)
+//   k_extract       per job: first k matching rows, total, last match, from those counts
+//   k_merge_shards* per-job merge of all-gathered per-GPU results
 //
 // Work decomposition of k_match.  The rows of the table are cut into P pieces per job group
 // (pa pieces in the "available" segment, pb in the rest; a piece never straddles the segment
@@ -11,7 +12,13 @@
 // counter in position-major order, so every CTA sees cheap and expensive rows and dense and
 // sparse job groups alike and the SMs finish together.  Inside a unit the piece is split evenly
 // over the 8 warps; warp w's results go to slot position*8 + w of each of the group's 128 jobs,
-// so a job's slots are in row order and k_merge takes "the first k matches" by walking them.
+// so a job's slots are in row order and k_extract finds "the first k matches" by walking them.
+//
+// Top-k calls do not transpose every block.  Each thread (= row lane) adds its match bits into
+// 4-bit vertical counters, one per job bit; after 15 blocks (a window) the four counter planes
+// are transposed once, which gives every job its match count in the window and the set of row
+// lanes (row mod 32) that matched.  k_extract then re-evaluates, for one job at a time, only
+// the candidate rows of the few windows that hold its first k matches and its last match.
 
 #pragma once
 
@@ -136,7 +143,7 @@ struct BuildParams {
   uint32_t* work_counter;  // reset here for the k_match that follows in the stream
 };
 
-// Pieces of the row axis (see the header comment); shared by k_match and k_merge.
+// Pieces of the row axis (see the header comment); shared by k_match and k_extract.
 struct Pieces {
   uint32_t n_groups;
   uint32_t n_blocks;     // 32-row blocks of the table
@@ -168,12 +175,9 @@ struct MatchParams {
   uint32_t n_entries;
   uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0..3)
   uint32_t n_jobs;
-  uint32_t k;
   uint32_t slots;        // slots per job = pieces per group * 8
   uint32_t* work_counter;
-  uint32_t* part_cnt;    // [jobs_pad][slots]
-  uint32_t* part_last;   // [jobs_pad][slots]: last 32-row block with a match (DSM_NO_ROW: none)
-  uint2* part_log;       // [jobs_pad][slots][k] x (block, match word)
+  uint32_t* part_cnt;    // count mode: [jobs_pad][slots] matches per slot
   uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
   uint32_t* win_rows;    // count mode: [groups][slots][wps][128]: per window of WIN_BLOCKS blocks and job,
                          // the row lanes (row mod 32) with at least one match
@@ -181,22 +185,17 @@ struct MatchParams {
 };
 
 // k_match modes
-#define MODE_LOG 0     // count + first-k log + last block per slot (k_merge finishes the job)
 #define MODE_BITMAP 1  // every match word, job-major
-#define MODE_COUNT 2   // counts per window only; k_extract re-evaluates the few windows it needs
+#define MODE_COUNT 2   // counts per slot and window only; k_extract re-evaluates the few rows it needs
 // count mode: a 4-bit vertical counter per (row lane, job bit) holds up to 15 blocks
 #define WIN_PLANES 4
 #define WIN_BLOCKS 15
-#define EXTRACT_BATCH 5  // blocks k_extract evaluates at a time (their loads overlap)
 
-struct MergeParams {
+struct ExtractParams {
   const uint32_t* part_cnt;
-  const uint32_t* part_last;
-  const uint2* part_log;
   const double* price;
   uint32_t n_jobs, k, slots, slots_a;  // slots below slots_a belong to the first segment
-  // to find the last matching row inside the last block with a match, that one block is
-  // evaluated again for the job from the global copies of rows and tables
+  // candidate rows are evaluated for one job from the global copies of rows and tables
   const uint16_t* rows16;
   const uint4* tabs;
   const uint32_t* recs;
@@ -316,7 +315,7 @@ __device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCod
 
 template <int NC, bool ROW32, int MODE, bool HAS_LUT, bool REP8>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
-  constexpr bool BITMAP = MODE == MODE_BITMAP;
+  static_assert(MODE == MODE_BITMAP || MODE == MODE_COUNT, "unknown k_match mode");
   constexpr bool COUNT = MODE == MODE_COUNT;
   // shared memory: [staging: E entries][table: E entries x R copies][cut-offs: 2 x 128]
   // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
@@ -350,7 +349,6 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   const Pieces pc = p.pc;
   const uint32_t n_units = pc.count();
   const uint32_t n_blocks = pc.n_blocks;
-  const uint32_t kk = p.k;
   const uint4* rows_lane = p.rows + (ROW32 ? 2u * lane : lane);  // this lane's row inside a block
   uint32_t parity = 0;
   uint32_t cur_group = 0xFFFFFFFFu;
@@ -411,15 +409,12 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     uint32_t full[TPG];
     uint32_t next_evt = b0;  // forces the classification on the first block
 
-    // per job (lane j, tile t): matches, last block with a match, next free element of the
-    // job's first-k log in this slot (index into part_log; the host checks it fits 32 bits)
-    uint32_t cnt[TPG], last_blk[TPG], lidx[TPG];
+    // count mode, per job (lane j, tile t): matches in this slot
+    uint32_t cnt[TPG];
 #pragma unroll
     for (int t = 0; t < TPG; ++t) {
       cnt[t] = 0;
-      last_blk[t] = DSM_NO_ROW;
       full[t] = 0;
-      lidx[t] = ((group * JPG + t * 32 + lane) * p.slots + slot) * kk;
     }
 
     // count mode: vertical match counters of the current window and the window's number
@@ -529,34 +524,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
       xpose4(T);
 
-      if constexpr (BITMAP) {
 #pragma unroll
-        for (int t = 0; t < TPG; ++t) {
-          const uint32_t job = group * JPG + t * 32 + lane;
-          if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T[t];
-        }
-      } else {
-        // branch-free bookkeeping; the first-k log is behind one warp-uniform vote
-        bool want = false;
-#pragma unroll
-        for (int t = 0; t < TPG; ++t) {
-          const bool hit = T[t] != 0u;
-          want = want || (hit && cnt[t] < kk);
-          last_blk[t] = hit ? blk : last_blk[t];
-        }
-        if (__any_sync(0xFFFFFFFFu, want)) {
-          // a job that still lacks k matches logs (block, match word); k_merge expands the
-          // words to rows.  At most k entries per (job, slot): every entry has >= 1 match.
-#pragma unroll
-          for (int t = 0; t < TPG; ++t) {
-            if (T[t] != 0u && cnt[t] < kk) {
-              p.part_log[lidx[t]] = make_uint2(blk, T[t]);
-              lidx[t] += 1;
-            }
-          }
-        }
-#pragma unroll
-        for (int t = 0; t < TPG; ++t) cnt[t] += __popc(T[t]);
+      for (int t = 0; t < TPG; ++t) {
+        const uint32_t job = group * JPG + t * 32 + lane;
+        if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T[t];
       }
     };
 
@@ -586,13 +557,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     }
     if (blk < b1) step(blk, ra);
 
-    if constexpr (!BITMAP) {
+    if constexpr (COUNT) {
 #pragma unroll
-      for (int t = 0; t < TPG; ++t) {
-        const size_t o = (size_t)(group * JPG + t * 32 + lane) * p.slots + slot;
-        p.part_cnt[o] = cnt[t];
-        p.part_last[o] = last_blk[t];  // k_merge finds the row inside the block
-      }
+      for (int t = 0; t < TPG; ++t)
+        p.part_cnt[(size_t)(group * JPG + t * 32 + lane) * p.slots + slot] = cnt[t];
     }
   }
 #ifdef DSM_CTA_TIMING
@@ -609,161 +577,15 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 }
 
 // ------------------------------------------------------------------------------------------
-// k_merge: WPJ warps per job (1 when a job has few slots, 8 when a small batch was cut into
-// thousands of pieces).  Pass 1 sums the per-slot counts 32 slots ("a chunk") at a time, all
-// loads independent; pass 2 (one warp) prefix-sums the chunk totals and opens only the chunks
-// that hold some of the job's first k matches.
-// ------------------------------------------------------------------------------------------
-
-template <int WPJ>
-__global__ void __launch_bounds__(256) k_merge(const MergeParams p) {
-  constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
-  extern __shared__ uint32_t chunk_sums[];  // [JPC][n_chunks]
-  __shared__ uint32_t red_total[8];
-  __shared__ int red_last_a[8], red_last_b[8];
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t warp = threadIdx.x >> 5;
-  const uint32_t jl = warp / WPJ, wj = warp % WPJ;
-  const uint32_t job = blockIdx.x * JPC + jl;
-  const bool live = job < p.n_jobs;
-  const uint32_t n_slots = p.slots;
-  const uint32_t n_chunks = (n_slots + 31u) / 32u;
-  const uint32_t* cnt = p.part_cnt + (size_t)(live ? job : 0u) * p.slots;
-  const uint32_t* lst = p.part_last + (size_t)(live ? job : 0u) * p.slots;
-  uint32_t* csum = chunk_sums + jl * n_chunks;
-
-  {  // pass 1
-    uint32_t tot = 0;
-    int ls_a = -1, ls_b = -1;  // last slot with a match, per segment
-    for (uint32_t ch0 = wj; ch0 < n_chunks; ch0 += 4u * WPJ) {
-      uint32_t c[4];
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t s = (ch0 + u * WPJ) * 32u + lane;
-        c[u] = (live && s < n_slots) ? cnt[s] : 0u;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; ++u) {
-        const uint32_t ch = ch0 + u * WPJ;
-        if (ch >= n_chunks) break;  // warp-uniform
-        const uint32_t s = ch * 32u + lane;
-        const uint32_t sum = __reduce_add_sync(0xFFFFFFFFu, c[u]);
-        const uint32_t hit_a = __ballot_sync(0xFFFFFFFFu, c[u] != 0 && s < p.slots_a);
-        const uint32_t hit_b = __ballot_sync(0xFFFFFFFFu, c[u] != 0 && s >= p.slots_a);
-        if (hit_a) ls_a = (int)(ch * 32u + 31u - __clz(hit_a));
-        if (hit_b) ls_b = (int)(ch * 32u + 31u - __clz(hit_b));
-        if (lane == 0) csum[ch] = sum;
-        tot += sum;
-      }
-    }
-    if (lane == 0) { red_total[warp] = tot; red_last_a[warp] = ls_a; red_last_b[warp] = ls_b; }
-  }
-  __syncthreads();
-  if (!live || wj != 0) return;
-
-  const uint2* log = p.part_log + (size_t)job * p.slots * p.k;
-  uint32_t* out = p.out_idx + (size_t)job * p.k;
-  uint32_t total = 0, have = 0;
-  uint32_t last_a = DSM_NO_ROW, last_b = DSM_NO_ROW;
-  {
-    int ls_a = -1, ls_b = -1;
-#pragma unroll
-    for (int w = 0; w < WPJ; ++w) {
-      total += red_total[jl * WPJ + w];
-      ls_a = max(ls_a, red_last_a[jl * WPJ + w]);
-      ls_b = max(ls_b, red_last_b[jl * WPJ + w]);
-    }
-    if (ls_a >= 0) last_a = lst[ls_a];  // last block with a match in that slot
-    if (ls_b >= 0) last_b = lst[ls_b];
-  }
-  // pass 2
-  for (uint32_t c0 = 0; c0 < n_chunks && have < p.k; c0 += 32) {
-    const uint32_t cs = c0 + lane < n_chunks ? csum[c0 + lane] : 0u;
-    uint32_t cincl = cs;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, cincl, d);
-      if (lane >= (uint32_t)d) cincl += v;
-    }
-    const uint32_t cbefore = have + (cincl - cs);
-    uint32_t open = __ballot_sync(0xFFFFFFFFu, cs != 0 && cbefore < p.k);
-    while (open) {  // warp-uniform
-      const int src_lane = __ffs(open) - 1;
-      open &= open - 1;
-      const uint32_t base_have = __shfl_sync(0xFFFFFFFFu, cbefore, src_lane);
-      const uint32_t s = (c0 + src_lane) * 32u + lane;
-      const uint32_t c = s < n_slots ? cnt[s] : 0u;
-      uint32_t incl = c;  // inclusive prefix sum over the chunk's 32 slots
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, d);
-        if (lane >= (uint32_t)d) incl += v;
-      }
-      const uint32_t before = base_have + (incl - c);  // matches that precede this slot
-      if (c && before < p.k) {
-        // expand the slot's log of (block, match word) entries into rows, ascending
-        uint32_t take = min(c, p.k - before);
-        const uint2* src = log + (size_t)s * p.k;
-        uint32_t o = before;
-        for (uint32_t i = 0; take; ++i) {
-          const uint2 e = src[i];
-          uint32_t w = e.y;
-          while (w && take) {
-            out[o++] = e.x * 32u + (__ffs(w) - 1);
-            w &= w - 1;
-            --take;
-          }
-        }
-      }
-    }
-    const uint32_t sum = __shfl_sync(0xFFFFFFFFu, cincl, 31);
-    have = (sum >= p.k - have) ? p.k : have + sum;  // saturating: only used against k
-  }
-  for (uint32_t i = have + lane; i < p.k; i += 32) out[i] = DSM_NO_ROW;
-
-  // last_a / last_b are blocks: evaluate the 32 rows of each (lane = row) to get the last row
-  {
-    const uint32_t tile = (job % JPG) / 32u, bit = job & 31u;
-    const uint32_t* tab = reinterpret_cast<const uint32_t*>(p.tabs + (size_t)(job / JPG) * p.n_entries);
-    const uint32_t cut_a = p.recs[(size_t)job * p.rec_words + 0];
-    const uint32_t cut_b = p.recs[(size_t)job * p.rec_words + 1];
-    uint32_t* last[2] = {&last_a, &last_b};
-    const uint32_t cut[2] = {cut_a, cut_b};
-    for (int seg = 0; seg < 2; ++seg) {
-      const uint32_t blk = *last[seg];
-      if (blk == DSM_NO_ROW) continue;  // warp-uniform
-      const uint32_t row = blk * 32u + lane;
-      bool ok = row < cut[seg];
-      const uint16_t* codes = p.rows16 + (size_t)row * p.n_cols;
-      for (uint32_t c = 0; c < p.n_used; ++c) {
-        uint32_t code = codes[c];
-        if (p.lut[c] != nullptr) code = p.lut[c][code];
-        ok = ok && ((tab[(size_t)(p.base[c] + code) * 4u + tile] >> bit) & 1u);
-      }
-      const uint32_t hits = __ballot_sync(0xFFFFFFFFu, ok);
-      *last[seg] = hits ? blk * 32u + 31u - __clz(hits) : DSM_NO_ROW;
-    }
-  }
-  if (lane == 0) {
-    p.out_cnt[job] = total;
-    uint32_t best = last_a;
-    if (last_b != DSM_NO_ROW) {
-      if (best == DSM_NO_ROW) best = last_b;
-      else if (p.price != nullptr && p.price[last_b] > p.price[last_a]) best = last_b;
-    }
-    p.out_max[job] = best;
-  }
-}
-
-// ------------------------------------------------------------------------------------------
 // k_extract: finishes a count-mode k_match.  Per job the per-slot and per-window counts say where
 // the first k matches and the last match of each segment lie; only those windows (15 blocks)
 // are evaluated again for this one job, lane = row, straight from the global rows and tables.
-// A job needs at most k + 2 windows, usually one to three.  WPJ as in k_merge.
+// A job needs at most k + 2 windows, usually one to three.  WPJ warps per job: 1 when a job has few slots, 8 when a small batch
+// was cut into thousands of pieces (pass 1 then sums the slot counts with all 8 warps).
 // ------------------------------------------------------------------------------------------
 
 template <int WPJ>
-__global__ void __launch_bounds__(256) k_extract(const MergeParams p) {
+__global__ void __launch_bounds__(256) k_extract(const ExtractParams p) {
   constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   extern __shared__ uint32_t chunk_sums[];  // [JPC][n_chunks]
