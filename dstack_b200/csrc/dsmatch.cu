@@ -85,7 +85,7 @@ struct dsm_ctx {
   bool timing = false;
   std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
   size_t timing_used = 0;
-  DevBuf tabs, counter, part_cnt, win_rows, d_jobs, d_idx, d_cnt, d_max, d_bits;
+  DevBuf tabs, counter, part_cnt, win_rows, slot_start, d_jobs, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
 };
 
@@ -263,6 +263,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     wps = (longest + WIN_BLOCKS - 1) / WIN_BLOCKS;
     if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
     if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * wps * 4))) return rc;
+    if ((rc = ensure(ctx->slot_start, ((size_t)pl.slots + 1) * 4))) return rc;
   }
 
   BuildParams bp;
@@ -297,6 +298,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   mp.work_counter = (uint32_t*)ctx->counter.p;
   mp.part_cnt = (uint32_t*)ctx->part_cnt.p;
   mp.win_rows = (uint32_t*)ctx->win_rows.p;
+  mp.slot_start = (uint32_t*)ctx->slot_start.p;
   mp.wps = wps;
   mp.bits = d_bits;
 
@@ -321,6 +323,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     ExtractParams gp;
     gp.pc = pl.pc;
     gp.win_rows = mp.win_rows;
+    gp.slot_start = mp.slot_start;
     gp.wps = mp.wps;
     gp.part_cnt = mp.part_cnt;
     gp.price = t->price;
@@ -386,7 +389,7 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
   if (!ctx) return 0;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->win_rows, &ctx->d_jobs,
+  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->win_rows, &ctx->slot_start, &ctx->d_jobs,
                     &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);

@@ -182,6 +182,7 @@ struct MatchParams {
   uint32_t* win_rows;    // count mode: [groups][slots][wps][128]: per window of WIN_BLOCKS blocks and job,
                          // the row lanes (row mod 32) with at least one match
   uint32_t wps;          // count mode: windows reserved per slot
+  uint32_t* slot_start;  // count mode: [slots + 1] first block of every slot, then n_blocks
 };
 
 // k_match modes
@@ -190,6 +191,7 @@ struct MatchParams {
 // count mode: a 4-bit vertical counter per (row lane, job bit) holds up to 15 blocks
 #define WIN_PLANES 4
 #define WIN_BLOCKS 15
+#define EXTRACT_PENDING 16  // windows k_extract queues before it evaluates their candidate rows
 
 struct ExtractParams {
   const uint32_t* part_cnt;
@@ -209,6 +211,7 @@ struct ExtractParams {
   Pieces pc;
   const uint32_t* win_rows;
   uint32_t wps;
+  const uint32_t* slot_start;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -401,6 +404,14 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     const uint32_t b0 = lo + (uint32_t)(((unsigned long long)len * warp) / MATCH_WARPS);
     const uint32_t b1 = lo + (uint32_t)(((unsigned long long)len * (warp + 1)) / MATCH_WARPS);
     const uint32_t slot = pos * MATCH_WARPS + warp;
+    if constexpr (COUNT) {
+      // k_extract reads the slots' block ranges instead of redoing this arithmetic per job:
+      // slot s covers blocks [slot_start[s], slot_start[s + 1])
+      if (group == 0 && lane == 0) {
+        p.slot_start[slot] = b0;
+        if (slot + 1 == p.slots) p.slot_start[slot + 1] = b1;
+      }
+    }
 
     // Rows below a job's cut-off pass its price / availability test.  full[t] holds the jobs
     // of tile t that pass on every row of the current block; it only changes at an "event"
@@ -585,7 +596,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 // ------------------------------------------------------------------------------------------
 
 template <int WPJ>
-__global__ void __launch_bounds__(256) k_extract(const ExtractParams p) {
+__global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   extern __shared__ uint32_t chunk_sums[];  // [JPC][n_chunks]
@@ -604,15 +615,15 @@ __global__ void __launch_bounds__(256) k_extract(const ExtractParams p) {
   {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
     uint32_t tot = 0;
     int ls_a = -1, ls_b = -1;
-    for (uint32_t ch0 = wj; ch0 < n_chunks; ch0 += 4u * WPJ) {
-      uint32_t c[4];
+    for (uint32_t ch0 = wj; ch0 < n_chunks; ch0 += 8u * WPJ) {
+      uint32_t c[8];
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) {
         const uint32_t s = (ch0 + u * WPJ) * 32u + lane;
         c[u] = (live && s < n_slots) ? cnt[s] : 0u;
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {
+      for (int u = 0; u < 8; ++u) {
         const uint32_t ch = ch0 + u * WPJ;
         if (ch >= n_chunks) break;  // warp-uniform
         const uint32_t s = ch * 32u + lane;
@@ -644,53 +655,92 @@ __global__ void __launch_bounds__(256) k_extract(const ExtractParams p) {
   const uint32_t* tab = reinterpret_cast<const uint32_t*>(p.tabs + (size_t)group * p.n_entries) + tile;
   const uint32_t cut_a = p.recs[(size_t)job * p.rec_words + 0];
   const uint32_t cut_b = p.recs[(size_t)job * p.rec_words + 1];
-  const uint32_t row_u4 = p.n_cols >> 3;  // uint4 per row: 1 or 2
-  const uint4* rows4 = reinterpret_cast<const uint4*>(p.rows16);
   auto eval_row = [&](const uint32_t row, const uint32_t cut) -> uint32_t {
-    const uint4* rp = rows4 + (size_t)row * row_u4;
-    const uint4 v0 = __ldg(rp);
-    const uint4 v1 = row_u4 == 2u ? __ldg(rp + 1) : make_uint4(0, 0, 0, 0);
-    const uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+    // a rolled loop on purpose: this body is inlined at every flush site and k_extract is
+    // bound by instruction fetch and load latency, not by instruction count
+    const uint16_t* codes = p.rows16 + (size_t)row * p.n_cols;
     uint32_t ok = row < cut ? 1u : 0u;
-#pragma unroll
-    for (int c = 0; c < DSM_MAX_COLS; ++c) {
-      if ((uint32_t)c < p.n_used) {  // warp-uniform
-        uint32_t code = (c & 1) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
-        if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-        ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
-      }
+#pragma unroll 2
+    for (uint32_t c = 0; c < p.n_used; ++c) {
+      uint32_t code = __ldg(codes + c);
+      if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+      ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
     }
     return ok & 1u;
   };
-  // block range, cut-off and window records of a slot (same arithmetic as k_match)
-  struct SlotGeom { uint32_t b0, b1, cut, n_win; const uint32_t* wr; };
-  auto geom_of = [&](const uint32_t sl) -> SlotGeom {
-    SlotGeom g;
-    const uint32_t pos = sl / MATCH_WARPS, wq = sl % MATCH_WARPS;
-    uint32_t lo, hi;
-    p.pc.blocks_of(pos, lo, hi);
-    const uint32_t len = hi - lo;
-    g.b0 = lo + (uint32_t)(((unsigned long long)len * wq) / MATCH_WARPS);
-    g.b1 = lo + (uint32_t)(((unsigned long long)len * (wq + 1)) / MATCH_WARPS);
-    g.cut = pos >= p.pc.pa ? cut_b : cut_a;
-    g.n_win = (g.b1 - g.b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
-    g.wr = p.win_rows + (((size_t)group * p.slots + sl) * p.wps) * JPG + (job % JPG);
-    return g;
-  };
   // A window's record is the set R of row lanes (row mod 32) with a match somewhere in its
   // blocks, so its candidate rows are {32 * blk + l : blk in window, l in R}; candidate i (in
-  // row order) is block i / |R|, the (i mod |R|)-th lane of R.  A sparse job has |R| = 1 or 2
-  // and the whole window is one warp-wide evaluation.
-  auto candidate = [&](const uint32_t i, const uint32_t bs, const uint32_t R, const uint32_t nR) -> uint32_t {
-    const uint32_t b = i / nR;
-    return (bs + b) * 32u + __fns(R, 0u, (int)(i - b * nR) + 1);
+  // row order) is block i / |R|, the (i mod |R|)-th lane of R.  A sparse job has |R| = 1 or 2.
+  auto candidate = [&](const uint32_t i, const uint32_t bs, const uint32_t R) -> uint32_t {
+    const uint32_t nR = __popc(R);
+    const uint32_t b = (i * (65535u / nR + 1u)) >> 16;  // i / nR, exact for i < 512
+    uint32_t r = i - b * nR, m = R, l = 0;              // l = position of the r-th set bit of R
+#pragma unroll
+    for (int s = 16; s >= 1; s >>= 1) {
+      const uint32_t c = __popc(m & ((1u << s) - 1u));
+      if (r >= c) { r -= c; m >>= s; l += s; }
+    }
+    return (bs + b) * 32u + l;
+  };
+  const uint32_t* wr_job = p.win_rows + (size_t)group * p.slots * p.wps * JPG + (job % JPG);
+
+  // ---- windows waiting to be evaluated (warp-private): first block, row-lane set, cut-off,
+  // index of the window's first candidate among all queued candidates.  Candidates are
+  // evaluated 64 at a time, so a sparse job's one-lane windows share evaluations.
+  uint32_t* out = p.out_idx + (size_t)job * p.k;
+  const uint32_t k = p.k;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  __shared__ uint32_t s_pend[8][EXTRACT_PENDING][4];
+  uint32_t (*pend)[4] = s_pend[warp];
+  uint32_t n_pend = 0, q_total = 0;
+  uint32_t have = 0;             // forward mode: matches written so far
+  uint32_t last = DSM_NO_ROW;    // backward mode: highest matching row seen
+  auto push = [&](const uint32_t bs, const uint32_t nb, const uint32_t R, const uint32_t cut) {
+    if (lane == 0) {
+      pend[n_pend][0] = bs;
+      pend[n_pend][1] = R;
+      pend[n_pend][2] = cut;
+      pend[n_pend][3] = q_total;
+    }
+    q_total += nb * (uint32_t)__popc(R);
+    ++n_pend;
+  };
+  // forward: append the matching candidates to out[] until k are there;
+  // backward: walk the candidates from the end and stop at the first match
+  auto flush = [&](const bool backward) {  // warp-uniform
+    __syncwarp();
+    for (uint32_t q0 = 0; q0 < q_total; q0 += 64) {
+      if (backward ? last != DSM_NO_ROW : have >= k) break;
+      uint32_t row[2] = {0, 0}, ok[2] = {0, 0};
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const uint32_t qi = q0 + u * 32 + lane;
+        if (qi < q_total) {
+          const uint32_t q = backward ? q_total - 1u - qi : qi;
+          uint32_t e = 0;
+          for (uint32_t i = 1; i < n_pend; ++i) e = q >= pend[i][3] ? i : e;  // starts ascend
+          row[u] = candidate(q - pend[e][3], pend[e][0], pend[e][1]);
+          ok[u] = eval_row(row[u], pend[e][2]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const uint32_t hits = __ballot_sync(FULL, ok[u]);
+        if (backward) {
+          if (hits && last == DSM_NO_ROW) last = __shfl_sync(FULL, row[u], __ffs(hits) - 1);
+        } else {
+          const uint32_t rank = have + __popc(hits & lt_mask);
+          if (ok[u] && rank < k) out[rank] = row[u];
+          have = min(k, have + (uint32_t)__popc(hits));
+        }
+      }
+    }
+    n_pend = 0;
+    q_total = 0;
+    __syncwarp();
   };
 
   // ---- first k matches: walk slots and windows in row order, skipping empty ones
-  uint32_t* out = p.out_idx + (size_t)job * p.k;
-  const uint32_t k = p.k;
-  uint32_t have = 0;
-  const uint32_t lt_mask = (1u << lane) - 1u;
   for (uint32_t c0 = 0; c0 < n_chunks && have < k; c0 += 32) {
     const uint32_t cs = c0 + lane < n_chunks ? csum[c0 + lane] : 0u;
     uint32_t open_ch = __ballot_sync(FULL, cs != 0);
@@ -699,65 +749,78 @@ __global__ void __launch_bounds__(256) k_extract(const ExtractParams p) {
       open_ch &= open_ch - 1;
       const uint32_t s = ch * 32u + lane;
       const uint32_t c = s < n_slots ? cnt[s] : 0u;
+      const uint32_t my_b0 = s <= n_slots ? p.slot_start[s] : 0u;  // lane 31 may read slot_start[n_slots]
       uint32_t open_sl = __ballot_sync(FULL, c != 0);
+      // slots of at most 8 windows: every lane fetches the window records of its own slot, so
+      // the whole chunk costs one memory round trip instead of one per non-empty slot
+      uint32_t mk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      const bool short_slots = p.wps <= 8u;
+      if (short_slots && c != 0) {
+        const uint32_t my_b1 = p.slot_start[s + 1];
+        const uint32_t my_nwin = (my_b1 - my_b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+        const uint32_t* wr = wr_job + (size_t)s * p.wps * JPG;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < my_nwin ? wr[(size_t)w * JPG] : 0u;
+      }
       while (open_sl && have < k) {
-        const uint32_t sl = ch * 32u + __ffs(open_sl) - 1;
+        const uint32_t sl_lane = __ffs(open_sl) - 1;
         open_sl &= open_sl - 1;
-        const SlotGeom g = geom_of(sl);
-        for (uint32_t w0 = 0; w0 < g.n_win && have < k; w0 += 32) {
-          const uint32_t wv = w0 + lane < g.n_win ? g.wr[(size_t)(w0 + lane) * JPG] : 0u;
+        const uint32_t sl = ch * 32u + sl_lane;
+        const uint32_t b0 = __shfl_sync(FULL, my_b0, sl_lane);
+        const uint32_t b1 = sl_lane < 31u ? __shfl_sync(FULL, my_b0, sl_lane + 1) : p.slot_start[sl + 1];
+        const uint32_t cut = sl >= p.slots_a ? cut_b : cut_a;
+        if (short_slots) {
+#pragma unroll
+          for (int w = 0; w < 8; ++w) {
+            const uint32_t R = __shfl_sync(FULL, mk[w], sl_lane);
+            if (R != 0) {
+              const uint32_t bs = b0 + (uint32_t)w * WIN_BLOCKS;
+              push(bs, min(bs + WIN_BLOCKS, b1) - bs, R, cut);
+            }
+          }
+          // one flush site per slot (the queue holds two slots' worth of windows)
+          if (n_pend > EXTRACT_PENDING - 8u || q_total >= 64u) flush(false);
+          continue;
+        }
+        const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+        const uint32_t* wr = wr_job + (size_t)sl * p.wps * JPG;
+        for (uint32_t w0 = 0; w0 < n_win && have < k; w0 += 32) {
+          const uint32_t wv = w0 + lane < n_win ? wr[(size_t)(w0 + lane) * JPG] : 0u;
           uint32_t open_w = __ballot_sync(FULL, wv != 0);
           while (open_w && have < k) {
-            const uint32_t w = w0 + __ffs(open_w) - 1;
+            const uint32_t wl = __ffs(open_w) - 1;
             open_w &= open_w - 1;
-            const uint32_t R = __shfl_sync(FULL, wv, w - w0), nR = __popc(R);
-            const uint32_t bs = g.b0 + w * WIN_BLOCKS, be = min(bs + WIN_BLOCKS, g.b1);
-            const uint32_t n_cand = (be - bs) * nR;
-            for (uint32_t i0 = 0; i0 < n_cand && have < k; i0 += 32) {
-              const uint32_t i = i0 + lane;
-              uint32_t row = 0, ok = 0;
-              if (i < n_cand) {
-                row = candidate(i, bs, R, nR);
-                ok = eval_row(row, g.cut);
-              }
-              const uint32_t hits = __ballot_sync(FULL, ok);
-              const uint32_t rank = have + __popc(hits & lt_mask);
-              if (ok && rank < k) out[rank] = row;
-              have = min(k, have + (uint32_t)__popc(hits));
-            }
+            const uint32_t bs = b0 + (w0 + wl) * WIN_BLOCKS;
+            push(bs, min(bs + WIN_BLOCKS, b1) - bs, __shfl_sync(FULL, wv, wl), cut);
+            if (n_pend == EXTRACT_PENDING || q_total >= 64u) flush(false);
           }
         }
       }
     }
   }
+  flush(false);
   for (uint32_t i = have + lane; i < k; i += 32) out[i] = DSM_NO_ROW;
 
   // ---- last match of each segment: last non-empty slot -> its last non-empty window ->
   // candidates from the end
   auto last_row_of = [&](const int sl) -> uint32_t {
     if (sl < 0) return DSM_NO_ROW;
-    const SlotGeom g = geom_of((uint32_t)sl);
-    for (int w0 = (int)((g.n_win - 1) / 32u * 32u); w0 >= 0; w0 -= 32) {
-      const uint32_t wv = (uint32_t)w0 + lane < g.n_win ? g.wr[(size_t)(w0 + lane) * JPG] : 0u;
+    const uint32_t b0 = p.slot_start[sl], b1 = p.slot_start[sl + 1];
+    const uint32_t cut = (uint32_t)sl >= p.slots_a ? cut_b : cut_a;
+    const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+    const uint32_t* wr = wr_job + (size_t)sl * p.wps * JPG;
+    last = DSM_NO_ROW;
+    for (int w0 = (int)((n_win - 1) / 32u * 32u); w0 >= 0; w0 -= 32) {
+      const uint32_t wv = (uint32_t)w0 + lane < n_win ? wr[(size_t)(w0 + lane) * JPG] : 0u;
       const uint32_t nz = __ballot_sync(FULL, wv != 0);
       if (!nz) continue;
       const uint32_t wl = 31u - __clz(nz);
-      const uint32_t w = (uint32_t)w0 + wl;
-      const uint32_t R = __shfl_sync(FULL, wv, wl), nR = __popc(R);
-      const uint32_t bs = g.b0 + w * WIN_BLOCKS, be = min(bs + WIN_BLOCKS, g.b1);
-      const uint32_t n_cand = (be - bs) * nR;
-      for (uint32_t hi = n_cand; hi > 0; hi -= min(hi, 32u)) {  // lane 0 takes the last candidate
-        uint32_t row = 0, ok = 0;
-        if (lane < hi) {
-          row = candidate(hi - 1u - lane, bs, R, nR);
-          ok = eval_row(row, g.cut);
-        }
-        const uint32_t hits = __ballot_sync(FULL, ok);
-        if (hits) return __shfl_sync(FULL, row, __ffs(hits) - 1);
-      }
+      const uint32_t bs = b0 + ((uint32_t)w0 + wl) * WIN_BLOCKS;
+      push(bs, min(bs + WIN_BLOCKS, b1) - bs, __shfl_sync(FULL, wv, wl), cut);
+      flush(true);
       break;
     }
-    return DSM_NO_ROW;
+    return last;
   };
   const uint32_t last_a = last_row_of(ls_a);
   const uint32_t last_b = last_row_of(ls_b);
