@@ -74,6 +74,29 @@ def test_large_k_stays_exact(matcher):
     assert (got.count > 2048).any()
 
 
+def test_long_slots_with_many_windows(matcher, monkeypatch):
+    """Few, long row pieces (what a 16k-job batch over tens of millions of offers gets): every
+    slot holds more than 32 windows, so k_extract pages through a slot's window records.
+    Checked like the benchmark does at full size: sampled jobs against the oracle, properties
+    for every job."""
+    import bench
+
+    monkeypatch.setenv("DSM_UNITS_PER_CTA", "1")  # read by the library at call time
+    cat = synth.make_catalog(2_000_000, seed=71, n_shapes=1024)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, 4096, seed=72)
+    dt = matcher.upload(table)
+    try:
+        plan = matcher.plan(dt, pack_jobs(table, sj.columns), 16)
+        blocks_per_warp = table.n_rows // 32 / (plan["pieces_a"] + plan["pieces_b"]) / 8
+        assert blocks_per_warp > 32 * 15
+        got = matcher.match_topk(dt, sj.columns, 16)
+    finally:
+        dt.close()
+    n = bench.verify(cat.columns, sj, 16, got.index, got.count, got.max_price, np.random.default_rng(5), n_sample=12)
+    assert n == 12 and (got.count > 16).any() and ((got.count > 0) & (got.count < 16)).any()
+
+
 def test_bitmap_equals_oracle_matrix(matcher):
     cat = synth.make_catalog(20_000, seed=8, n_shapes=512)
     table = encode_table(cat.columns)
