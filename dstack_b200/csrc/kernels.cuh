@@ -74,9 +74,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-// 128-bit row load through L1: the line was requested PREFETCH_BLOCKS blocks earlier by
-// prefetch_l1, so this normally hits L1 (each row is used once per unit; L1 is only the
-// landing buffer of the software prefetch).
+// 128-bit read-only row load.  Rows are loaded into registers two blocks ahead of their use.
+// PREFETCH_BLOCKS > 2 additionally requests lines into L1 that many blocks ahead; with three
+// CTAs' tables in shared memory only ~24 KB of L1 is left per SM, 24 warps x 6 blocks of
+// prefetched rows do not fit (ncu: 8 % L1 hit rate) and the kernel measured 3-5 % slower with
+// it, on tables inside and outside L2 alike -- so it is off by default.
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 r;
   asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -88,7 +90,7 @@ __device__ __forceinline__ void prefetch_l1(const void* p) {
   asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
 #ifndef PREFETCH_BLOCKS
-#define PREFETCH_BLOCKS 6
+#define PREFETCH_BLOCKS 2
 #endif
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
@@ -542,8 +544,8 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       }
     };
 
-    // two row buffers used alternately (no register rotation); the rows themselves were
-    // requested PREFETCH_BLOCKS blocks ahead into L1
+    // two row buffers used alternately (no register rotation, and explicit names: an indexed
+    // array of buffers made the compiler spill)
     RowCodes<NC> ra, rb;
     if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, ra);
     if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rb);
@@ -556,7 +558,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     auto step = [&](const uint32_t blk, RowCodes<NC>& buf) {
       const RowCodes<NC> cur = buf;
       if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, buf);
-      if (blk + PREFETCH_BLOCKS < b1)
+      if (PREFETCH_BLOCKS > 2 && blk + PREFETCH_BLOCKS < b1)
         prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
       process(blk, cur);
     };
@@ -692,6 +694,8 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   const uint32_t lt_mask = (1u << lane) - 1u;
   __shared__ uint32_t s_pend[8][EXTRACT_PENDING][4];
   uint32_t (*pend)[4] = s_pend[warp];
+  __shared__ uint32_t s_wlist[8][256][2];  // long slots: (window, row-lane set) of non-empty windows
+  uint32_t (*wlist)[2] = s_wlist[warp];
   uint32_t n_pend = 0, q_total = 0;
   uint32_t have = 0;             // forward mode: matches written so far
   uint32_t last = DSM_NO_ROW;    // backward mode: highest matching row seen
@@ -784,16 +788,33 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
         }
         const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
         const uint32_t* wr = wr_job + (size_t)sl * p.wps * JPG;
-        for (uint32_t w0 = 0; w0 < n_win && have < k; w0 += 32) {
-          const uint32_t wv = w0 + lane < n_win ? wr[(size_t)(w0 + lane) * JPG] : 0u;
-          uint32_t open_w = __ballot_sync(FULL, wv != 0);
-          while (open_w && have < k) {
-            const uint32_t wl = __ffs(open_w) - 1;
-            open_w &= open_w - 1;
-            const uint32_t bs = b0 + (w0 + wl) * WIN_BLOCKS;
-            push(bs, min(bs + WIN_BLOCKS, b1) - bs, __shfl_sync(FULL, wv, wl), cut);
+        // long slots: fetch 256 window records at once, compact the non-empty ones into a
+        // short list, then queue them from a rolled loop (one flush site)
+        for (uint32_t w0 = 0; w0 < n_win && have < k; w0 += 256) {
+          uint32_t wv[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t w = w0 + u * 32 + lane;
+            wv[u] = w < n_win ? wr[(size_t)w * JPG] : 0u;
+          }
+          uint32_t n_list = 0;
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const uint32_t nz = __ballot_sync(FULL, wv[u] != 0);
+            if (wv[u] != 0) {
+              const uint32_t at = n_list + __popc(nz & lt_mask);
+              wlist[at][0] = w0 + u * 32 + lane;
+              wlist[at][1] = wv[u];
+            }
+            n_list += __popc(nz);
+          }
+          __syncwarp();
+          for (uint32_t i = 0; i < n_list && have < k; ++i) {
+            const uint32_t bs = b0 + wlist[i][0] * WIN_BLOCKS;
+            push(bs, min(bs + WIN_BLOCKS, b1) - bs, wlist[i][1], cut);
             if (n_pend == EXTRACT_PENDING || q_total >= 64u) flush(false);
           }
+          __syncwarp();
         }
       }
     }
