@@ -74,11 +74,13 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-// 128-bit read-only row load.  Rows are loaded into registers two blocks ahead of their use.
-// PREFETCH_BLOCKS > 2 additionally requests lines into L1 that many blocks ahead; with three
-// CTAs' tables in shared memory only ~24 KB of L1 is left per SM, 24 warps x 6 blocks of
-// prefetched rows do not fit (ncu: 8 % L1 hit rate) and the kernel measured 3-5 % slower with
-// it, on tables inside and outside L2 alike -- so it is off by default.
+// 128-bit read-only row load.  Rows are loaded into registers two blocks ahead of their use;
+// PREFETCH_BLOCKS > 2 additionally requests the lines into L1 that many blocks ahead.  With
+// three CTAs' tables in shared memory only ~24 KB of L1 is left per SM, so most prefetched
+// lines are gone again before use (ncu: 8 % L1 hit rate), but the request still pulls the row
+// from DRAM into L2 early.  Measured (config 3 kernel time): table cold in DRAM 0.226 ms
+// without, 0.203 ms with a distance of 4 or 6; table already in L2 0.187 vs 0.191 ms; 16 M rows
+// (larger than L2) 3.08 vs 3.15 ms.  The cold case is the one a scheduler tick sees.
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 r;
   asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -87,10 +89,10 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   return r;
 }
 __device__ __forceinline__ void prefetch_l1(const void* p) {
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));  // prefetch.global.L2 measured the same
 }
 #ifndef PREFETCH_BLOCKS
-#define PREFETCH_BLOCKS 2
+#define PREFETCH_BLOCKS 4
 #endif
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
@@ -558,7 +560,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     auto step = [&](const uint32_t blk, RowCodes<NC>& buf) {
       const RowCodes<NC> cur = buf;
       if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, buf);
-      if (PREFETCH_BLOCKS > 2 && blk + PREFETCH_BLOCKS < b1)
+      if (blk + PREFETCH_BLOCKS < b1)
         prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
       process(blk, cur);
     };
