@@ -196,6 +196,9 @@ struct MatchParams {
 #define WIN_PLANES 4
 #define WIN_BLOCKS 15
 #define EXTRACT_PENDING 16  // windows k_extract queues before it evaluates their candidate rows
+#ifndef EXTRACT_LANE_ROWS
+#define EXTRACT_LANE_ROWS 2  // candidate rows per lane and evaluation step (their loads overlap; 4 measured slower)
+#endif
 
 struct ExtractParams {
   const uint32_t* part_cnt;
@@ -715,12 +718,14 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   // backward: walk the candidates from the end and stop at the first match
   auto flush = [&](const bool backward) {  // warp-uniform
     __syncwarp();
-    for (uint32_t q0 = 0; q0 < q_total; q0 += 64) {
+    for (uint32_t q0 = 0; q0 < q_total; q0 += 32u * EXTRACT_LANE_ROWS) {
       if (backward ? last != DSM_NO_ROW : have >= k) break;
-      uint32_t row[2] = {0, 0}, ok[2] = {0, 0};
+      uint32_t row[EXTRACT_LANE_ROWS], ok[EXTRACT_LANE_ROWS];
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
+      for (int u = 0; u < EXTRACT_LANE_ROWS; ++u) {
         const uint32_t qi = q0 + u * 32 + lane;
+        row[u] = 0;
+        ok[u] = 0;
         if (qi < q_total) {
           const uint32_t q = backward ? q_total - 1u - qi : qi;
           uint32_t e = 0;
@@ -730,7 +735,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
         }
       }
 #pragma unroll
-      for (int u = 0; u < 2; ++u) {
+      for (int u = 0; u < EXTRACT_LANE_ROWS; ++u) {
         const uint32_t hits = __ballot_sync(FULL, ok[u]);
         if (backward) {
           if (hits && last == DSM_NO_ROW) last = __shfl_sync(FULL, row[u], __ffs(hits) - 1);
@@ -785,7 +790,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
             }
           }
           // one flush site per slot (the queue holds two slots' worth of windows)
-          if (n_pend > EXTRACT_PENDING - 8u || q_total >= 64u) flush(false);
+          if (n_pend > EXTRACT_PENDING - 8u || q_total >= 32u * EXTRACT_LANE_ROWS) flush(false);
           continue;
         }
         const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
@@ -814,7 +819,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
           for (uint32_t i = 0; i < n_list && have < k; ++i) {
             const uint32_t bs = b0 + wlist[i][0] * WIN_BLOCKS;
             push(bs, min(bs + WIN_BLOCKS, b1) - bs, wlist[i][1], cut);
-            if (n_pend == EXTRACT_PENDING || q_total >= 64u) flush(false);
+            if (n_pend == EXTRACT_PENDING || q_total >= 32u * EXTRACT_LANE_ROWS) flush(false);
           }
           __syncwarp();
         }
