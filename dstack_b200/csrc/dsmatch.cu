@@ -261,6 +261,8 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
       if (per_warp > longest) longest = per_warp;
     }
     wps = (longest + WIN_BLOCKS - 1) / WIN_BLOCKS;
+    if ((unsigned long long)jobs_pad * pl.slots * wps * 4ull > (64ull << 30))
+      return fail(DSM_E_TOO_LARGE, "per-window match records of this call exceed 64 GiB; split the jobs over several calls");
     if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
     if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * wps * 4))) return rc;
     if ((rc = ensure(ctx->slot_start, ((size_t)pl.slots + 1) * 4))) return rc;

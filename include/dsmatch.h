@@ -151,7 +151,10 @@ int dsm_lut_upload(dsm_ctx* ctx, uint32_t column, const uint16_t* lut, uint32_t 
 /* For each job: the first k matching rows in table order (= the reference's offers[:k]),
  * the number of matching rows (= len(offers)) and the row holding the highest price among
  * the matches (= max(offer.price)), DSM_NO_ROW if none.
- * out_idx: n_jobs*k u32, unused slots DSM_NO_ROW.  out_cnt, out_max: n_jobs u32.
+ * out_idx: n_jobs*k u32, unused slots DSM_NO_ROW.  out_cnt, out_max: n_jobs u32.  1 <= k <= 4096.
+ * Scratch (owned by the context, grown on demand, independent of k): about
+ * n_jobs * n_rows / 120 bytes of per-window match records; a call that would need more than
+ * 64 GiB of it returns DSM_E_TOO_LARGE -- split the jobs over several calls.
  * Reference: get_instance_offers + slicing, see the header comment. */
 int dsm_match_topk(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
                    const uint32_t* jobs, uint32_t n_jobs, uint32_t k, uint32_t* out_idx,
