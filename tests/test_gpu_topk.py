@@ -44,7 +44,7 @@ def test_topk_ragged_sizes(matcher, n_offers, n_jobs):
 @pytest.mark.parametrize("n_jobs", [1, 5, 130])
 def test_small_batch_over_many_pieces(matcher, n_jobs):
     """A scheduler tick: a handful of jobs against a large table is cut into thousands of row
-    pieces, which k_merge then walks with a whole CTA per job."""
+    pieces, whose counts k_extract then sums with a whole CTA per job."""
     cat = synth.make_catalog(400_000, seed=31, n_shapes=1024)
     table = encode_table(cat.columns)
     sj = synth.make_jobs(cat, table, n_jobs, seed=32)
