@@ -97,6 +97,55 @@ def test_long_slots_with_many_windows(matcher, monkeypatch):
     assert n == 12 and (got.count > 16).any() and ((got.count > 0) & (got.count < 16)).any()
 
 
+def test_dense_and_single_match_jobs(matcher):
+    """The extremes of k_extract's candidate search in one batch: jobs without any filter (every
+    live row matches: all 32 row lanes of every window, 480 candidates per window), jobs whose
+    matches are a price prefix ending at a chosen row (the last-match search must land exactly on
+    it: first rows, middle, end of the available segment), and jobs that ask for one instance
+    type (a handful of rows scattered over 300k: one candidate lane per window)."""
+    cat = synth.make_catalog(300_000, seed=51, n_shapes=256)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, 40, seed=52)
+    jc = sj.columns
+    nan2 = np.full((jc.n, 2), np.nan)
+    jc.max_price[:] = np.nan
+    jc.spot[:] = -1
+    for name in ("cpu", "memory", "disk", "gpu_count", "gpu_memory", "gpu_total"):
+        getattr(jc, name)[:] = nan2
+    jc.gpu_vendor[:] = 0
+    jc.cc_min[:] = -1
+    jc.gpu_name_any[:] = True
+    jc.src_backend_mask[:] = 0xFFFFFFFF
+    jc.off_backend_mask[:] = 0xFFFFFFFF
+    jc.exclude_not_available[:] = False
+    jc.region_any[:] = True
+    jc.itype_any[:] = True
+    # jobs 8.. : a price window around one row of the result order (prices are not unique, so
+    # take rows whose price occurs once among the available offers)
+    price = np.asarray(cat.columns.price)
+    order = columnar.rank_order(cat.columns)
+    n_avail = int(np.asarray(cat.columns.available).sum())
+    uniq, first, counts = np.unique(price[order[:n_avail]], return_index=True, return_counts=True)
+    singles = np.sort(first[counts == 1])  # positions in the result order
+    assert len(singles) > 16
+    picks = [singles[0], singles[len(singles) // 3], singles[len(singles) // 2], singles[-2], singles[-1]]
+    for j, pos in enumerate(picks, start=8):
+        jc.max_price[j] = price[order[pos]]
+        jc.exclude_not_available[j] = True
+    # jobs 16..23: one instance type each (CSR over the table's instance-type ids)
+    rng = np.random.default_rng(53)
+    want_types = rng.choice(len(cat.columns.itypes), size=8, replace=False)
+    counts_per_job = np.zeros(jc.n, np.int64)
+    counts_per_job[16:24] = 1
+    jc.itype_any[16:24] = False
+    jc.itype_ptr = np.concatenate(([0], np.cumsum(counts_per_job))).astype(np.int64)
+    jc.itype_ids = want_types.astype(np.int64)
+    got = _check(matcher, cat, sj, 50)
+    assert (got.count[:8] == len(price)).all()
+    for j, pos in enumerate(picks, start=8):
+        assert got.count[j] == pos + 1 and got.max_price[j] == price[order[pos]]
+
+
 def test_bitmap_equals_oracle_matrix(matcher):
     cat = synth.make_catalog(20_000, seed=8, n_shapes=512)
     table = encode_table(cat.columns)
