@@ -146,6 +146,28 @@ def test_dense_and_single_match_jobs(matcher):
         assert got.count[j] == pos + 1 and got.max_price[j] == price[order[pos]]
 
 
+def test_random_shapes_against_oracle(matcher):
+    """Forty random (offers, jobs, k, share of not-available rows) combinations: segment
+    boundaries, partial last windows and slots of a block or two fall wherever they fall."""
+    rng = np.random.default_rng(2024)
+    for case in range(40):
+        n_offers = int(rng.choice([1, 5, 31, 32, 33, 479, 480, 481, 960, 1500, 4096, 9999, 20011, 50000]))
+        n_jobs = int(rng.choice([1, 2, 31, 33, 127, 128, 129, 300]))
+        k = int(rng.choice([1, 2, 15, 16, 17, 50, 64, 200]))
+        cat = synth.make_catalog(n_offers, seed=1000 + case, n_shapes=int(rng.choice([1, 8, 64, 300])))
+        share = float(rng.choice([0.0, 0.1, 0.5, 1.0]))
+        flip = rng.random(n_offers) < share
+        cat.columns.available[:] = ~flip
+        table = encode_table(cat.columns)
+        sj = synth.make_jobs(cat, table, n_jobs, seed=2000 + case)
+        if case % 3 == 0:
+            sj.columns.exclude_not_available[:] = rng.random(n_jobs) < 0.5
+        try:
+            _check(matcher, cat, sj, k)
+        except AssertionError as e:  # name the case that failed
+            raise AssertionError(f"case {case}: offers={n_offers} jobs={n_jobs} k={k} not-available={share}") from e
+
+
 def test_bitmap_equals_oracle_matrix(matcher):
     cat = synth.make_catalog(20_000, seed=8, n_shapes=512)
     table = encode_table(cat.columns)
