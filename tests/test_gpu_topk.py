@@ -191,3 +191,36 @@ def test_all_not_available_and_all_available(matcher):
         sj = synth.make_jobs(cat, table, 40, seed=5)
         sj.columns.exclude_not_available[::2] = True
         _check(matcher, cat, sj, 16)
+
+
+def test_topk_on_a_pool_table_agrees_with_its_bitmap(matcher):
+    """32-byte rows (pool tables, up to 16 code columns) through the count-mode kernel: first k,
+    count and max price must be what the bitmap of the same call implies."""
+    import test_configs as T
+    from dstack_b200 import pools as PP
+    from dstack_b200.ingest import job_columns
+
+    rows = synth.make_pool(6000, seed=11, n_fleets=12)
+    calls = T._config2_jobs(rows, 90)
+    index = PP.PoolIndex(rows, matcher=matcher)
+    try:
+        assert index.table.n_cols == 16
+        filters = [PP._pool_filter(p, requirements=kw["requirements"], status=kw["status"],
+                                   fleet_model=kw.get("fleet_model"), multinode=kw.get("multinode", False),
+                                   master_job_provisioning_data=kw.get("master_job_provisioning_data"),
+                                   volumes=None, shared=False) for p, kw in calls]
+        jobs = job_columns(index.table, filters)
+        top = matcher.match_topk(index.device_table, jobs, 16)
+        every = matcher.match_all(index.device_table, jobs, order="rank")
+    finally:
+        index.close()
+    price = np.array([PP.M.InstanceOffer.parse_raw(r.offer).price if r.offer is not None else np.nan for r in rows])
+    assert sum(len(e) > 16 for e in every) > 10 and sum(0 < len(e) <= 16 for e in every) > 0
+    for j, e in enumerate(every):
+        assert top.count[j] == len(e)
+        n = min(16, len(e))
+        assert list(top.index[j][:n]) == list(e[:n]) and (top.index[j][n:] == -1).all()
+        if len(e):
+            assert top.max_price[j] == price[e].max()
+        else:
+            assert np.isnan(top.max_price[j])
