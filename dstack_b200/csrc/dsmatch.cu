@@ -190,6 +190,13 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   return 0;
 }
 
+// k_build_tables: x = 32-job tiles, y = columns, z = chunks of BUILD_CHUNK dictionary entries
+static dim3 build_grid(const Plan& pl) {
+  uint32_t longest = 1;
+  for (uint32_t c = 0; c < pl.lay.n_used; ++c) longest = pl.lay.card[c] > longest ? pl.lay.card[c] : longest;
+  return dim3(pl.n_groups * TPG, pl.lay.n_used, (longest + BUILD_CHUNK - 1) / BUILD_CHUNK);
+}
+
 template <int NC, bool ROW32, int MODE, bool HAS_LUT, bool REP8>
 static cudaError_t launch_match_v(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
   cudaError_t e = cudaFuncSetAttribute(k_match<NC, ROW32, MODE, HAS_LUT, REP8>,
@@ -278,7 +285,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   bp.bk_entries = t->bk_entries;
   bp.tabs = (uint4*)ctx->tabs.p;
   bp.work_counter = (uint32_t*)ctx->counter.p;
-  k_build_tables<<<dim3(pl.n_groups * TPG, pl.lay.n_used), 256, 0, ctx->stream>>>(bp);
+  k_build_tables<<<build_grid(pl), 256, 0, ctx->stream>>>(bp);
   CK(cudaGetLastError());
   ctx->launches++;
 
@@ -724,7 +731,7 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   bp.bk_entries = t->bk_entries;
   bp.tabs = reinterpret_cast<uint4*>(scratch + 256);
   bp.work_counter = reinterpret_cast<uint32_t*>(scratch);  // k_build_tables zeroes it
-  k_build_tables<<<dim3(pl.n_groups * TPG, pl.lay.n_used), 256, 0, ctx->stream>>>(bp);
+  k_build_tables<<<build_grid(pl), 256, 0, ctx->stream>>>(bp);
   CK(cudaGetLastError());
   ctx->launches++;
 

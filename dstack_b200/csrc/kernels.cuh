@@ -222,16 +222,18 @@ struct ExtractParams {
 };
 
 // ------------------------------------------------------------------------------------------
-// k_build_tables: grid (groups*4, n_used), block 256 = 8 warps; lane = job of the tile,
+// k_build_tables: grid (groups*4, n_used, entry chunks), block 256 = 8 warps; lane = job of the tile,
 // warps stride over the column's dictionary entries; one ballot = one table word.
 // ------------------------------------------------------------------------------------------
+
+#define BUILD_CHUNK 64u
 
 __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
   const uint32_t tile = blockIdx.x;
   const uint32_t col = blockIdx.y;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warp = threadIdx.x >> 5;
-  if (tile == 0 && col == 0 && threadIdx.x == 0) *p.work_counter = 0u;
+  if (tile == 0 && col == 0 && blockIdx.z == 0 && threadIdx.x == 0) *p.work_counter = 0u;
   const uint32_t job = tile * 32u + lane;
   const bool live = job < p.n_jobs;
   const uint32_t* rec = p.recs + (size_t)(live ? job : 0) * p.lay.rec_words + p.lay.rec_off[col];
@@ -247,7 +249,10 @@ __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
     if (kind == DSM_COL_BK) { r1 = rec[1]; r2 = rec[2]; r3 = rec[3]; }
   }
 
-  for (uint32_t e = warp; e < card; e += 8u) {
+  // blockIdx.z cuts long dictionaries into chunks of BUILD_CHUNK entries so that the largest
+  // column does not set the kernel's duration (8 entries are in flight per CTA)
+  const uint32_t e_end = min(card, (blockIdx.z + 1u) * BUILD_CHUNK);
+  for (uint32_t e = blockIdx.z * BUILD_CHUNK + warp; e < e_end; e += 8u) {
     bool ok = false;
     if (live) {
       if (kind == DSM_COL_RANGE) {
