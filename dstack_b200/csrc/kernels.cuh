@@ -600,11 +600,13 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 }
 
 // ------------------------------------------------------------------------------------------
-// k_extract: finishes a count-mode k_match.  Per job the per-slot and per-window counts say where
-// the first k matches and the last match of each segment lie; only those windows (15 blocks)
-// are evaluated again for this one job, lane = row, straight from the global rows and tables.
-// A job needs at most k + 2 windows, usually one to three.  WPJ warps per job: 1 when a job has few slots, 8 when a small batch
-// was cut into thousands of pieces (pass 1 then sums the slot counts with all 8 warps).
+// k_extract: finishes a count-mode k_match.  Per job the per-slot counts and the per-window
+// row-lane records say where the first k matches and the last match of each segment lie; only
+// the candidate rows of those windows are evaluated again for this one job, lane = row, straight
+// from the global rows and tables.  A job needs at most k + 2 windows: one to three when its
+// matches are dense, k when they are sparse.  WPJ warps per job: 1 when a job has few slots,
+// 8 when a small batch was cut into thousands of pieces (pass 1 then sums the slot counts with
+// all 8 warps; the rest is done by the first of them).
 // ------------------------------------------------------------------------------------------
 
 template <int WPJ>
@@ -685,6 +687,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   // row order) is block i / |R|, the (i mod |R|)-th lane of R.  A sparse job has |R| = 1 or 2.
   auto candidate = [&](const uint32_t i, const uint32_t bs, const uint32_t R) -> uint32_t {
     const uint32_t nR = __popc(R);
+    if (nR == 1u) return (bs + i) * 32u + (__ffs(R) - 1);  // the usual case of a sparse job
     const uint32_t b = (i * (65535u / nR + 1u)) >> 16;  // i / nR, exact for i < 512
     uint32_t r = i - b * nR, m = R, l = 0;              // l = position of the r-th set bit of R
 #pragma unroll
