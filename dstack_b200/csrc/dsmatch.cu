@@ -110,7 +110,8 @@ struct Plan {
   uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, grid;
 };
 
-// k = 0: bitmap mode (no per-slot logs, so nothing limits the number of pieces).
+// k = 0: bitmap mode.  The geometry does not depend on k (kept in the signature for
+// dsm_plan_query, which reports the plan of a concrete call).
 static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, uint32_t n_jobs,
                      uint32_t k, Plan& pl) {
   if (!L || L->n_used < 1 || L->n_used > t->desc.n_cols)
