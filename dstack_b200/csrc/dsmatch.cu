@@ -107,7 +107,7 @@ static int ensure(DevBuf& b, size_t bytes) {
 struct Plan {
   LayoutDev lay;
   Pieces pc;
-  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, grid;
+  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, direct_fill, grid;
 };
 
 // k = 0: bitmap mode.  The geometry does not depend on k (kept in the signature for
@@ -153,6 +153,16 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   if (force_rep) pl.rep_shift = atoi(force_rep) >= 3 ? 3u : 0u;
   pl.smem = base * 16u * (pl.rep_shift ? (1u << pl.rep_shift) + 1u : 1u) + cuts;
   if (pl.smem > MAX_SMEM_BYTES) { pl.rep_shift = 0; pl.smem = base * 16u + cuts; }
+  // Eight copies fit beside MATCH_CTAS_PER_SM CTAs but a ninth (the TMA staging copy) does not:
+  // keep the eight and let the threads fill them from global memory.
+  pl.direct_fill = 0;
+  const char* no_direct = getenv("DSM_NO_DIRECT_FILL");  // tuning only
+  if (pl.rep_shift == 0 && !force_rep && !no_direct &&
+      MATCH_CTAS_PER_SM * (base * 128u + cuts + 1024u) <= 220u * 1024u) {
+    pl.rep_shift = 3;
+    pl.direct_fill = 1;
+    pl.smem = base * 128u + cuts;
+  }
   pl.n_groups = (n_jobs + JPG - 1) / JPG;
   pl.n_blocks = t->desc.n_rows / 32u;
   pl.split_block = t->desc.split_row / 32u;
@@ -305,6 +315,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   mp.rec_words = L->rec_words;
   mp.n_entries = pl.lay.n_entries;
   mp.rep_shift = pl.rep_shift;
+  mp.direct_fill = pl.direct_fill;
   mp.n_jobs = n_jobs;
   mp.slots = pl.slots;
   mp.work_counter = (uint32_t*)ctx->counter.p;
@@ -751,6 +762,7 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   mp.rec_words = layout->rec_words;
   mp.n_entries = pl.lay.n_entries;
   mp.rep_shift = pl.rep_shift;
+  mp.direct_fill = pl.direct_fill;
   mp.n_jobs = n_jobs;
   mp.slots = pl.slots;
   mp.work_counter = bp.work_counter;

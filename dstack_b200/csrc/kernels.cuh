@@ -178,6 +178,8 @@ struct MatchParams {
   uint32_t rec_words;
   uint32_t n_entries;
   uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0..3)
+  uint32_t direct_fill;  // 1: the 8 copies fit but no staging copy beside them; the threads fill the
+                         // copies straight from global memory instead of fanning out a TMA-staged table
   uint32_t n_jobs;
   uint32_t slots;        // slots per job = pieces per group * 8
   uint32_t* work_counter;
@@ -336,11 +338,14 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
   // R = 8 copy r lies in bank group r (4 banks), lane l reads copy l%8, and the 8 lanes of every
   // quarter-warp phase of a 128-bit gather hit 8 different bank groups: no bank conflicts
-  // whatever the codes are.  R < 8 (large dictionaries) only reduces them.
+  // whatever the codes are.  R < 8 (large dictionaries) only reduces them.  When the eight
+  // copies fit but not a ninth for staging (p.direct_fill) there is no staging area: the threads
+  // fill the copies straight from global memory.
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr uint32_t rep_shift = REP8 ? 3u : 0u;
+  const bool direct_fill = REP8 && p.direct_fill != 0u;
   uint4* s_stage = reinterpret_cast<uint4*>(smem_raw);
-  uint4* s_tab = rep_shift ? s_stage + p.n_entries : s_stage;
+  uint4* s_tab = (rep_shift && !direct_fill) ? s_stage + p.n_entries : s_stage;
   uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + ((size_t)p.n_entries << rep_shift));  // [2][128]
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ uint32_t s_unit;
@@ -383,7 +388,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 
     if (group != cur_group) {
       // ---- stage this group's acceptance table (TMA bulk copy) and cut-off rows
-      if (tid == 0) {
+      if (tid == 0 && !direct_fill) {
         const uint32_t bytes = p.n_entries * 16u;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         mbar_expect_tx(&s_bar, bytes);
@@ -399,11 +404,17 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         s_cut[tid] = ca;
         s_cut[JPG + tid] = cb;
       }
-      mbar_wait(&s_bar, parity);
-      parity ^= 1u;
-      if (rep_shift) {  // fan the staged table out into its R interleaved copies
-        const uint32_t n_copy = p.n_entries << rep_shift;
-        for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = s_stage[i >> rep_shift];
+      if (direct_fill) {  // 8 consecutive threads read the same entry: one 16-byte request per 8 lanes
+        const uint4* src = p.tabs + (size_t)group * p.n_entries;
+        const uint32_t n_copy = p.n_entries << 3;
+        for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = __ldg(src + (i >> 3));
+      } else {
+        mbar_wait(&s_bar, parity);
+        parity ^= 1u;
+        if (rep_shift) {  // fan the staged table out into its R interleaved copies
+          const uint32_t n_copy = p.n_entries << rep_shift;
+          for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = s_stage[i >> rep_shift];
+        }
       }
       __syncthreads();
       cur_group = group;

@@ -224,3 +224,19 @@ def test_topk_on_a_pool_table_agrees_with_its_bitmap(matcher):
             assert top.max_price[j] == price[e].max()
         else:
             assert np.isnan(top.max_price[j])
+
+
+def test_tables_that_fit_eight_times_only_without_a_staging_copy(matcher):
+    """Dictionaries of 467..570 entries: eight shared-memory copies fit beside three CTAs, a ninth
+    (the TMA staging copy) does not, so the kernel fills the copies straight from global memory.
+    The plan must say so (shared memory = entries * 128 + cut-offs) and results stay exact."""
+    cat = synth.make_catalog(200_000, seed=4, n_shapes=4096)
+    table = encode_table(cat.columns)
+    sj = synth.make_jobs(cat, table, 300, seed=4)
+    dt = matcher.upload(table)
+    try:
+        plan = matcher.plan(dt, pack_jobs(table, sj.columns), 16)
+    finally:
+        dt.close()
+    assert 466 < plan["entries"] <= 570 and plan["smem"] == plan["entries"] * 128 + 1024
+    _check(matcher, cat, sj, 16)
