@@ -162,6 +162,9 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     pl.rep_shift = 3;
     pl.direct_fill = 1;
     pl.smem = base * 128u + cuts;
+  } else if (pl.rep_shift == 3 && getenv("DSM_FORCE_DIRECT_FILL")) {  // tuning only
+    pl.direct_fill = 1;
+    pl.smem = base * 128u + cuts;
   }
   pl.n_groups = (n_jobs + JPG - 1) / JPG;
   pl.n_blocks = t->desc.n_rows / 32u;
