@@ -195,8 +195,10 @@ struct MatchParams {
 #define MODE_BITMAP 1  // every match word, job-major
 #define MODE_COUNT 2   // counts per slot and window only; k_extract re-evaluates the few rows it needs
 // count mode: a 4-bit vertical counter per (row lane, job bit) holds up to 15 blocks
+#ifndef WIN_PLANES
 #define WIN_PLANES 4
-#define WIN_BLOCKS 15
+#endif
+#define WIN_BLOCKS ((1 << WIN_PLANES) - 1)
 #define EXTRACT_PENDING 16  // windows k_extract queues before it evaluates their candidate rows
 #ifndef EXTRACT_LANE_ROWS
 #define EXTRACT_LANE_ROWS 2  // candidate rows per lane and evaluation step (their loads overlap; 4 measured slower)
