@@ -5,9 +5,12 @@
 //   records [J][rec_words] u32 --k_build_tables--> tabs [groups][E][4] u32        (scratch)
 //   rows [N][n_cols] u16 + tabs --k_match--> counts                                (scratch)
 //        part_cnt [J][S] matches per slot, win_rows [groups][S][W][128] matching row lanes per
-//        15-block window (S slots per job, W windows per slot)
+//        15-block window (S slots per job, W windows per slot), group_nact [groups]
 //   counts + rows + tabs + price --k_extract--> idx [J][k], cnt [J], max [J]
 //   (bitmap calls: k_match writes every 32-row match word, job-major, and nothing follows)
+//
+// Jobs are evaluated in the order dsm_layout.job_order gives (128 per group); scratch is indexed
+// by evaluation slot, results by job.
 //
 // k_match is the hot kernel.  One thread owns one row (a single 128-bit load of its 8 codes,
 // or two for 16-code rows) and, for each column, gathers a 128-bit word group from the
@@ -66,6 +69,13 @@ struct dsm_table {
   double* price;
   uint32_t* gpu_entries;
   uint32_t* bk_entries;
+  uint32_t* pair_entries;
+};
+
+// events around the launches of one call: build | match | extract (n = events used)
+struct StepEvents {
+  cudaEvent_t e[4];
+  int n = 0;
 };
 
 struct DevBuf {
@@ -78,16 +88,39 @@ struct dsm_ctx {
   cudaStream_t stream;
   bool own_stream;
   int sm_count;
+  // tuning knobs, read from the environment once when the context is created (0 = default)
+  int force_rep = -1;        // DSM_REP_SHIFT: 0 single table copy, 3 eight copies
+  bool no_direct = false;    // DSM_NO_DIRECT_FILL
+  bool force_direct = false; // DSM_FORCE_DIRECT_FILL
+  uint32_t units_per_cta = 0;// DSM_UNITS_PER_CTA
   std::mutex mu;
   uint64_t launches;
   // optional timing of the match kernel alone (bench.py's roofline): event pairs recorded
   // around each k_match launch while enabled, read back by dsm_timing_read
   bool timing = false;
-  std::vector<std::pair<cudaEvent_t, cudaEvent_t>> timing_events;
+  std::vector<StepEvents> timing_events;
   size_t timing_used = 0;
-  DevBuf tabs, counter, part_cnt, win_rows, slot_start, d_jobs, d_idx, d_cnt, d_max, d_bits;
+  DevBuf tabs, counter, part_cnt, win_rows, slot_start, group_nact, d_jobs, d_order, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
 };
+
+// Every entry point makes the context's device current for its own work and puts the caller's
+// device back on return, so a host framework that keeps "its" device current is not disturbed.
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int device) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    ok = (prev == device) || cudaSetDevice(device) == cudaSuccess;
+    if (prev == device) prev = -1;  // nothing to restore
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+#define USE_DEVICE(dev)   \
+  DeviceGuard guard_(dev); \
+  if (!guard_.ok) return fail(DSM_E_CUDA, "cudaSetDevice failed")
 
 static int ensure(DevBuf& b, size_t bytes) {
   if (bytes <= b.cap) return 0;
@@ -107,29 +140,49 @@ static int ensure(DevBuf& b, size_t bytes) {
 struct Plan {
   LayoutDev lay;
   Pieces pc;
-  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, direct_fill, grid;
+  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, direct_fill, grid, wps, dead_entry;
 };
 
-// k = 0: bitmap mode.  The geometry does not depend on k (kept in the signature for
-// dsm_plan_query, which reports the plan of a concrete call).
-static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, uint32_t n_jobs,
-                     uint32_t k, Plan& pl) {
+// Words of a record a column's predicate occupies.
+static uint32_t pred_words(const dsm_layout* L, uint32_t c) {
+  switch (L->kind[c]) {
+    case DSM_COL_RANGE: return 1;
+    case DSM_COL_BITSET: return (L->card[c] + 31u) / 32u;
+    case DSM_COL_GPU: return 5u + L->aux[c];
+    case DSM_COL_BK: return 4;
+    case DSM_COL_PAIR: return L->aux[c] + 1u;
+    default: return 0;
+  }
+}
+
+// Geometry of a call; pure arithmetic.  Does not depend on k.
+static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, uint32_t n_jobs, Plan& pl) {
   if (!L || L->n_used < 1 || L->n_used > t->desc.n_cols)
     return fail(DSM_E_ARG, "layout.n_used out of range");
   if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
+  if (L->rec_words < 3 || L->rec_words > 65536) return fail(DSM_E_ARG, "layout.rec_words out of range");
   LayoutDev& d = pl.lay;
   memset(&d, 0, sizeof d);
   d.n_used = L->n_used;
   d.rec_words = L->rec_words;
   uint32_t base = 0;
+  pl.dead_entry = 0xFFFFFFFFu;
   for (uint32_t c = 0; c < L->n_used; ++c) {
-    if (L->kind[c] < DSM_COL_RANGE || L->kind[c] > DSM_COL_BK)
+    if (L->kind[c] < DSM_COL_RANGE || L->kind[c] > DSM_COL_PAIR)
       return fail(DSM_E_ARG, "layout.kind invalid");
     if (L->card[c] == 0 || L->card[c] > 65536) return fail(DSM_E_ARG, "layout.card invalid");
     if (L->kind[c] == DSM_COL_GPU && L->card[c] != t->desc.n_gpu_entries)
       return fail(DSM_E_ARG, "GPU column card != table GPU dictionary size");
     if (L->kind[c] == DSM_COL_BK && L->card[c] != t->desc.n_bk_entries)
       return fail(DSM_E_ARG, "BK column card != table BK dictionary size");
+    if (L->kind[c] == DSM_COL_PAIR && (L->card[c] != t->desc.n_pair_entries || L->aux[c] == 0))
+      return fail(DSM_E_ARG, "PAIR column card != table pair dictionary size (or aux = 0)");
+    if (L->kind[c] == DSM_COL_GPU && L->aux[c] > 2048) return fail(DSM_E_ARG, "GPU-name bitset too long");
+    // the predicate must lie inside the record, behind the two cut-off words
+    const uint32_t words = pred_words(L, c);
+    if (L->rec_off[c] < 2 || (unsigned long long)L->rec_off[c] + words > L->rec_words)
+      return fail(DSM_E_ARG, "layout.rec_off: a column's predicate does not fit in the record");
+    if (L->kind[c] == DSM_COL_BK) pl.dead_entry = base;  // entry 0 of that column
     d.kind[c] = L->kind[c];
     d.card[c] = L->card[c];
     d.flags[c] = L->flags[c];
@@ -139,30 +192,25 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     base += L->card[c];
   }
   d.n_entries = base;
-  // Replicate the table in shared memory as far as it fits: 8 copies make the gathers
-  // bank-conflict free.  Prefer keeping MATCH_CTAS_PER_SM CTAs resident, then fewer copies.
+  // Replicate the table in shared memory when it fits: 8 copies make the gathers bank-conflict
+  // free (2 and 4 copies measured slower than one).  Prefer keeping MATCH_CTAS_PER_SM CTAs resident.
   const uint32_t cuts = 2u * JPG * 4u;
   if (base * 16u + cuts > MAX_SMEM_BYTES)
     return fail(DSM_E_DICT_TOO_LARGE, "acceptance tables need more shared memory than one CTA has");
-  const char* force_rep = getenv("DSM_REP_SHIFT");  // tuning / tests only
   pl.rep_shift = 0;
-  for (uint32_t rs = 3; rs >= 3; --rs) {  // 8 copies or none: 2 and 4 copies measured slower than none
-    const uint32_t need = base * 16u * ((1u << rs) + 1u) + cuts;
-    if (need <= MAX_SMEM_BYTES / MATCH_CTAS_PER_SM) { pl.rep_shift = rs; break; }
-  }
-  if (force_rep) pl.rep_shift = atoi(force_rep) >= 3 ? 3u : 0u;
-  pl.smem = base * 16u * (pl.rep_shift ? (1u << pl.rep_shift) + 1u : 1u) + cuts;
+  if (base * 16u * 9u + cuts <= MAX_SMEM_BYTES / MATCH_CTAS_PER_SM) pl.rep_shift = 3;
+  if (ctx->force_rep >= 0) pl.rep_shift = ctx->force_rep >= 3 ? 3u : 0u;
+  pl.smem = base * 16u * (pl.rep_shift ? 9u : 1u) + cuts;
   if (pl.smem > MAX_SMEM_BYTES) { pl.rep_shift = 0; pl.smem = base * 16u + cuts; }
   // Eight copies fit beside MATCH_CTAS_PER_SM CTAs but a ninth (the TMA staging copy) does not:
   // keep the eight and let the threads fill them from global memory.
   pl.direct_fill = 0;
-  const char* no_direct = getenv("DSM_NO_DIRECT_FILL");  // tuning only
-  if (pl.rep_shift == 0 && !force_rep && !no_direct &&
+  if (pl.rep_shift == 0 && ctx->force_rep < 0 && !ctx->no_direct &&
       MATCH_CTAS_PER_SM * (base * 128u + cuts + 1024u) <= 220u * 1024u) {
     pl.rep_shift = 3;
     pl.direct_fill = 1;
     pl.smem = base * 128u + cuts;
-  } else if (pl.rep_shift == 3 && getenv("DSM_FORCE_DIRECT_FILL")) {  // tuning only
+  } else if (pl.rep_shift == 3 && ctx->force_direct) {
     pl.direct_fill = 1;
     pl.smem = base * 128u + cuts;
   }
@@ -170,35 +218,41 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   pl.n_blocks = t->desc.n_rows / 32u;
   pl.split_block = t->desc.split_row / 32u;
 
-  // Resident CTAs: a multiple of the SM count.  Work units (piece, group): about UNITS_PER_CTA
-  // per resident CTA so that the dynamic draw balances the SMs, but every warp of a unit keeps
-  // at least a couple of blocks.
+  // Resident CTAs: a multiple of the SM count.  Work units (piece, group): about units_per_cta
+  // per resident CTA so that the dynamic draw balances the SMs; a piece is a whole number of
+  // 15-block windows and gives every warp at least one.
   uint32_t per_sm = MATCH_CTAS_PER_SM;
   const uint32_t smem_cap = 220u * 1024u;
   while (per_sm > 1 && per_sm * (pl.smem + 1024u) > smem_cap) --per_sm;
   const uint32_t resident = (uint32_t)ctx->sm_count * per_sm;
-  const char* env_units = getenv("DSM_UNITS_PER_CTA");  // tuning only
-  // measured: 4-6 units per CTA balance a 32-group batch best; with <= 8 groups the pieces get
-  // so short that the per-unit table staging shows, and 2 is 15 % faster
-  const uint32_t units_per_cta = env_units ? (uint32_t)atoi(env_units) : (pl.n_groups <= 8u ? 2u : 4u);
-  uint32_t want = (resident * (units_per_cta ? units_per_cta : 1u) + pl.n_groups - 1) / pl.n_groups;
-  if (want < 1) want = 1;
-  (void)k;  // the scratch of a top-k call (counts per slot and window) does not depend on k
+  // Units per resident CTA: many short units balance the SMs (8 per CTA measured best on a
+  // 128-group batch over 8 M rows: 3.73 ms against 3.84 with 4 and 4.10 with 2), but every unit
+  // stages its group's table first, so a warp's share of a unit is kept at MIN_WPW windows or more
+  // (4096 jobs x 1 M rows: 0.146 ms with 10 windows per warp against 0.154 with 5 and 0.168 with 2)
+  // -- unless that would leave CTAs without any unit.
+  const uint32_t MIN_WPW = 10;
+  const uint32_t units_per_cta = ctx->units_per_cta ? ctx->units_per_cta : 8u;
   const uint32_t a_blocks = pl.split_block, b_blocks = pl.n_blocks - pl.split_block;
-  const uint32_t min_piece = MATCH_WARPS * 2u;
-  auto pieces_for = [&](uint32_t blocks) -> uint32_t {
-    if (blocks == 0) return 0u;
-    uint32_t n = (uint32_t)(((unsigned long long)want * blocks + pl.n_blocks - 1) / pl.n_blocks);
-    const uint32_t cap = blocks / min_piece;
-    if (n > cap) n = cap;
-    return n < 1 ? 1u : n;
+  const unsigned long long n_win = (unsigned long long)Pieces::windows(a_blocks) + Pieces::windows(b_blocks);
+  auto wpw_for = [&](unsigned long long units) -> unsigned long long {  // windows per warp for about `units` units
+    unsigned long long pieces = (units + pl.n_groups - 1) / pl.n_groups;
+    if (pieces < 1) pieces = 1;
+    const unsigned long long w = (n_win + pieces * MATCH_WARPS / 2) / (pieces * MATCH_WARPS);
+    return w < 1 ? 1 : w;
   };
+  unsigned long long wpw = wpw_for((unsigned long long)resident * units_per_cta);
+  if (!ctx->units_per_cta && wpw < MIN_WPW) {
+    const unsigned long long fill = wpw_for(resident);  // the share that gives every CTA one unit
+    wpw = fill < MIN_WPW ? fill : MIN_WPW;
+  }
   pl.pc.n_groups = pl.n_groups;
   pl.pc.n_blocks = pl.n_blocks;
   pl.pc.split_block = pl.split_block;
-  pl.pc.pa = pieces_for(a_blocks);
-  pl.pc.pb = pieces_for(b_blocks);
+  pl.pc.wpw = (uint32_t)wpw;
+  pl.pc.pa = Pieces::pieces_for(a_blocks, pl.pc.wpw);
+  pl.pc.pb = Pieces::pieces_for(b_blocks, pl.pc.wpw);
   pl.slots = pl.pc.per_group() * MATCH_WARPS;
+  pl.wps = pl.pc.wpw;  // windows per slot
   const uint32_t units = pl.pc.count();
   pl.grid = units < resident ? units : resident;
   return 0;
@@ -211,153 +265,142 @@ static dim3 build_grid(const Plan& pl) {
   return dim3(pl.n_groups * TPG, pl.lay.n_used, (longest + BUILD_CHUNK - 1) / BUILD_CHUNK);
 }
 
-template <int NC, bool ROW32, int MODE, bool HAS_LUT, bool REP8>
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT>
 static cudaError_t launch_match_v(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(k_match<NC, ROW32, MODE, HAS_LUT, REP8>,
+  cudaError_t e = cudaFuncSetAttribute(k_match<NCMAX, ROW32, MODE, HAS_LUT>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  k_match<NC, ROW32, MODE, HAS_LUT, REP8><<<grid, MATCH_THREADS, smem, st>>>(mp);
+  k_match<NCMAX, ROW32, MODE, HAS_LUT><<<grid, MATCH_THREADS, smem, st>>>(mp);
   return cudaGetLastError();
 }
 
-template <int NC, bool ROW32, int MODE>
-static cudaError_t launch_match_nc(const MatchParams& mp, bool has_lut, uint32_t grid, uint32_t smem,
-                                   cudaStream_t st) {
-  const bool rep8 = mp.rep_shift == 3u;
-  if (has_lut) return rep8 ? launch_match_v<NC, ROW32, MODE, true, true>(mp, grid, smem, st)
-                           : launch_match_v<NC, ROW32, MODE, true, false>(mp, grid, smem, st);
-  return rep8 ? launch_match_v<NC, ROW32, MODE, false, true>(mp, grid, smem, st)
-              : launch_match_v<NC, ROW32, MODE, false, false>(mp, grid, smem, st);
-}
-
 template <int MODE>
-static cudaError_t launch_match(uint32_t nc, bool row32, const MatchParams& mp, bool has_lut,
-                                uint32_t grid, uint32_t smem, cudaStream_t st) {
-#define CASE_NC(n, r) case n: return launch_match_nc<n, r, MODE>(mp, has_lut, grid, smem, st);
-#ifdef DSM_FAST_BUILD  // experiments: only the shapes the benchmark uses
-  if (!row32) {
-    switch (nc) { CASE_NC(5, false) CASE_NC(6, false) }
-  }
-  return cudaErrorInvalidValue;
+static cudaError_t launch_match(bool row32, const MatchParams& mp, bool has_lut, uint32_t grid, uint32_t smem,
+                                cudaStream_t st) {
+#ifdef DSM_FAST_BUILD  // experiments: only the shape the benchmark uses
+  if (row32 || has_lut) return cudaErrorInvalidValue;
+  return launch_match_v<8, false, MODE, false>(mp, grid, smem, st);
+#else
+  if (!row32) return has_lut ? launch_match_v<8, false, MODE, true>(mp, grid, smem, st)
+                             : launch_match_v<8, false, MODE, false>(mp, grid, smem, st);
+  return has_lut ? launch_match_v<16, true, MODE, true>(mp, grid, smem, st)
+                 : launch_match_v<16, true, MODE, false>(mp, grid, smem, st);
 #endif
-  if (!row32) {
-    switch (nc) {
-      CASE_NC(1, false) CASE_NC(2, false) CASE_NC(3, false) CASE_NC(4, false)
-      CASE_NC(5, false) CASE_NC(6, false) CASE_NC(7, false) CASE_NC(8, false)
-    }
-  } else {
-    switch (nc) {
-      CASE_NC(5, true) CASE_NC(6, true) CASE_NC(7, true) CASE_NC(8, true) CASE_NC(9, true)
-      CASE_NC(10, true) CASE_NC(11, true) CASE_NC(12, true) CASE_NC(13, true) CASE_NC(14, true)
-      CASE_NC(15, true) CASE_NC(16, true)
-    }
-  }
-#undef CASE_NC
-  return cudaErrorInvalidValue;
 }
 
-// Issue build -> match -> merge on the context's stream.  d_jobs and the outputs are device
-// pointers.  Caller holds ctx->mu.
-static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, const uint32_t* d_jobs,
-                     uint32_t n_jobs, uint32_t k, bool bitmap, uint32_t* d_idx, uint32_t* d_cnt,
-                     uint32_t* d_max, uint32_t* d_bits) {
-  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
-  if (!bitmap && (k == 0 || k > 4096)) return fail(DSM_E_ARG, "k must be in 1..4096");
-  Plan pl;
-  int rc = make_plan(ctx, t, L, n_jobs, bitmap ? 0u : k, pl);
-  if (rc) return rc;
-  const bool row32 = t->desc.n_cols == 16;
-  if (row32 && L->n_used < 5) return fail(DSM_E_ARG, "16-column tables need n_used >= 5");
-  CK(cudaSetDevice(ctx->device));
-
-  const size_t jobs_pad = (size_t)pl.n_groups * JPG;
-  if ((rc = ensure(ctx->tabs, (size_t)pl.n_groups * pl.lay.n_entries * 16))) return rc;
-  if ((rc = ensure(ctx->counter, 256))) return rc;
-  uint32_t wps = 0;
-  if (!bitmap) {
-    // windows per slot: the longest warp range of any piece, in windows of WIN_BLOCKS blocks
-    uint32_t longest = 0;
-    for (uint32_t pos = 0; pos < pl.pc.per_group(); ++pos) {
-      uint32_t lo, hi;
-      pl.pc.blocks_of(pos, lo, hi);
-      const uint32_t per_warp = (hi - lo + MATCH_WARPS - 1) / MATCH_WARPS + 1;
-      if (per_warp > longest) longest = per_warp;
-    }
-    wps = (longest + WIN_BLOCKS - 1) / WIN_BLOCKS;
-    if ((unsigned long long)jobs_pad * pl.slots * wps * 4ull > (64ull << 30))
-      return fail(DSM_E_TOO_LARGE, "per-window match records of this call exceed 64 GiB; split the jobs over several calls");
-    if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
-    if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * wps * 4))) return rc;
-    if ((rc = ensure(ctx->slot_start, ((size_t)pl.slots + 1) * 4))) return rc;
-  }
-
-  BuildParams bp;
+// Fill the kernel parameters shared by every way of running k_build_tables + k_match.
+static void fill_params(const dsm_table* t, const dsm_layout* L, const Plan& pl, const uint32_t* d_jobs,
+                        const uint32_t* d_order, uint32_t n_jobs, uint4* tabs, uint32_t* counter,
+                        uint32_t* group_nact, BuildParams& bp, MatchParams& mp, bool& has_lut) {
   bp.lay = pl.lay;
   bp.recs = d_jobs;
+  bp.job_order = d_order;
   bp.n_jobs = n_jobs;
   bp.gpu_entries = t->gpu_entries;
   bp.bk_entries = t->bk_entries;
-  bp.tabs = (uint4*)ctx->tabs.p;
-  bp.work_counter = (uint32_t*)ctx->counter.p;
-  k_build_tables<<<build_grid(pl), 256, 0, ctx->stream>>>(bp);
-  CK(cudaGetLastError());
-  ctx->launches++;
+  bp.pair_entries = t->pair_entries;
+  bp.tabs = tabs;
+  bp.work_counter = counter;
 
-  MatchParams mp;
   memset(&mp, 0, sizeof mp);
   mp.rows = t->rows;
-  mp.tabs = (const uint4*)ctx->tabs.p;
+  mp.tabs = tabs;
   mp.recs = d_jobs;
-  bool has_lut = false;
+  mp.job_order = d_order;
+  has_lut = false;
   for (uint32_t c = 0; c < L->n_used; ++c) {
     mp.lut[c] = L->lut[c];
     has_lut = has_lut || L->lut[c] != nullptr;
     mp.base[c] = pl.lay.base[c];
   }
   mp.pc = pl.pc;
+  mp.n_used = L->n_used;
   mp.rec_words = L->rec_words;
   mp.n_entries = pl.lay.n_entries;
+  mp.dead_entry = pl.dead_entry;
+  mp.live_a = t->desc.n_live_a;
+  mp.live_b = t->desc.split_row + t->desc.n_live_b;
   mp.rep_shift = pl.rep_shift;
   mp.direct_fill = pl.direct_fill;
   mp.n_jobs = n_jobs;
   mp.slots = pl.slots;
-  mp.work_counter = (uint32_t*)ctx->counter.p;
+  mp.work_counter = counter;
+  mp.group_nact = group_nact;
+  mp.wps = pl.wps;
+}
+
+// Issue build -> match -> extract on the context's stream.  d_jobs, d_order (may be NULL) and the
+// outputs are device pointers.  Caller holds ctx->mu and has made the context's device current.
+static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, const uint32_t* d_jobs,
+                     const uint32_t* d_order, uint32_t n_jobs, uint32_t k, bool bitmap, uint32_t* d_idx,
+                     uint32_t* d_cnt, uint32_t* d_max, uint32_t* d_bits) {
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  if (!bitmap && (k == 0 || k > 4096)) return fail(DSM_E_ARG, "k must be in 1..4096");
+  Plan pl;
+  int rc = make_plan(ctx, t, L, n_jobs, pl);
+  if (rc) return rc;
+  const bool row32 = t->desc.n_cols == 16;
+
+  const size_t jobs_pad = (size_t)pl.n_groups * JPG;
+  if ((rc = ensure(ctx->tabs, (size_t)pl.n_groups * pl.lay.n_entries * 16))) return rc;
+  if ((rc = ensure(ctx->counter, 256))) return rc;
+  if ((rc = ensure(ctx->group_nact, (size_t)pl.n_groups * 4))) return rc;
+  if (!bitmap) {
+    if ((unsigned long long)jobs_pad * pl.slots * pl.wps * 4ull > (64ull << 30))
+      return fail(DSM_E_TOO_LARGE, "per-window match records of this call exceed 64 GiB; split the jobs over several calls");
+    if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
+    if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * pl.wps * 4))) return rc;
+    if ((rc = ensure(ctx->slot_start, ((size_t)pl.slots + 1) * 4))) return rc;
+  }
+
+  BuildParams bp;
+  MatchParams mp;
+  bool has_lut;
+  fill_params(t, L, pl, d_jobs, d_order, n_jobs, (uint4*)ctx->tabs.p, (uint32_t*)ctx->counter.p,
+              (uint32_t*)ctx->group_nact.p, bp, mp, has_lut);
   mp.part_cnt = (uint32_t*)ctx->part_cnt.p;
   mp.win_rows = (uint32_t*)ctx->win_rows.p;
   mp.slot_start = (uint32_t*)ctx->slot_start.p;
-  mp.wps = wps;
   mp.bits = d_bits;
 
-  std::pair<cudaEvent_t, cudaEvent_t>* tev = nullptr;
+  StepEvents* tev = nullptr;
   if (ctx->timing) {
     if (ctx->timing_used == ctx->timing_events.size()) {
-      std::pair<cudaEvent_t, cudaEvent_t> pr;
-      CK(cudaEventCreate(&pr.first));
-      CK(cudaEventCreate(&pr.second));
-      ctx->timing_events.push_back(pr);
+      StepEvents ev;
+      for (cudaEvent_t& e : ev.e) CK(cudaEventCreate(&e));
+      ctx->timing_events.push_back(ev);
     }
     tev = &ctx->timing_events[ctx->timing_used++];
-    CK(cudaEventRecord(tev->first, ctx->stream));
+    tev->n = bitmap ? 3 : 4;
+    CK(cudaEventRecord(tev->e[0], ctx->stream));
   }
-  cudaError_t e = bitmap ? launch_match<MODE_BITMAP>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
-                         : launch_match<MODE_COUNT>(L->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  k_build_tables<<<build_grid(pl), 256, 0, ctx->stream>>>(bp);
+  CK(cudaGetLastError());
+  ctx->launches++;
+  if (tev) CK(cudaEventRecord(tev->e[1], ctx->stream));
+
+  cudaError_t e = bitmap ? launch_match<MODE_BITMAP>(row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
+                         : launch_match<MODE_COUNT>(row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
-  if (tev) CK(cudaEventRecord(tev->second, ctx->stream));
+  if (tev) CK(cudaEventRecord(tev->e[2], ctx->stream));
   ctx->launches++;
 
   if (!bitmap) {
     ExtractParams gp;
+    memset(&gp, 0, sizeof gp);
     gp.pc = pl.pc;
     gp.win_rows = mp.win_rows;
     gp.slot_start = mp.slot_start;
     gp.wps = mp.wps;
+    gp.group_nact = mp.group_nact;
     gp.part_cnt = mp.part_cnt;
     gp.price = t->price;
+    gp.job_order = d_order;
     gp.n_jobs = n_jobs;
     gp.k = k;
     gp.slots = pl.slots;
     gp.slots_a = pl.pc.pa * MATCH_WARPS;
-    gp.rows16 = reinterpret_cast<const uint16_t*>(t->rows);
+    gp.rows = t->rows;
     gp.tabs = mp.tabs;
     gp.recs = d_jobs;
     for (uint32_t c = 0; c < DSM_MAX_COLS; ++c) { gp.lut[c] = mp.lut[c]; gp.base[c] = mp.base[c]; }
@@ -365,6 +408,8 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     gp.n_used = L->n_used;
     gp.n_entries = pl.lay.n_entries;
     gp.rec_words = L->rec_words;
+    gp.live_a = mp.live_a;
+    gp.live_b = mp.live_b;
     gp.out_idx = d_idx;
     gp.out_cnt = d_cnt;
     gp.out_max = d_max;
@@ -374,7 +419,26 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     else k_extract<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
     CK(cudaGetLastError());
     ctx->launches++;
+    if (tev) CK(cudaEventRecord(tev->e[3], ctx->stream));
   }
+  return 0;
+}
+
+// Host-buffer entry points: layout->job_order is a host array; validate that it is a permutation
+// (a bad one would make the kernels write outside the result buffers) and copy it to the device.
+static int upload_order(dsm_ctx* ctx, const dsm_layout* L, uint32_t n_jobs, const uint32_t** d_order) {
+  *d_order = nullptr;
+  if (!L->job_order) return 0;
+  std::vector<bool> seen(n_jobs, false);
+  for (uint32_t i = 0; i < n_jobs; ++i) {
+    const uint32_t j = L->job_order[i];
+    if (j >= n_jobs || seen[j]) return fail(DSM_E_ARG, "layout.job_order is not a permutation of 0..n_jobs-1");
+    seen[j] = true;
+  }
+  int rc = ensure(ctx->d_order, (size_t)n_jobs * 4);
+  if (rc) return rc;
+  CK(cudaMemcpyAsync(ctx->d_order.p, L->job_order, (size_t)n_jobs * 4, cudaMemcpyHostToDevice, ctx->stream));
+  *d_order = (const uint32_t*)ctx->d_order.p;
   return 0;
 }
 
@@ -391,7 +455,7 @@ int dsm_ctx_create(int device, void* stream, dsm_ctx** out) {
   if (e != cudaSuccess || n == 0)
     return fail(DSM_E_NO_DEVICE, "no CUDA device: %s", cudaGetErrorString(e));
   if (device < 0 || device >= n) return fail(DSM_E_ARG, "device ordinal out of range");
-  CK(cudaSetDevice(device));
+  USE_DEVICE(device);
   dsm_ctx* c = new (std::nothrow) dsm_ctx();
   if (!c) return fail(DSM_E_ARG, "out of host memory");
   c->device = device;
@@ -407,19 +471,24 @@ int dsm_ctx_create(int device, void* stream, dsm_ctx** out) {
   e = cudaGetDeviceProperties(&prop, device);
   if (e != cudaSuccess) { delete c; return fail(DSM_E_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e)); }
   c->sm_count = prop.multiProcessorCount;
+  // tuning knobs are read here, once: a stray variable cannot change a running scheduler
+  if (const char* v = getenv("DSM_REP_SHIFT")) c->force_rep = atoi(v);
+  c->no_direct = getenv("DSM_NO_DIRECT_FILL") != nullptr;
+  c->force_direct = getenv("DSM_FORCE_DIRECT_FILL") != nullptr;
+  if (const char* v = getenv("DSM_UNITS_PER_CTA")) c->units_per_cta = (uint32_t)atoi(v);
   *out = c;
   return 0;
 }
 
 int dsm_ctx_destroy(dsm_ctx* ctx) {
   if (!ctx) return 0;
-  cudaSetDevice(ctx->device);
+  DeviceGuard guard_(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->win_rows, &ctx->slot_start, &ctx->d_jobs,
-                    &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
+  DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->win_rows, &ctx->slot_start, &ctx->group_nact,
+                    &ctx->d_jobs, &ctx->d_order, &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);
-  for (auto& pr : ctx->timing_events) { cudaEventDestroy(pr.first); cudaEventDestroy(pr.second); }
+  for (auto& ev : ctx->timing_events) for (cudaEvent_t e : ev.e) cudaEventDestroy(e);
   if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
   delete ctx;
   return 0;
@@ -427,13 +496,15 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
 
 int dsm_table_create(dsm_ctx* ctx, const dsm_table_desc* desc, const uint16_t* rows,
                      const double* price, const uint32_t* gpu_entries, const uint32_t* bk_entries,
-                     dsm_table** out) {
+                     const uint32_t* pair_entries, dsm_table** out) {
   if (!ctx || !desc || !rows || !out) return fail(DSM_E_ARG, "NULL argument");
   if (desc->n_cols != 8 && desc->n_cols != 16) return fail(DSM_E_ARG, "n_cols must be 8 or 16");
   if (desc->n_rows == 0 || desc->n_rows % 32 || desc->split_row % 32 || desc->split_row > desc->n_rows)
     return fail(DSM_E_ARG, "n_rows / split_row must be multiples of 32, split_row <= n_rows");
+  if (desc->n_live_a > desc->split_row || desc->n_live_b > desc->n_rows - desc->split_row)
+    return fail(DSM_E_ARG, "n_live_a / n_live_b exceed their segments");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   dsm_table* t = new (std::nothrow) dsm_table();
   if (!t) return fail(DSM_E_ARG, "out of host memory");
   memset(t, 0, sizeof *t);
@@ -462,8 +533,17 @@ int dsm_table_create(dsm_ctx* ctx, const dsm_table_desc* desc, const uint16_t* r
       if (e == cudaSuccess) e = cudaMemcpyAsync(t->bk_entries, bk_entries, b, cudaMemcpyHostToDevice, ctx->stream);
     }
   }
+  if (e == cudaSuccess && desc->n_pair_entries) {
+    if (!pair_entries) { e = cudaErrorInvalidValue; }
+    else {
+      const size_t b = (size_t)desc->n_pair_entries * 4;
+      e = cudaMalloc((void**)&t->pair_entries, b);
+      if (e == cudaSuccess) e = cudaMemcpyAsync(t->pair_entries, pair_entries, b, cudaMemcpyHostToDevice, ctx->stream);
+    }
+  }
   if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
   if (e != cudaSuccess) {
+    if (t->pair_entries) cudaFree(t->pair_entries);
     if (t->rows) cudaFree(t->rows);
     if (t->price) cudaFree(t->price);
     if (t->gpu_entries) cudaFree(t->gpu_entries);
@@ -477,7 +557,8 @@ int dsm_table_create(dsm_ctx* ctx, const dsm_table_desc* desc, const uint16_t* r
 
 int dsm_table_destroy(dsm_table* t) {
   if (!t) return 0;
-  cudaSetDevice(t->device);
+  DeviceGuard guard_(t->device);
+  if (t->pair_entries) cudaFree(t->pair_entries);
   if (t->rows) cudaFree(t->rows);
   if (t->price) cudaFree(t->price);
   if (t->gpu_entries) cudaFree(t->gpu_entries);
@@ -490,7 +571,7 @@ int dsm_lut_upload(dsm_ctx* ctx, uint32_t column, const uint16_t* lut, uint32_t 
                    const uint16_t** dev_out) {
   if (!ctx || !lut || !dev_out || column >= DSM_MAX_COLS || n == 0) return fail(DSM_E_ARG, "bad argument");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   int rc = ensure(ctx->lut[column], (size_t)n * 2);
   if (rc) return rc;
   CK(cudaMemcpyAsync(ctx->lut[column].p, lut, (size_t)n * 2, cudaMemcpyHostToDevice, ctx->stream));
@@ -504,14 +585,16 @@ int dsm_match_topk_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layou
                        uint32_t* d_cnt, uint32_t* d_max) {
   if (!ctx || !t || !layout || !d_jobs || !d_idx || !d_cnt || !d_max) return fail(DSM_E_ARG, "NULL argument");
   std::lock_guard<std::mutex> g(ctx->mu);
-  return run_match(ctx, t, layout, d_jobs, n_jobs, k, false, d_idx, d_cnt, d_max, nullptr);
+  USE_DEVICE(ctx->device);
+  return run_match(ctx, t, layout, d_jobs, layout->job_order, n_jobs, k, false, d_idx, d_cnt, d_max, nullptr);
 }
 
 int dsm_match_bitmap_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
                          const uint32_t* d_jobs, uint32_t n_jobs, uint32_t* d_bits) {
   if (!ctx || !t || !layout || !d_jobs || !d_bits) return fail(DSM_E_ARG, "NULL argument");
   std::lock_guard<std::mutex> g(ctx->mu);
-  return run_match(ctx, t, layout, d_jobs, n_jobs, 1, true, nullptr, nullptr, nullptr, d_bits);
+  USE_DEVICE(ctx->device);
+  return run_match(ctx, t, layout, d_jobs, layout->job_order, n_jobs, 1, true, nullptr, nullptr, nullptr, d_bits);
 }
 
 int dsm_match_topk(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const uint32_t* jobs,
@@ -519,8 +602,10 @@ int dsm_match_topk(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, c
                    uint32_t* out_max) {
   if (!ctx || !t || !layout || !jobs || !out_idx || !out_cnt || !out_max) return fail(DSM_E_ARG, "NULL argument");
   if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
+  if (k == 0 || k > 4096) return fail(DSM_E_ARG, "k must be in 1..4096");
+  if (layout->rec_words < 3 || layout->rec_words > 65536) return fail(DSM_E_ARG, "layout.rec_words out of range");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   int rc;
   const size_t jb = (size_t)n_jobs * layout->rec_words * 4;
   if ((rc = ensure(ctx->d_jobs, jb))) return rc;
@@ -528,7 +613,9 @@ int dsm_match_topk(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, c
   if ((rc = ensure(ctx->d_cnt, (size_t)n_jobs * 4))) return rc;
   if ((rc = ensure(ctx->d_max, (size_t)n_jobs * 4))) return rc;
   CK(cudaMemcpyAsync(ctx->d_jobs.p, jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
-  rc = run_match(ctx, t, layout, (const uint32_t*)ctx->d_jobs.p, n_jobs, k, false,
+  const uint32_t* d_order = nullptr;
+  if ((rc = upload_order(ctx, layout, n_jobs, &d_order))) return rc;
+  rc = run_match(ctx, t, layout, (const uint32_t*)ctx->d_jobs.p, d_order, n_jobs, k, false,
                  (uint32_t*)ctx->d_idx.p, (uint32_t*)ctx->d_cnt.p, (uint32_t*)ctx->d_max.p, nullptr);
   if (rc) return rc;
   CK(cudaMemcpyAsync(out_idx, ctx->d_idx.p, (size_t)n_jobs * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -542,15 +629,18 @@ int dsm_match_bitmap(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
                      uint32_t n_jobs, uint32_t* out_bits) {
   if (!ctx || !t || !layout || !jobs || !out_bits) return fail(DSM_E_ARG, "NULL argument");
   if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
+  if (layout->rec_words < 3 || layout->rec_words > 65536) return fail(DSM_E_ARG, "layout.rec_words out of range");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   int rc;
   const size_t jb = (size_t)n_jobs * layout->rec_words * 4;
   const size_t bb = (size_t)n_jobs * (t->desc.n_rows / 32) * 4;
   if ((rc = ensure(ctx->d_jobs, jb))) return rc;
   if ((rc = ensure(ctx->d_bits, bb))) return rc;
   CK(cudaMemcpyAsync(ctx->d_jobs.p, jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
-  rc = run_match(ctx, t, layout, (const uint32_t*)ctx->d_jobs.p, n_jobs, 1, true, nullptr, nullptr,
+  const uint32_t* d_order = nullptr;
+  if ((rc = upload_order(ctx, layout, n_jobs, &d_order))) return rc;
+  rc = run_match(ctx, t, layout, (const uint32_t*)ctx->d_jobs.p, d_order, n_jobs, 1, true, nullptr, nullptr,
                  nullptr, (uint32_t*)ctx->d_bits.p);
   if (rc) return rc;
   CK(cudaMemcpyAsync(out_bits, ctx->d_bits.p, bb, cudaMemcpyDeviceToHost, ctx->stream));
@@ -568,7 +658,7 @@ static int merge_shards(dsm_ctx* ctx, uint32_t n_shards, uint32_t n_jobs, uint32
     return fail(DSM_E_ARG, "NULL argument");
   if (n_shards == 0 || n_jobs == 0 || k == 0) return fail(DSM_E_ARG, "empty merge");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   k_merge_shards<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
       n_shards, n_jobs, k, d_idx_all, d_cnt_all, d_max_all, d_maxprice_all, shard_stride_bytes,
       d_shard_base, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
@@ -610,7 +700,7 @@ int dsm_merge_shards_interleaved_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n
   if (chunk_rows == 0) return fail(DSM_E_ARG, "chunk_rows must be > 0");
   if (shard_stride_bytes == 0 || shard_stride_bytes % 8) return fail(DSM_E_ARG, "shard stride must be a non-zero multiple of 8");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   k_merge_shards_interleaved<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
       n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
       reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
@@ -623,7 +713,7 @@ int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_row
                          double* d_out) {
   if (!ctx || !t || !d_rows || !d_out || n == 0) return fail(DSM_E_ARG, "bad argument");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   k_gather_price<<<(n + 255) / 256, 256, 0, ctx->stream>>>(t->price, d_rows, n, d_out);
   CK(cudaGetLastError());
   ctx->launches++;
@@ -632,7 +722,7 @@ int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_row
 
 int dsm_sync(dsm_ctx* ctx) {
   if (!ctx) return fail(DSM_E_ARG, "NULL ctx");
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   CK(cudaStreamSynchronize(ctx->stream));
   return 0;
 }
@@ -661,16 +751,35 @@ int dsm_timing_enable(dsm_ctx* ctx, int on) {
 int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches) {
   if (!ctx || !total_ms || !n_launches) return fail(DSM_E_ARG, "NULL argument");
   std::lock_guard<std::mutex> g(ctx->mu);
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   CK(cudaStreamSynchronize(ctx->stream));
   double sum = 0.0;
   for (size_t i = 0; i < ctx->timing_used; ++i) {
     float ms = 0.f;
-    CK(cudaEventElapsedTime(&ms, ctx->timing_events[i].first, ctx->timing_events[i].second));
+    CK(cudaEventElapsedTime(&ms, ctx->timing_events[i].e[1], ctx->timing_events[i].e[2]));
     sum += ms;
   }
   *total_ms = sum;
   *n_launches = (uint32_t)ctx->timing_used;
+  ctx->timing_used = 0;
+  return 0;
+}
+
+int dsm_timing_read_parts(dsm_ctx* ctx, double parts_ms[3], uint32_t* n_calls) {
+  if (!ctx || !parts_ms || !n_calls) return fail(DSM_E_ARG, "NULL argument");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  CK(cudaStreamSynchronize(ctx->stream));
+  parts_ms[0] = parts_ms[1] = parts_ms[2] = 0.0;
+  for (size_t i = 0; i < ctx->timing_used; ++i) {
+    const StepEvents& ev = ctx->timing_events[i];
+    for (int q = 0; q + 1 < ev.n; ++q) {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, ev.e[q], ev.e[q + 1]));
+      parts_ms[q] += ms;
+    }
+  }
+  *n_calls = (uint32_t)ctx->timing_used;
   ctx->timing_used = 0;
   return 0;
 }
@@ -719,58 +828,37 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
   std::lock_guard<std::mutex> g(ctx->mu);
   Plan pl;
-  int rc = make_plan(ctx, t, layout, n_jobs, 0u, pl);  // pure arithmetic, allocates nothing
+  int rc = make_plan(ctx, t, layout, n_jobs, pl);  // pure arithmetic, allocates nothing
   if (rc) return rc;
   const bool row32 = t->desc.n_cols == 16;
-  if (row32 && layout->n_used < 5) return fail(DSM_E_ARG, "16-column tables need n_used >= 5");
 
-  // layout of the array: [0,256) work counter, then the tables [groups][entries] x 16 bytes
+  // layout of the array: [0,256) work counter, then one word per job group (columns the group
+  // needs, written and read by k_match), then the tables [groups][entries] x 16 bytes
+  const size_t nact_bytes = ((size_t)pl.n_groups * 4 + 255) / 256 * 256;
   const size_t table_bytes = (size_t)pl.n_groups * pl.lay.n_entries * 16;
-  if (256 + table_bytes > DSM_STATIC_SCRATCH_BYTES) {
+  if (256 + nact_bytes + table_bytes > DSM_STATIC_SCRATCH_BYTES) {
     char msg[256];
     snprintf(msg, sizeof msg,
              "dsm_match_bitmap_static: %u job groups x %u dictionary entries need %zu bytes of "
              "scratch, the built-in array holds %u; split the batch or use dsm_match_bitmap_dev",
-             pl.n_groups, pl.lay.n_entries, 256 + table_bytes, (unsigned)DSM_STATIC_SCRATCH_BYTES);
+             pl.n_groups, pl.lay.n_entries, 256 + nact_bytes + table_bytes, (unsigned)DSM_STATIC_SCRATCH_BYTES);
     return fail(DSM_E_TOO_LARGE, "%s", msg);
   }
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   unsigned char* scratch = nullptr;
   if ((rc = static_scratch_address(ctx->device, &scratch))) return rc;
 
   BuildParams bp;
-  bp.lay = pl.lay;
-  bp.recs = d_jobs;
-  bp.n_jobs = n_jobs;
-  bp.gpu_entries = t->gpu_entries;
-  bp.bk_entries = t->bk_entries;
-  bp.tabs = reinterpret_cast<uint4*>(scratch + 256);
-  bp.work_counter = reinterpret_cast<uint32_t*>(scratch);  // k_build_tables zeroes it
+  MatchParams mp;
+  bool has_lut;
+  fill_params(t, layout, pl, d_jobs, layout->job_order, n_jobs, reinterpret_cast<uint4*>(scratch + 256 + nact_bytes),
+              reinterpret_cast<uint32_t*>(scratch) /* k_build_tables zeroes it */,
+              reinterpret_cast<uint32_t*>(scratch + 256), bp, mp, has_lut);
+  mp.bits = d_bits;
   k_build_tables<<<build_grid(pl), 256, 0, ctx->stream>>>(bp);
   CK(cudaGetLastError());
   ctx->launches++;
-
-  MatchParams mp;
-  memset(&mp, 0, sizeof mp);
-  mp.rows = t->rows;
-  mp.tabs = bp.tabs;
-  mp.recs = d_jobs;
-  bool has_lut = false;
-  for (uint32_t c = 0; c < layout->n_used; ++c) {
-    mp.lut[c] = layout->lut[c];
-    has_lut = has_lut || layout->lut[c] != nullptr;
-    mp.base[c] = pl.lay.base[c];
-  }
-  mp.pc = pl.pc;
-  mp.rec_words = layout->rec_words;
-  mp.n_entries = pl.lay.n_entries;
-  mp.rep_shift = pl.rep_shift;
-  mp.direct_fill = pl.direct_fill;
-  mp.n_jobs = n_jobs;
-  mp.slots = pl.slots;
-  mp.work_counter = bp.work_counter;
-  mp.bits = d_bits;
-  cudaError_t e = launch_match<MODE_BITMAP>(layout->n_used, row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  cudaError_t e = launch_match<MODE_BITMAP>(row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   ctx->launches++;
   return 0;
@@ -779,7 +867,7 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
 #ifdef DSM_CTA_TIMING
 // debug builds only: copy the per-CTA (start ns, end ns, SM id) triples of the last k_match
 int dsm_debug_cta_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_ctas) {
-  CK(cudaSetDevice(ctx->device));
+  USE_DEVICE(ctx->device);
   CK(cudaStreamSynchronize(ctx->stream));
   CK(cudaMemcpyFromSymbol(out, g_cta_times, (size_t)n_ctas * 3 * 8));
   return 0;
@@ -789,8 +877,9 @@ int dsm_debug_cta_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_ctas) 
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, uint32_t n_jobs,
                    uint32_t k, uint32_t out[8]) {
   if (!ctx || !t || !layout || !out) return fail(DSM_E_ARG, "NULL argument");
+  (void)k;  // the geometry of a call does not depend on k
   Plan pl;
-  int rc = make_plan(ctx, t, layout, n_jobs, k, pl);
+  int rc = make_plan(ctx, t, layout, n_jobs, pl);
   if (rc) return rc;
   out[0] = pl.grid;
   out[1] = pl.pc.count();

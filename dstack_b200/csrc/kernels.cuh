@@ -74,13 +74,11 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src, uint32
       "l"(src), "r"(bytes), "r"(smem_u32(bar))
       : "memory");
 }
-// 128-bit read-only row load.  Rows are loaded into registers two blocks ahead of their use;
-// PREFETCH_BLOCKS > 2 additionally requests the lines into L1 that many blocks ahead.  With
-// three CTAs' tables in shared memory only ~24 KB of L1 is left per SM, so most prefetched
-// lines are gone again before use (ncu: 8 % L1 hit rate), but the request still pulls the row
-// from DRAM into L2 early.  Measured (config 3 kernel time): table cold in DRAM 0.226 ms
-// without, 0.203 ms with a distance of 4 or 6; table already in L2 0.187 vs 0.191 ms; 16 M rows
-// (larger than L2) 3.08 vs 3.15 ms.  The cold case is the one a scheduler tick sees.
+// 128-bit read-only row load.  Rows are loaded into registers two blocks ahead of their use,
+// and every warp asks for the lines of its next window (15 blocks) to be brought into L2 while
+// it works on the current one: with three CTAs' tables in shared memory only ~24 KB of L1 is left
+// per SM, so the point of the prefetch is to pull rows out of DRAM early (measured in round 1 on
+// config 3 with the table cold in DRAM: 0.226 ms without any prefetch, 0.203 ms with).
 __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
   uint4 r;
   asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];"
@@ -88,17 +86,15 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
                : "l"(p));
   return r;
 }
-__device__ __forceinline__ void prefetch_l1(const void* p) {
-  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));  // prefetch.global.L2 measured the same
+__device__ __forceinline__ void prefetch_l2(const void* p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
 }
-#ifndef PREFETCH_BLOCKS
-#define PREFETCH_BLOCKS 4
-#endif
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 r;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];"
                : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-               : "r"(addr));
+               : "r"(addr)
+               : "memory");
   return r;
 }
 
@@ -107,6 +103,7 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // partner's word left by s (lanes with bit s clear) or right by s (the others) and keeps its
 // own bits under `keep`.  Afterwards lane j holds in bit l what lane l held in bit j.
 struct XposeCtl {
+  uint32_t sel[2];  // steps 0, 1 move half-words / bytes: one byte permute each
   uint32_t rot[5];
   uint32_t keep[5];
 };
@@ -119,6 +116,11 @@ __device__ __forceinline__ void transpose_setup(XposeCtl& c, uint32_t lane) {
     c.rot[i] = upper ? 32u - s : s;
     c.keep[i] = upper ? ~lowmask[i] : lowmask[i];
   }
+  // __byte_perm(own, partner, sel): lanes with bit 16 (8) clear keep their low half-word (even
+  // bytes) and take the partner's low half-word (even bytes) into the high one (odd bytes); the
+  // other lanes keep the high part and take the partner's high part into the low one
+  c.sel[0] = (lane & 16u) ? 0x3276u : 0x5410u;
+  c.sel[1] = (lane & 8u) ? 0x3715u : 0x6240u;
 }
 
 // ------------------------------------------------------------------------------------------
@@ -140,31 +142,50 @@ struct LayoutDev {
 struct BuildParams {
   LayoutDev lay;
   const uint32_t* recs;
+  const uint32_t* job_order;  // evaluation slot -> job (nullptr: identity); see dsm_layout.job_order
   uint32_t n_jobs;
   const uint32_t* gpu_entries;
   const uint32_t* bk_entries;
+  const uint32_t* pair_entries;
   uint4* tabs;             // [groups][n_entries] x 4 words
   uint32_t* work_counter;  // reset here for the k_match that follows in the stream
 };
 
-// Pieces of the row axis (see the header comment); shared by k_match and k_extract.
+// count mode: a window is WIN_BLOCKS 32-row blocks; a 4-bit counter per (row lane, job) holds it
+#define WIN_PLANES 4
+#define WIN_BLOCKS 15
+#define EXTRACT_PENDING 16  // windows k_extract queues before it evaluates their candidate rows
+#ifndef EXTRACT_LANE_ROWS
+#define EXTRACT_LANE_ROWS 2  // candidate rows per lane and evaluation step (their loads overlap; 4 measured slower)
+#endif
+
+// Pieces of the row axis (see the header comment); shared by k_match and k_extract.  Every warp
+// of a piece gets the same whole number of windows (wpw), counted from the start of the piece's
+// segment, so the eight warps of a unit reach its closing barrier together and only the last
+// piece of a segment has short or empty shares.
 struct Pieces {
   uint32_t n_groups;
   uint32_t n_blocks;     // 32-row blocks of the table
   uint32_t split_block;  // first block of the second segment
   uint32_t pa, pb;       // pieces in the first / second segment
+  uint32_t wpw;          // windows per warp
   __host__ __device__ uint32_t per_group() const { return pa + pb; }
   __host__ __device__ uint32_t count() const { return n_groups * (pa + pb); }
-  __host__ __device__ void blocks_of(uint32_t pos, uint32_t& lo, uint32_t& hi) const {
-    if (pos < pa) {
-      lo = (uint32_t)((unsigned long long)split_block * pos / pa);
-      hi = (uint32_t)((unsigned long long)split_block * (pos + 1) / pa);
-    } else {
-      const unsigned long long nb = n_blocks - split_block;
-      const uint32_t i = pos - pa;
-      lo = split_block + (uint32_t)(nb * i / pb);
-      hi = split_block + (uint32_t)(nb * (i + 1) / pb);
-    }
+  __host__ __device__ static uint32_t windows(uint32_t blocks) { return (blocks + WIN_BLOCKS - 1) / WIN_BLOCKS; }
+  // pieces needed for `blocks` blocks when every warp takes wpw windows
+  __host__ __device__ static uint32_t pieces_for(uint32_t blocks, uint32_t wpw) {
+    const uint32_t per_piece = wpw * MATCH_WARPS;
+    return (windows(blocks) + per_piece - 1) / per_piece;
+  }
+  // blocks [b0, b1) of warp `warp` of piece `pos`
+  __host__ __device__ void warp_blocks(uint32_t pos, uint32_t warp, uint32_t& b0, uint32_t& b1) const {
+    uint32_t seg_lo = 0, seg_hi = split_block, i = pos;
+    if (pos >= pa) { seg_lo = split_block; seg_hi = n_blocks; i = pos - pa; }
+    const unsigned long long w0 = ((unsigned long long)i * MATCH_WARPS + warp) * wpw;  // first window
+    const unsigned long long x0 = seg_lo + w0 * WIN_BLOCKS;
+    const unsigned long long x1 = x0 + (unsigned long long)wpw * WIN_BLOCKS;
+    b0 = x0 < seg_hi ? (uint32_t)x0 : seg_hi;
+    b1 = x1 < seg_hi ? (uint32_t)x1 : seg_hi;
   }
 };
 
@@ -172,49 +193,47 @@ struct MatchParams {
   const uint4* rows;
   const uint4* tabs;
   const uint32_t* recs;
+  const uint32_t* job_order;  // evaluation slot -> job (nullptr: identity)
   const uint16_t* lut[DSM_MAX_COLS];
   uint32_t base[DSM_MAX_COLS];
   Pieces pc;
+  uint32_t n_used;       // columns of the call
   uint32_t rec_words;
   uint32_t n_entries;
-  uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0..3)
+  uint32_t dead_entry;   // table entry every job rejects by construction (padding rows), or ~0
+  uint32_t live_a, live_b;  // rows >= live_a in the first segment / >= live_b in the second are padding
+  uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0 or 3)
   uint32_t direct_fill;  // 1: the 8 copies fit but no staging copy beside them; the threads fill the
                          // copies straight from global memory instead of fanning out a TMA-staged table
   uint32_t n_jobs;
   uint32_t slots;        // slots per job = pieces per group * 8
   uint32_t* work_counter;
-  uint32_t* part_cnt;    // count mode: [jobs_pad][slots] matches per slot
+  uint32_t* part_cnt;    // count mode: [jobs_pad][slots] matches per slot (indexed by evaluation slot)
   uint32_t* bits;        // bitmap mode: [n_jobs][n_blocks]
   uint32_t* win_rows;    // count mode: [groups][slots][wps][128]: per window of WIN_BLOCKS blocks and job,
                          // the row lanes (row mod 32) with at least one match
   uint32_t wps;          // count mode: windows reserved per slot
   uint32_t* slot_start;  // count mode: [slots + 1] first block of every slot, then n_blocks
+  uint32_t* group_nact;  // [groups] leading columns k_match gathered for the group (k_extract re-uses it)
 };
 
 // k_match modes
 #define MODE_BITMAP 1  // every match word, job-major
 #define MODE_COUNT 2   // counts per slot and window only; k_extract re-evaluates the few rows it needs
-// count mode: a 4-bit vertical counter per (row lane, job bit) holds up to 15 blocks
-#ifndef WIN_PLANES
-#define WIN_PLANES 4
-#endif
-#define WIN_BLOCKS ((1 << WIN_PLANES) - 1)
-#define EXTRACT_PENDING 16  // windows k_extract queues before it evaluates their candidate rows
-#ifndef EXTRACT_LANE_ROWS
-#define EXTRACT_LANE_ROWS 2  // candidate rows per lane and evaluation step (their loads overlap; 4 measured slower)
-#endif
 
 struct ExtractParams {
   const uint32_t* part_cnt;
   const double* price;
+  const uint32_t* job_order;
   uint32_t n_jobs, k, slots, slots_a;  // slots below slots_a belong to the first segment
   // candidate rows are evaluated for one job from the global copies of rows and tables
-  const uint16_t* rows16;
+  const uint4* rows;
   const uint4* tabs;
   const uint32_t* recs;
   const uint16_t* lut[DSM_MAX_COLS];
   uint32_t base[DSM_MAX_COLS];
   uint32_t n_cols, n_used, n_entries, rec_words;
+  uint32_t live_a, live_b;
   uint32_t* out_idx;
   uint32_t* out_cnt;
   uint32_t* out_max;
@@ -223,6 +242,7 @@ struct ExtractParams {
   const uint32_t* win_rows;
   uint32_t wps;
   const uint32_t* slot_start;
+  const uint32_t* group_nact;
 };
 
 // ------------------------------------------------------------------------------------------
@@ -232,15 +252,20 @@ struct ExtractParams {
 
 #define BUILD_CHUNK 64u
 
+__device__ __forceinline__ bool range_accepts(uint32_t word, uint32_t e) {
+  return e >= (word & 0xFFFFu) && e <= (word >> 16);
+}
+
 __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
   const uint32_t tile = blockIdx.x;
   const uint32_t col = blockIdx.y;
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warp = threadIdx.x >> 5;
   if (tile == 0 && col == 0 && blockIdx.z == 0 && threadIdx.x == 0) *p.work_counter = 0u;
-  const uint32_t job = tile * 32u + lane;
-  const bool live = job < p.n_jobs;
-  const uint32_t* rec = p.recs + (size_t)(live ? job : 0) * p.lay.rec_words + p.lay.rec_off[col];
+  const uint32_t slot = tile * 32u + lane;
+  const bool live = slot < p.n_jobs;
+  const uint32_t job = live ? (p.job_order ? p.job_order[slot] : slot) : 0u;
+  const uint32_t* rec = p.recs + (size_t)job * p.lay.rec_words + p.lay.rec_off[col];
   const uint32_t kind = p.lay.kind[col];
   const uint32_t card = p.lay.card[col];
   uint4* out = p.tabs + (size_t)(tile / TPG) * p.lay.n_entries + p.lay.base[col];
@@ -260,11 +285,19 @@ __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
     bool ok = false;
     if (live) {
       if (kind == DSM_COL_RANGE) {
-        const uint32_t lo = r0 & 0xFFFFu, hi = r0 >> 16;
-        ok = (e >= lo && e <= hi);
+        ok = range_accepts(r0, e);
         if ((p.lay.flags[col] & DSM_COLF_NULL_PASSES) && e == card - 1u) ok = true;
       } else if (kind == DSM_COL_BITSET) {
         ok = (rec[e >> 5] >> (e & 31u)) & 1u;
+      } else if (kind == DSM_COL_PAIR) {
+        // entry = (ordinal of member A | ordinal of member B << 16); member A's predicate is a
+        // range word or (DSM_COLF_PAIR_A_BITSET) a bitset of aux words, member B's a range word
+        const uint32_t ent = p.pair_entries[e];
+        const uint32_t a = ent & 0xFFFFu, b = ent >> 16;
+        const uint32_t aw = p.lay.aux[col];  // words of member A's predicate
+        if (p.lay.flags[col] & DSM_COLF_PAIR_A_BITSET) ok = (rec[a >> 5] >> (a & 31u)) & 1u;
+        else ok = range_accepts(r0, a);
+        ok = ok && range_accepts(rec[aw], b);
       } else if (kind == DSM_COL_GPU) {
         const uint32_t* ent = p.gpu_entries + (size_t)e * DSM_GPU_ENTRY_WORDS;
         const uint32_t e0 = ent[0], e1 = ent[1], e2 = ent[2];
@@ -314,53 +347,60 @@ struct RowCodes {
   uint32_t w[(NC + 1) / 2];
 };
 
-// `rows` already points at this lane's row of block 0; `row` is the first row of the block.
+// `rows` already points at this lane's row of the block.
 template <int NC, bool ROW32>
-__device__ __forceinline__ void load_row(const uint4* rows, uint32_t row, RowCodes<NC>& rc) {
+__device__ __forceinline__ void load_row(const uint4* rows, RowCodes<NC>& rc) {
   if constexpr (!ROW32) {
-    const uint4 v = ldg_stream(rows + row);
-    const uint32_t t[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-    for (int i = 0; i < (NC + 1) / 2; ++i) rc.w[i] = t[i];
+    const uint4 v = ldg_stream(rows);
+    rc.w[0] = v.x; rc.w[1] = v.y; rc.w[2] = v.z; rc.w[3] = v.w;
   } else {
-    const uint4 v0 = ldg_stream(rows + 2 * (size_t)row);
-    uint4 v1 = make_uint4(0, 0, 0, 0);
-    if constexpr (NC > 8) v1 = ldg_stream(rows + 2 * (size_t)row + 1);
-    const uint32_t t[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
-#pragma unroll
-    for (int i = 0; i < (NC + 1) / 2; ++i) rc.w[i] = t[i];
+    const uint4 v0 = ldg_stream(rows);
+    const uint4 v1 = ldg_stream(rows + 1);
+    rc.w[0] = v0.x; rc.w[1] = v0.y; rc.w[2] = v0.z; rc.w[3] = v0.w;
+    rc.w[4] = v1.x; rc.w[5] = v1.y; rc.w[6] = v1.z; rc.w[7] = v1.w;
   }
 }
 
-template <int NC, bool ROW32, int MODE, bool HAS_LUT, bool REP8>
+template <int V>
+struct IntC {
+  static constexpr int value = V;
+};
+
+__device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { return (a & b) | (c & (a | b)); }
+
+// NCMAX = 8 (16-byte rows) or 16 (32-byte rows); the number of columns a call uses and the number
+// a job group needs are run-time values (p.n_used, n_act).
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
   static_assert(MODE == MODE_BITMAP || MODE == MODE_COUNT, "unknown k_match mode");
   constexpr bool COUNT = MODE == MODE_COUNT;
+  constexpr uint32_t FULL = 0xFFFFFFFFu;
+  constexpr uint32_t ROW_U4 = ROW32 ? 2u : 1u;  // uint4 per row
   // shared memory: [staging: E entries][table: E entries x R copies][cut-offs: 2 x 128]
   // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
   // R = 8 copy r lies in bank group r (4 banks), lane l reads copy l%8, and the 8 lanes of every
   // quarter-warp phase of a 128-bit gather hit 8 different bank groups: no bank conflicts
-  // whatever the codes are.  R < 8 (large dictionaries) only reduces them.  When the eight
-  // copies fit but not a ninth for staging (p.direct_fill) there is no staging area: the threads
-  // fill the copies straight from global memory.
+  // whatever the codes are.  R = 1 (large dictionaries) gathers from a single copy.  When the
+  // eight copies fit but not a ninth for staging (p.direct_fill) there is no staging area: the
+  // threads fill the copies straight from global memory.
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  constexpr uint32_t rep_shift = REP8 ? 3u : 0u;
-  const bool direct_fill = REP8 && p.direct_fill != 0u;
+  const uint32_t rep_shift = p.rep_shift;
+  const bool direct_fill = rep_shift != 0u && p.direct_fill != 0u;
   uint4* s_stage = reinterpret_cast<uint4*>(smem_raw);
   uint4* s_tab = (rep_shift && !direct_fill) ? s_stage + p.n_entries : s_stage;
   uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + ((size_t)p.n_entries << rep_shift));  // [2][128]
   __shared__ __align__(8) uint64_t s_bar;
-  __shared__ uint32_t s_unit;
+  __shared__ uint32_t s_unit, s_nact;
 
   const uint32_t tid = threadIdx.x;
   const uint32_t lane = tid & 31u;
-  const uint32_t warp = tid >> 5;
+  const uint32_t warp = __shfl_sync(FULL, tid >> 5, 0);  // provably warp-uniform for the compiler
   XposeCtl xc;
   transpose_setup(xc, lane);
 
   // Gather address of column c for a row: lane_base (table start + this lane's copy)
-  //                                      + (code << SHIFT) + (base[c] << SHIFT, warp-uniform)
-  constexpr uint32_t SHIFT = 4u + rep_shift;
+  //                                      + (code + base[c]) * stride
+  const uint32_t stride = 16u << rep_shift;
   const uint32_t lane_base = smem_u32(s_tab) + ((lane & ((1u << rep_shift) - 1u)) << 4);
 
   if (tid == 0) {
@@ -371,9 +411,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   const Pieces pc = p.pc;
   const uint32_t n_units = pc.count();
   const uint32_t n_blocks = pc.n_blocks;
-  const uint4* rows_lane = p.rows + (ROW32 ? 2u * lane : lane);  // this lane's row inside a block
+  const uint4* rows_lane = p.rows + ROW_U4 * lane;  // this lane's row inside block 0
   uint32_t parity = 0;
   uint32_t cur_group = 0xFFFFFFFFu;
+  uint32_t n_act = p.n_used;
 #ifdef DSM_CTA_TIMING
   unsigned long long dbg_t0 = 0;
   if (tid == 0) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_t0));
@@ -381,7 +422,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 
   for (;;) {
     __syncthreads();  // the previous unit is finished: table and s_unit may be overwritten
-    if (tid == 0) s_unit = atomicAdd(p.work_counter, 1u);
+    if (tid == 0) {
+      s_unit = atomicAdd(p.work_counter, 1u);
+      s_nact = 1u;
+    }
     __syncthreads();
     const uint32_t unit = s_unit;
     if (unit >= n_units) break;
@@ -397,37 +441,60 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         bulk_g2s(s_stage, p.tabs + (size_t)group * p.n_entries, bytes, &s_bar);
       }
       if (tid < JPG) {
-        const uint32_t job = group * JPG + tid;
+        const uint32_t slot_j = group * JPG + tid;
         uint32_t ca = 0, cb = 0;  // padding jobs accept nothing
-        if (job < p.n_jobs) {
-          ca = p.recs[(size_t)job * p.rec_words + 0];
-          cb = p.recs[(size_t)job * p.rec_words + 1];
+        if (slot_j < p.n_jobs) {
+          const uint32_t job = p.job_order ? p.job_order[slot_j] : slot_j;
+          ca = min(p.recs[(size_t)job * p.rec_words + 0], p.live_a);  // padding rows never pass
+          cb = min(p.recs[(size_t)job * p.rec_words + 1], p.live_b);
         }
         s_cut[tid] = ca;
         s_cut[JPG + tid] = cb;
       }
-      if (direct_fill) {  // 8 consecutive threads read the same entry: one 16-byte request per 8 lanes
-        const uint4* src = p.tabs + (size_t)group * p.n_entries;
-        const uint32_t n_copy = p.n_entries << 3;
-        for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = __ldg(src + (i >> 3));
-      } else {
+      // columns are ordered so that the ones jobs most often leave open come last; a column whose
+      // every entry is accepted by every job of this group changes nothing, so only the columns
+      // up to the last one that rejects something are gathered for this group (n_act)
+      const uint32_t nj = min(JPG, p.n_jobs - group * JPG);
+      uint32_t live[TPG];
+#pragma unroll
+      for (int t = 0; t < TPG; ++t)
+        live[t] = nj >= 32u * (t + 1) ? FULL : (nj > 32u * t ? (1u << (nj - 32u * t)) - 1u : 0u);
+      if (!direct_fill) {
         mbar_wait(&s_bar, parity);
         parity ^= 1u;
-        if (rep_shift) {  // fan the staged table out into its R interleaved copies
-          const uint32_t n_copy = p.n_entries << rep_shift;
-          for (uint32_t i = tid; i < n_copy; i += MATCH_THREADS) s_tab[i] = s_stage[i >> rep_shift];
+      }
+      // one thread per entry: read it once (from global memory, or from the TMA-staged copy) and
+      // write its R copies, lane l starting at copy l so that the eight lanes of a store phase hit
+      // eight different bank groups
+      {
+        const uint4* src = direct_fill ? p.tabs + (size_t)group * p.n_entries : s_stage;
+        uint32_t need = 0;
+        for (uint32_t e = tid; e < p.n_entries; e += MATCH_THREADS) {
+          const uint4 v = direct_fill ? __ldg(src + e) : src[e];
+          if (rep_shift) {
+#pragma unroll
+            for (uint32_t r = 0; r < 8u; ++r) s_tab[(size_t)e * 8u + ((r + lane) & 7u)] = v;
+          }
+          const bool all = ((v.x & live[0]) == live[0]) && ((v.y & live[1]) == live[1]) &&
+                           ((v.z & live[2]) == live[2]) && ((v.w & live[3]) == live[3]);
+          if (!all && e != p.dead_entry) {
+            uint32_t c = 0;
+#pragma unroll
+            for (int i = 1; i < NCMAX; ++i) c += (i < (int)p.n_used && e >= p.base[i]) ? 1u : 0u;
+            need = max(need, c + 1u);
+          }
         }
+        if (need > 1u) atomicMax(&s_nact, need);
       }
       __syncthreads();
+      n_act = s_nact;
+      if (tid == 0) p.group_nact[group] = n_act;
       cur_group = group;
     }
 
     // ---- this warp's rows of the piece
-    uint32_t lo, hi;
-    pc.blocks_of(pos, lo, hi);
-    const uint32_t len = hi - lo;
-    const uint32_t b0 = lo + (uint32_t)(((unsigned long long)len * warp) / MATCH_WARPS);
-    const uint32_t b1 = lo + (uint32_t)(((unsigned long long)len * (warp + 1)) / MATCH_WARPS);
+    uint32_t b0, b1;
+    pc.warp_blocks(pos, warp, b0, b1);
     const uint32_t slot = pos * MATCH_WARPS + warp;
     if constexpr (COUNT) {
       // k_extract reads the slots' block ranges instead of redoing this arithmetic per job:
@@ -442,24 +509,57 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     // of tile t that pass on every row of the current block; it only changes at an "event"
     // block, the block a cut-off falls into, where the per-row comparison is done.
     const uint32_t* cut_lane = s_cut + (pos >= pc.pa ? JPG : 0u) + lane;  // + 32t: job 32t+lane's cut-off
-    uint32_t full[TPG];
-    uint32_t next_evt = b0;  // forces the classification on the first block
+    uint32_t full[TPG] = {0, 0, 0, 0};
+    uint32_t next_evt = b0;
 
-    // count mode, per job (lane j, tile t): matches in this slot
-    uint32_t cnt[TPG];
+    // classify block `blk`: full[] for it and the blocks after it, the rows of jobs whose cut-off
+    // lies inside it (pw), and the next block at which a job leaves full[]
+    auto classify = [&](const uint32_t blk, uint32_t (&pw)[TPG]) -> bool {
+      const uint32_t row = blk * 32u + lane;
+      const uint32_t row_end = (blk + 1u) * 32u;
+      uint32_t nxt = 0xFFFFFFFFu;
+      uint32_t any_part = 0;
 #pragma unroll
-    for (int t = 0; t < TPG; ++t) {
-      cnt[t] = 0;
-      full[t] = 0;
-    }
+      for (int t = 0; t < TPG; ++t) {
+        const uint32_t cutv = cut_lane[t * 32];  // lane j: cut-off row of job 32t+j
+        full[t] = __ballot_sync(FULL, cutv >= row_end);
+        uint32_t part = __ballot_sync(FULL, cutv > blk * 32u && cutv < row_end);
+        any_part |= part;
+        pw[t] = 0;
+        while (part) {
+          const uint32_t j = __ffs(part) - 1;
+          part &= part - 1;
+          pw[t] |= (row < __shfl_sync(FULL, cutv, j)) ? (1u << j) : 0u;
+        }
+        if (cutv >= row_end) nxt = min(nxt, cutv >> 5);  // block where this job leaves `full`
+      }
+      next_evt = __reduce_min_sync(FULL, nxt);
+      return any_part != 0;
+    };
+    auto block_mask = [&](const uint32_t blk) -> uint4 {
+      if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
+        uint32_t pw[TPG];
+        classify(blk, pw);
+        return make_uint4(full[0] | pw[0], full[1] | pw[1], full[2] | pw[2], full[3] | pw[3]);
+      }
+      return make_uint4(full[0], full[1], full[2], full[3]);
+    };
 
-    // count mode: vertical match counters of the current window and the window's number
-    uint32_t pln[TPG][WIN_PLANES];
-    uint32_t in_win = 0, widx = 0;
+    // gather one 128-bit word group per needed column and AND them
+    auto gather_generic = [&](const RowCodes<NCMAX>& cur, uint4 m) -> uint4 {
 #pragma unroll
-    for (int t = 0; t < TPG; ++t)
-#pragma unroll
-      for (int b = 0; b < WIN_PLANES; ++b) pln[t][b] = 0;
+      for (int c = 0; c < NCMAX; ++c) {
+        if (c < (int)n_act) {
+          uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
+          if constexpr (HAS_LUT) {
+            if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+          }
+          const uint4 a = lds128(lane_base + (code + p.base[c]) * stride);
+          m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
+        }
+      }
+      return m;
+    };
 
     // four independent 32x32 bit transposes, interleaved step by step so the shuffles overlap
     auto xpose4 = [&](uint32_t (&T)[TPG]) {
@@ -467,75 +567,157 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
       for (int i = 0; i < 5; ++i) {
         uint32_t y[TPG];
 #pragma unroll
-        for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(0xFFFFFFFFu, T[t], 16u >> i);
+        for (int t = 0; t < TPG; ++t) y[t] = __shfl_xor_sync(FULL, T[t], 16u >> i);
 #pragma unroll
         for (int t = 0; t < TPG; ++t) {
-          const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
-          T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
+          if (i < 2) {  // half-word / byte exchange: one byte permute
+            T[t] = __byte_perm(T[t], y[t], xc.sel[i]);
+          } else {
+            const uint32_t moved = __funnelshift_l(y[t], y[t], xc.rot[i]);
+            T[t] = (T[t] & xc.keep[i]) | (moved & ~xc.keep[i]);
+          }
         }
       }
     };
 
-    auto process = [&](const uint32_t blk, const RowCodes<NC>& cur) {
-      uint4 m;
-      if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
-        const uint32_t row = blk * 32u + lane;
-        const uint32_t row_end = (blk + 1u) * 32u;
-        uint32_t pw[TPG] = {0, 0, 0, 0};
-        uint32_t nxt = 0xFFFFFFFFu;
-#pragma unroll
-        for (int t = 0; t < TPG; ++t) {
-          const uint32_t cutv = cut_lane[t * 32];  // lane j: cut-off row of job 32t+j
-          full[t] = __ballot_sync(0xFFFFFFFFu, cutv >= row_end);
-          uint32_t part = __ballot_sync(0xFFFFFFFFu, cutv > blk * 32u && cutv < row_end);
-          while (part) {
-            const uint32_t j = __ffs(part) - 1;
-            part &= part - 1;
-            pw[t] |= (row < __shfl_sync(0xFFFFFFFFu, cutv, j)) ? (1u << j) : 0u;
-          }
-          if (cutv >= row_end) nxt = min(nxt, cutv >> 5);  // block where this job leaves `full`
-        }
-        next_evt = __reduce_min_sync(0xFFFFFFFFu, nxt);
-        m = make_uint4(full[0] | pw[0], full[1] | pw[1], full[2] | pw[2], full[3] | pw[3]);
-      } else {
-        m = make_uint4(full[0], full[1], full[2], full[3]);
-      }
+    const uint4* rp = rows_lane + (size_t)b0 * (32u * ROW_U4);  // this lane's row of block b0
+    // ra: the current block, rb: the one after it; rc: third buffer of the unrolled windows, so
+    // that a block's codes need not be copied out of the buffer its successor's load overwrites
+    RowCodes<NCMAX> ra, rb, rc;
+    if (b0 < b1) load_row<NCMAX, ROW32>(rp, ra);
+    if (b0 + 1 < b1) load_row<NCMAX, ROW32>(rp + 32u * ROW_U4, rb);
 
-      // gather one 128-bit word group per column and AND them
-#pragma unroll
-      for (int c = 0; c < NC; ++c) {
-        uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
-        if constexpr (HAS_LUT) {
-          if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-        }
-        const uint4 a = lds128(lane_base + (code << SHIFT) + (p.base[c] << SHIFT));
-        m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
+    if constexpr (COUNT) {
+      uint32_t cnt[TPG] = {0, 0, 0, 0};  // per job (lane j, tile t): matches in this slot
+      uint32_t blk = b0, widx = 0;
+      if (b0 < b1) {
+        uint32_t pw[TPG];
+        if (classify(b0, pw)) next_evt = b0;  // a cut-off inside the first block: take the generic path
       }
-
-      if constexpr (COUNT) {
-        // add this block's match bits into the vertical counters: pln[t][b] is bit b of a
-        // counter kept per (row lane, job bit); no cross-lane traffic until the window ends
-        const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
+      while (blk < b1) {
+        const uint32_t nb = min((uint32_t)WIN_BLOCKS, b1 - blk);
+        // ask for the next window's rows (60 lines of 128 bytes with 16-byte rows) while this one
+        // is processed; lines past the end of the table are left alone
+        if (blk + WIN_BLOCKS < b1) {
+          constexpr uint32_t LINES = WIN_BLOCKS * 4u * ROW_U4;  // lines per window
+          const uint32_t first = (blk + WIN_BLOCKS) * 4u * ROW_U4;  // line index of the next window
+          const uint32_t last = n_blocks * 4u * ROW_U4;             // lines in the table
 #pragma unroll
-        for (int t = 0; t < TPG; ++t) {
-          uint32_t carry = mm[t];
-#pragma unroll
-          for (int b = 0; b < WIN_PLANES; ++b) {
-            const uint32_t up = pln[t][b] & carry;
-            pln[t][b] ^= carry;
-            carry = up;
+          for (uint32_t l = 0; l < LINES; l += 32u) {
+            const uint32_t line = first + l + lane;
+            if (l + lane < LINES && line < last)
+              prefetch_l2(reinterpret_cast<const char*>(p.rows) + (size_t)line * 128u);
           }
         }
-        if (++in_win == WIN_BLOCKS || blk + 1 == b1) {  // warp-uniform: the window is complete
-          // after the transposes lane j holds, per plane, which row lanes have that counter bit
-          // set for job 32t+j: popcounts give the window's matches, the OR of the planes the
-          // row lanes (row mod 32) that matched at all -- k_extract looks only at those rows
+        uint32_t P[TPG][WIN_PLANES];  // bit b of the number of matches per (row lane, job) in this window
+        bool fast_done = false;
+        if constexpr (!ROW32) {
+          if (nb == WIN_BLOCKS && next_evt >= blk + WIN_BLOCKS) {
+            // ---- the usual window: no cut-off inside, so full[] is constant; the 15 blocks are
+            // unrolled and their match words summed with a carry-save adder tree (11 full adders
+            // per tile and window instead of a ripple-carry add per block)
+            auto window = [&](auto na_tag) {
+              constexpr int NA = decltype(na_tag)::value;
+              uint32_t s1[TPG], p1[TPG], s2[TPG], p2[TPG], d1[TPG], d2[TPG];
+#pragma unroll
+              for (int i = 0; i < WIN_BLOCKS; ++i) {
+                const RowCodes<NCMAX>& cur = (i % 3 == 0) ? ra : (i % 3 == 1) ? rb : rc;
+                RowCodes<NCMAX>& nxt = (i % 3 == 0) ? rc : (i % 3 == 1) ? ra : rb;  // block i + 2
+                if (blk + i + 2 < b1) load_row<NCMAX, ROW32>(rp + (size_t)(i + 2) * 32u * ROW_U4, nxt);
+                uint4 m = make_uint4(full[0], full[1], full[2], full[3]);
+#pragma unroll
+                for (int c = 0; c < NA; ++c) {
+                  uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
+                  if constexpr (HAS_LUT) {
+                    if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+                  }
+                  const uint4 a = lds128(lane_base + (code + p.base[c]) * stride);
+                  m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
+                }
+                const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+                for (int t = 0; t < TPG; ++t) {
+                  if (i == 0) {
+                    s1[t] = mm[t];
+                  } else if (i & 1) {
+                    p1[t] = mm[t];
+                  } else {  // full adder of the running sum, the held word and this one
+                    const uint32_t c2 = maj3(s1[t], p1[t], mm[t]);
+                    s1[t] ^= p1[t] ^ mm[t];
+                    const int j = i / 2;  // carries 1..7 into the twos (a constant once unrolled)
+                    if (j == 1) {
+                      s2[t] = c2;
+                    } else if ((j & 1) == 0) {
+                      p2[t] = c2;
+                    } else {
+                      const uint32_t c4 = maj3(s2[t], p2[t], c2);
+                      s2[t] ^= p2[t] ^ c2;
+                      if (j == 3) d1[t] = c4;
+                      else if (j == 5) d2[t] = c4;
+                      else {
+                        P[t][2] = d1[t] ^ d2[t] ^ c4;
+                        P[t][3] = maj3(d1[t], d2[t], c4);
+                      }
+                    }
+                  }
+                }
+              }
+#pragma unroll
+              for (int t = 0; t < TPG; ++t) { P[t][0] = s1[t]; P[t][1] = s2[t]; }
+            };
+            switch (n_act) {
+              case 1: window(IntC<1>{}); break;
+              case 2: window(IntC<2>{}); break;
+              case 3: window(IntC<3>{}); break;
+              case 4: window(IntC<4>{}); break;
+              case 5: window(IntC<5>{}); break;
+              case 6: window(IntC<6>{}); break;
+              case 7: window(IntC<7>{}); break;
+              default: window(IntC<8>{}); break;
+            }
+            fast_done = true;  // 15 = 5 x 3 blocks: ra / rb again hold the next two blocks
+          }
+        }
+        if (!fast_done) {
+          // ---- a window with a cut-off inside, the short last window of a segment, or 32-byte
+          // rows: block by block, ripple-carry add into the counter planes
+#pragma unroll
+          for (int t = 0; t < TPG; ++t)
+#pragma unroll
+            for (int b = 0; b < WIN_PLANES; ++b) P[t][b] = 0;
+#pragma unroll 1
+          for (uint32_t i = 0; i < nb; ++i) {
+            const RowCodes<NCMAX> cur = ra;
+            ra = rb;
+            if (blk + i + 2 < b1) load_row<NCMAX, ROW32>(rp + (size_t)(i + 2) * 32u * ROW_U4, rb);
+            const uint4 m = gather_generic(cur, block_mask(blk + i));
+            const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
+#pragma unroll
+            for (int t = 0; t < TPG; ++t) {
+              uint32_t carry = mm[t];
+#pragma unroll
+              for (int b = 0; b < WIN_PLANES; ++b) {
+                const uint32_t up = P[t][b] & carry;
+                P[t][b] ^= carry;
+                carry = up;
+              }
+            }
+          }
+        }
+        // ---- the window is complete: after the transposes lane j holds, per plane, which row
+        // lanes have that counter bit set for job 32t+j: popcounts give the window's matches, the
+        // OR of the planes the row lanes (row mod 32) that matched at all -- k_extract looks only
+        // at those rows
+        {
           uint32_t c[TPG] = {0, 0, 0, 0}, any[TPG] = {0, 0, 0, 0};
 #pragma unroll
           for (int b = 0; b < WIN_PLANES; ++b) {
             uint32_t T[TPG];
 #pragma unroll
-            for (int t = 0; t < TPG; ++t) { T[t] = pln[t][b]; pln[t][b] = 0; }
+            for (int t = 0; t < TPG; ++t) T[t] = P[t][b];
+            // the high planes are empty unless some job matched 4 (8) or more of a lane's 15 rows:
+            // with selective jobs they usually are, and an empty plane needs no transpose
+            if (b >= 2 && !__any_sync(FULL, (T[0] | T[1] | T[2] | T[3]) != 0u)) continue;
             xpose4(T);
 #pragma unroll
             for (int t = 0; t < TPG; ++t) {
@@ -549,54 +731,36 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
             w[t * 32] = any[t];
             cnt[t] += c[t];
           }
-          ++widx;
-          in_win = 0;
         }
-        return;
+        blk += nb;
+        rp += (size_t)nb * 32u * ROW_U4;
+        ++widx;
       }
-
-      // four independent 32x32 transposes, interleaved step by step so the shuffles overlap:
-      // afterwards lane j holds in T[t] the rows of this block that match job 32t+j
-      uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
-      xpose4(T);
-
-#pragma unroll
-      for (int t = 0; t < TPG; ++t) {
-        const uint32_t job = group * JPG + t * 32 + lane;
-        if (job < p.n_jobs) p.bits[(size_t)job * n_blocks + blk] = T[t];
-      }
-    };
-
-    // two row buffers used alternately (no register rotation, and explicit names: an indexed
-    // array of buffers made the compiler spill)
-    RowCodes<NC> ra, rb;
-    if (b0 < b1) load_row<NC, ROW32>(rows_lane, b0 * 32u, ra);
-    if (b0 + 1 < b1) load_row<NC, ROW32>(rows_lane, (b0 + 1) * 32u, rb);
-#pragma unroll
-    for (uint32_t a = 2; a < PREFETCH_BLOCKS; ++a)
-      if (b0 + a < b1) prefetch_l1(rows_lane + (size_t)(b0 + a) * (ROW32 ? 64u : 32u));
-
-    // a block's codes are copied out of its buffer first and the buffer is reloaded at once,
-    // so every load has two blocks of work to land
-    auto step = [&](const uint32_t blk, RowCodes<NC>& buf) {
-      const RowCodes<NC> cur = buf;
-      if (blk + 2 < b1) load_row<NC, ROW32>(rows_lane, (blk + 2) * 32u, buf);
-      if (blk + PREFETCH_BLOCKS < b1)
-        prefetch_l1(rows_lane + (size_t)(blk + PREFETCH_BLOCKS) * (ROW32 ? 64u : 32u));
-      process(blk, cur);
-    };
-    uint32_t blk = b0;
-#pragma unroll 1
-    for (; blk + 1 < b1; blk += 2) {
-      step(blk, ra);
-      step(blk + 1, rb);
-    }
-    if (blk < b1) step(blk, ra);
-
-    if constexpr (COUNT) {
 #pragma unroll
       for (int t = 0; t < TPG; ++t)
         p.part_cnt[(size_t)(group * JPG + t * 32 + lane) * p.slots + slot] = cnt[t];
+    } else {
+      // ---- bitmap mode: every block is transposed and lane j stores the 32-row match word of
+      // the job evaluated in slot 32t+j
+      uint32_t out_job[TPG];
+#pragma unroll
+      for (int t = 0; t < TPG; ++t) {
+        const uint32_t s = group * JPG + t * 32 + lane;
+        out_job[t] = s < p.n_jobs ? (p.job_order ? p.job_order[s] : s) : 0xFFFFFFFFu;
+      }
+#pragma unroll 1
+      for (uint32_t blk = b0; blk < b1; ++blk) {
+        const RowCodes<NCMAX> cur = ra;
+        ra = rb;
+        if (blk + 2 < b1) load_row<NCMAX, ROW32>(rp + 2u * 32u * ROW_U4, rb);
+        rp += 32u * ROW_U4;
+        const uint4 m = gather_generic(cur, block_mask(blk));
+        uint32_t T[TPG] = {m.x, m.y, m.z, m.w};
+        xpose4(T);
+#pragma unroll
+        for (int t = 0; t < TPG; ++t)
+          if (out_job[t] != 0xFFFFFFFFu) p.bits[(size_t)out_job[t] * n_blocks + blk] = T[t];
+      }
     }
   }
 #ifdef DSM_CTA_TIMING
@@ -632,11 +796,14 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   const uint32_t lane = threadIdx.x & 31u;
   const uint32_t warp = threadIdx.x >> 5;
   const uint32_t jl = warp / WPJ, wj = warp % WPJ;
-  const uint32_t job = blockIdx.x * JPC + jl;
-  const bool live = job < p.n_jobs;
+  // k_match evaluated job `job` in evaluation slot `es` (bit es % 32 of tile es / 32 % 4 of group
+  // es / 128); its counts and window records are filed under the slot, the results under the job
+  const uint32_t es = blockIdx.x * JPC + jl;
+  const bool live = es < p.n_jobs;
+  const uint32_t job = live ? (p.job_order ? p.job_order[es] : es) : 0u;
   const uint32_t n_slots = p.slots;
   const uint32_t n_chunks = (n_slots + 31u) / 32u;
-  const uint32_t* cnt = p.part_cnt + (size_t)(live ? job : 0u) * p.slots;
+  const uint32_t* cnt = p.part_cnt + (size_t)(live ? es : 0u) * p.slots;
   uint32_t* csum = chunk_sums + jl * n_chunks;
 
   {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
@@ -678,20 +845,41 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   }
 
   // ---- what it takes to evaluate this job on one row per lane
-  const uint32_t group = job / JPG, tile = (job % JPG) / 32u, bit = job & 31u;
+  const uint32_t group = es / JPG, tile = (es % JPG) / 32u, bit = es & 31u;
   const uint32_t* tab = reinterpret_cast<const uint32_t*>(p.tabs + (size_t)group * p.n_entries) + tile;
-  const uint32_t cut_a = p.recs[(size_t)job * p.rec_words + 0];
-  const uint32_t cut_b = p.recs[(size_t)job * p.rec_words + 1];
+  const uint32_t cut_a = min(p.recs[(size_t)job * p.rec_words + 0], p.live_a);
+  const uint32_t cut_b = min(p.recs[(size_t)job * p.rec_words + 1], p.live_b);
+  const uint32_t n_act = min(p.n_used, p.group_nact[group]);  // the columns k_match gathered for this group
   auto eval_row = [&](const uint32_t row, const uint32_t cut) -> uint32_t {
-    // a rolled loop on purpose: this body is inlined at every flush site and k_extract is
-    // bound by instruction fetch and load latency, not by instruction count
-    const uint16_t* codes = p.rows16 + (size_t)row * p.n_cols;
+    // the row's codes come with one (16-byte rows) or two 128-bit loads, then the table words of
+    // all columns are fetched side by side: two dependent round trips per candidate.  A rolled
+    // loop on purpose: this body is inlined at every flush site and k_extract is bound by
+    // instruction fetch and load latency, not by instruction count
+    const uint4* rp = p.rows + (size_t)row * (p.n_cols >> 3);
+    const uint4 v0 = __ldg(rp);
+    uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, 0, 0, 0, 0};
+    if (n_act > 8u) {
+      const uint4 v1 = __ldg(rp + 1);
+      w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
+    }
     uint32_t ok = row < cut ? 1u : 0u;
-#pragma unroll 2
-    for (uint32_t c = 0; c < p.n_used; ++c) {
-      uint32_t code = __ldg(codes + c);
-      if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-      ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
+#pragma unroll
+    for (uint32_t c = 0; c < 8u; ++c) {
+      if (c < n_act) {
+        uint32_t code = (c & 1u) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
+        if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+        ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
+      }
+    }
+    if (n_act > 8u) {  // 32-byte rows (pool tables)
+#pragma unroll
+      for (uint32_t c = 8u; c < 16u; ++c) {
+        if (c < n_act) {
+          uint32_t code = (c & 1u) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
+          if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
+          ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
+        }
+      }
     }
     return ok & 1u;
   };
@@ -710,7 +898,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
     }
     return (bs + b) * 32u + l;
   };
-  const uint32_t* wr_job = p.win_rows + (size_t)group * p.slots * p.wps * JPG + (job % JPG);
+  const uint32_t* wr_job = p.win_rows + (size_t)group * p.slots * p.wps * JPG + (es % JPG);
 
   // ---- windows waiting to be evaluated (warp-private): first block, row-lane set, cut-off,
   // index of the window's first candidate among all queued candidates.  Candidates are

@@ -43,12 +43,17 @@ FLAG_SHARED = 4           # total_blocks > 1
 FLAG_NO_OFFER = 8         # instance.offer is None
 FLAG_AUTO_DIVISIBLE = 16  # is_divisible_into_blocks(cpu, gpu, "auto")[0]
 
-KIND_RANGE, KIND_BITSET, KIND_GPU, KIND_BK = 1, 2, 3, 4
+KIND_RANGE, KIND_BITSET, KIND_GPU, KIND_BK, KIND_PAIR = 1, 2, 3, 4, 5
 COLF_NULL_PASSES = 1
+COLF_PAIR_A_BITSET = 2
 GPUF_MEM_BOUNDED, GPUF_CC_BOUNDED, GPUF_NAME_ANY = 1, 2, 8
 NO_ROW = 0xFFFFFFFF
 MAX_CODES = 65535
 LUT_THRESHOLD = 1024  # set columns with more dictionary entries go through a per-call remap
+# Eight conflict-free copies of a job group's acceptance tables fit beside three resident CTAs per
+# SM up to this many table entries (dsmatch.cu:make_plan); cpu and memory are merged into one
+# pair-coded column only while the tables stay within it.
+PAIR_ENTRY_BUDGET = 570
 
 
 def backend_code(b: Any) -> int:
@@ -160,6 +165,16 @@ class EncodedTable:
     price_a: np.ndarray       # prices of the first segment (ascending)
     price_b: np.ndarray       # prices of the second segment (ascending)
     is_pool: bool
+    # cpu and memory as ONE column (kind PAIR) when the dictionaries are small enough: entry =
+    # cpu ordinal | memory ordinal << 16; cpu_values / memory_values are then kept here
+    pair_entries: Optional[np.ndarray] = None   # uint32 [n_pairs]
+    cpu_values: Optional[np.ndarray] = None
+    memory_values: Optional[np.ndarray] = None
+
+    @property
+    def n_rest(self) -> int:
+        """Live rows of the second segment."""
+        return self.n_src - self.n_avail
 
     def col(self, name: str) -> int:
         for i, c in enumerate(self.columns):
@@ -178,7 +193,10 @@ def _check_card(name: str, n: int) -> None:
         raise ValueError(f"column {name!r} has {n} distinct values; the u16 row format allows {MAX_CODES}")
 
 
-def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True) -> EncodedTable:
+def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
+                 pair_columns: Optional[bool] = None) -> EncodedTable:
+    """``pair_columns``: merge cpu and memory into one pair-coded column (one table gather per row
+    instead of two).  ``None`` = when the acceptance tables stay within ``PAIR_ENTRY_BUDGET``."""
     n = len(oc)
     sh = oc.shapes
     price = np.asarray(oc.price, dtype=np.float64)
@@ -270,31 +288,49 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True) -> Enc
         _check_card(name, card + 1)
         return np.where(ids < 0, card, ids), card + 1  # last entry = unknown
 
-    columns: List[Column] = [
-        Column("cpu", KIND_RANGE, len(cpu_vals), values=cpu_vals),
-        Column("memory", KIND_RANGE, len(mem_vals), values=mem_vals),
-        Column("disk", KIND_RANGE, len(disk_vals) + 1, flags=COLF_NULL_PASSES, values=disk_vals),
-        Column("gpu", KIND_GPU, len(guniq)),
-        Column("bk", KIND_BK, len(present) + 1),
-    ]
-    per_row: List[np.ndarray] = [cpu_ord[sid], mem_ord[sid], disk_ord[sid], ginv[sid], bk_code]
+    # Column order = gather order.  k_match gathers, per group of 128 jobs, only the columns up to
+    # the last one that rejects anything for that group, so the columns jobs usually leave open
+    # (default disk, no region / instance-type filter ...) come last.
     reg_codes, reg_card = set_codes(oc.region_id, len(oc.regions), "region")
     it_codes, it_card = set_codes(oc.itype_id, len(oc.itypes), "itype")
-    columns += [
+    tail_cols: List[Column] = [
+        Column("gpu", KIND_GPU, len(guniq)),
+        Column("bk", KIND_BK, len(present) + 1),
+        Column("disk", KIND_RANGE, len(disk_vals) + 1, flags=COLF_NULL_PASSES, values=disk_vals),
         Column("region", KIND_BITSET, reg_card, lookup={r: i for i, r in enumerate(oc.regions)}),
-        Column("itype", KIND_BITSET, it_card, lookup={r: i for i, r in enumerate(oc.itypes)}),
     ]
-    per_row += [reg_codes, it_codes]
+    tail_rows: List[np.ndarray] = [ginv[sid], bk_code, disk_ord[sid], reg_codes]
     if oc.is_pool:
         fl_codes, fl_card = set_codes(oc.fleet_id, len(oc.fleets), "fleet")
         nm_codes, nm_card = set_codes(oc.name_id, len(oc.names), "name")
         zn_codes, zn_card = set_codes(oc.zone_id, len(oc.zones), "zone")
-        columns += [
+        tail_cols += [
             Column("fleet", KIND_BITSET, fl_card, lookup={r: i for i, r in enumerate(oc.fleets)}),
+            Column("itype", KIND_BITSET, it_card, lookup={r: i for i, r in enumerate(oc.itypes)}),
             Column("name", KIND_BITSET, nm_card, lookup={r: i for i, r in enumerate(oc.names)}),
             Column("zone", KIND_BITSET, zn_card, lookup={r: i for i, r in enumerate(oc.zones)}),
         ]
-        per_row += [fl_codes, nm_codes, zn_codes]
+        tail_rows += [fl_codes, it_codes, nm_codes, zn_codes]
+    else:
+        tail_cols.append(Column("itype", KIND_BITSET, it_card, lookup={r: i for i, r in enumerate(oc.itypes)}))
+        tail_rows.append(it_codes)
+
+    # cpu + memory: one pair-coded column when the tables stay small enough for eight copies
+    pkey = cpu_ord.astype(np.int64) | (mem_ord.astype(np.int64) << 16)
+    puniq, pinv = np.unique(pkey, return_inverse=True)
+    resident_entries = sum(c.card for c in tail_cols if c.card <= LUT_THRESHOLD)
+    if pair_columns is None:
+        pair_columns = len(puniq) + resident_entries <= PAIR_ENTRY_BUDGET and len(puniq) <= MAX_CODES
+    pair_entries = None
+    if pair_columns:
+        _check_card("cpu_memory", len(puniq))
+        pair_entries = puniq.astype(np.uint32)
+        columns = [Column("cpu_memory", KIND_PAIR, len(puniq))] + tail_cols
+        per_row = [np.asarray(pinv).reshape(-1)[sid]] + tail_rows
+    else:
+        columns = [Column("cpu", KIND_RANGE, len(cpu_vals), values=cpu_vals),
+                   Column("memory", KIND_RANGE, len(mem_vals), values=mem_vals)] + tail_cols
+        per_row = [cpu_ord[sid], mem_ord[sid]] + tail_rows
     n_cols = 8 if len(columns) <= 8 else 16
 
     # ---- row order and padding
@@ -322,6 +358,7 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True) -> Enc
         price=price_phys, perm=perm, columns=columns, gpu_entries=gpu_entries, bk_entries=bk_entries,
         gpu_dict=dict(count=cnt_vals, memory=gm_vals, total=tot_vals, cc=cc_vals, names=lower_names),
         price_a=price[order[:n_avail]], price_b=price[order[n_avail:]], is_pool=oc.is_pool,
+        pair_entries=pair_entries, cpu_values=cpu_vals, memory_values=mem_vals,
     )
 
 
@@ -405,47 +442,42 @@ def _bitset_from_csr(any_mask: np.ndarray, ptr: np.ndarray, ids: np.ndarray, n_w
 
 @dataclass
 class PackedJobs:
-    records: np.ndarray            # uint32 [J, rec_words]
+    records: np.ndarray            # uint32 [J, rec_words], in the caller's job order
     layout: Dict[str, Any]         # n_used, kind[], card[], flags[], aux[], rec_off[], rec_words
     luts: Dict[int, np.ndarray]    # column -> uint16 remap, uploaded per call
+    order: Optional[np.ndarray] = None  # uint32 [J] evaluation order (dsm_layout.job_order), None = as given
+
+
+def _range_trivial(words: np.ndarray, n_values: int) -> np.ndarray:
+    """Jobs whose packed range accepts every one of ``n_values`` ordinals."""
+    if n_values == 0:
+        return np.ones(len(words), bool)
+    return ((words & 0xFFFF) == 0) & ((words >> 16) >= n_values - 1)
 
 
 def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     j = jc.n
-    parts: List[np.ndarray] = []
-    offs: List[int] = []
-    kinds: List[int] = []
-    cards: List[int] = []
-    cflags: List[int] = []
-    aux: List[int] = []
     luts: Dict[int, np.ndarray] = {}
-    trivial: List[bool] = []  # per column: every job accepts every entry
+    # per table column: (record words [J, w], kind, card, flags, aux, jobs that accept every entry)
+    preds: Dict[str, Tuple[np.ndarray, int, int, int, int, np.ndarray]] = {}
 
-    # words 0,1: row cut-offs (max_price and exclude_not_available)
+    # words 0,1: row cut-offs (max_price and exclude_not_available); padding rows lie behind them
     mp = np.asarray(jc.max_price, dtype=np.float64)
     no_mp = np.isnan(mp)
     mp0 = np.where(no_mp, 0.0, mp)
-    cut_a = np.where(no_mp, t.split_row, np.searchsorted(t.price_a, mp0, side="right"))
-    cut_b = np.where(no_mp, t.n_rows, t.split_row + np.searchsorted(t.price_b, mp0, side="right"))
+    cut_a = np.where(no_mp, t.n_avail, np.searchsorted(t.price_a, mp0, side="right"))
+    cut_b = np.where(no_mp, t.split_row + t.n_rest, t.split_row + np.searchsorted(t.price_b, mp0, side="right"))
     cut_b = np.where(np.asarray(jc.exclude_not_available, dtype=bool), t.split_row, cut_b)
-    parts.append(np.stack([cut_a, cut_b], axis=1).astype(np.uint32))
-    pos = 2
+    cuts = np.stack([cut_a, cut_b], axis=1).astype(np.uint32)
 
-    def add(words: np.ndarray, kind: int, card: int, flags: int = 0, ax: int = 0) -> None:
-        nonlocal pos
+    def put(name: str, words: np.ndarray, kind: int, card: int, trivial: np.ndarray, flags: int = 0,
+            ax: int = 0) -> None:
         words = np.ascontiguousarray(words, dtype=np.uint32).reshape(j, -1)
-        parts.append(words)
-        offs.append(pos)
-        kinds.append(kind)
-        cards.append(card)
-        cflags.append(flags)
-        aux.append(ax)
-        trivial.append(False)
-        pos += words.shape[1]
+        preds[name] = (words, kind, card, flags, ax, np.asarray(trivial, dtype=bool))
 
-    def add_set(col_idx: int, any_mask, ptr, ids, unknown_passes: bool) -> None:
-        col = t.columns[col_idx]
-        card = col.card  # ids 0..card-2, last = unknown
+    def put_set(name: str, any_mask, ptr, ids, unknown_passes: bool) -> None:
+        col_idx = t.col(name)
+        card = t.columns[col_idx].card  # ids 0..card-2, last = unknown
         any_mask = np.asarray(any_mask, dtype=bool)
         ids = np.asarray(ids, dtype=np.int64)
         if card > LUT_THRESHOLD:
@@ -461,10 +493,8 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
             luts[col_idx] = lut
         nw = (card + 31) // 32
         bits = _bitset_from_csr(any_mask, ptr, ids, nw, pass_bits=[card - 1] if unknown_passes else [])
-        add(bits, KIND_BITSET, card)
-        trivial[-1] = bool(any_mask.all())
+        put(name, bits, KIND_BITSET, card, any_mask)
 
-    c = t.col
     # explicit block counts (offers.py:102-118): b > 1 keeps rows with cpu % b == 0 and gpus % b == 0,
     # b < 0 stands for an invalid count (nothing is divisible); 0 = no block filter
     blocks = np.zeros(j, dtype=np.int64) if jc.blocks is None else np.asarray(jc.blocks, dtype=np.int64)
@@ -472,23 +502,34 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
         raise ValueError("block counts above 65535 are not supported")
     if (blocks > 1).any() and len(t.gpu_entries) and int((t.gpu_entries[:, 2] >> 25).max()) >= 127:
         raise ValueError("an instance with more than 126 GPUs cannot be matched against an explicit block count")
-    cpu_col = t.columns[c("cpu")]
+    cpu_vals, mem_vals = t.cpu_values, t.memory_values
+    cpu_w = _range_words(cpu_vals, jc.cpu)
+    mem_w = _range_words(mem_vals, jc.memory)
+    cpu_bits = None
     if (blocks != 0).any():
         # the cpu test becomes "in range and divisible": an irregular set, sent as a bitset
-        w = _range_words(cpu_col.values, jc.cpu)
-        e = np.arange(cpu_col.card, dtype=np.uint32)[None, :]
-        ok = (e >= (w & 0xFFFF)[:, None]) & (e <= (w >> 16)[:, None])
-        vals = cpu_col.values.astype(np.int64)[None, :]
+        e = np.arange(len(cpu_vals), dtype=np.uint32)[None, :]
+        ok = (e >= (cpu_w & 0xFFFF)[:, None]) & (e <= (cpu_w >> 16)[:, None])
+        vals = cpu_vals.astype(np.int64)[None, :]
         ok &= np.where(blocks[:, None] > 1, vals % np.maximum(blocks, 1)[:, None] == 0, blocks[:, None] == 0)
-        bits = np.zeros((j, (cpu_col.card + 31) // 32), dtype=np.uint32)
+        cpu_bits = np.zeros((j, (len(cpu_vals) + 31) // 32), dtype=np.uint32)
         jj, ee = np.nonzero(ok)
-        np.bitwise_or.at(bits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
-        add(bits, KIND_BITSET, cpu_col.card)
+        np.bitwise_or.at(cpu_bits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
+    cpu_triv = _range_trivial(cpu_w, len(cpu_vals)) & (blocks == 0)
+    mem_triv = _range_trivial(mem_w, len(mem_vals))
+    if t.pair_entries is not None:
+        a_words = cpu_w[:, None] if cpu_bits is None else cpu_bits
+        put("cpu_memory", np.concatenate([a_words, mem_w[:, None]], axis=1), KIND_PAIR, len(t.pair_entries),
+            cpu_triv & mem_triv, flags=0 if cpu_bits is None else COLF_PAIR_A_BITSET, ax=a_words.shape[1])
     else:
-        add(_range_words(cpu_col.values, jc.cpu), KIND_RANGE, cpu_col.card)
-    add(_range_words(t.columns[c("memory")].values, jc.memory), KIND_RANGE, t.columns[c("memory")].card)
-    dcol = t.columns[c("disk")]
-    add(_range_words(dcol.values, jc.disk), KIND_RANGE, dcol.card, COLF_NULL_PASSES)
+        if cpu_bits is None:
+            put("cpu", cpu_w, KIND_RANGE, len(cpu_vals), cpu_triv)
+        else:
+            put("cpu", cpu_bits, KIND_BITSET, len(cpu_vals), cpu_triv)
+        put("memory", mem_w, KIND_RANGE, len(mem_vals), mem_triv)
+    dcol = t.columns[t.col("disk")]
+    disk_w = _range_words(dcol.values, jc.disk)
+    put("disk", disk_w, KIND_RANGE, dcol.card, _range_trivial(disk_w, len(dcol.values)), COLF_NULL_PASSES)
 
     # accelerator sub-predicate
     gd = t.gpu_dict
@@ -504,15 +545,19 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     gv = np.asarray(jc.gpu_vendor, dtype=np.int64)
     vmask = np.where(gv == 0, 0xFF, 1 << gv).astype(np.uint32)
     name_bits = _bitset_from_csr(np.zeros(j, dtype=bool), jc.gpu_name_ptr, jc.gpu_name_ids, nwn)
+    cnt_w = _range_words(gd["count"], jc.gpu_count)
+    tot_w = _range_words(gd["total"], jc.gpu_total)
     gwords = np.concatenate([
-        _range_words(gd["count"], jc.gpu_count)[:, None],
+        cnt_w[:, None],
         _range_words(gd["memory"], gm)[:, None],
-        _range_words(gd["total"], jc.gpu_total)[:, None],
+        tot_w[:, None],
         (np.minimum(cc_ord, 0xFFFE) | (gflags << np.uint32(16)))[:, None],
         (vmask | (np.where(blocks > 1, blocks, 0).astype(np.uint32) << np.uint32(16)))[:, None],
         name_bits,
     ], axis=1)
-    add(gwords, KIND_GPU, t.columns[c("gpu")].card, ax=nwn)
+    gpu_triv = (_range_trivial(cnt_w, len(gd["count"])) & _range_trivial(tot_w, len(gd["total"]))
+                & (gflags == GPUF_NAME_ANY) & (gv == 0) & (blocks <= 1))
+    put("gpu", gwords, KIND_GPU, t.columns[t.col("gpu")].card, gpu_triv, ax=nwn)
 
     # backend / spot / status / flags
     spot = np.asarray(jc.spot, dtype=np.int64)
@@ -520,41 +565,56 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     st_mask = np.full(j, 0xFF, dtype=np.uint32) if jc.status_mask is None else np.asarray(jc.status_mask, dtype=np.uint32)
     req = np.zeros(j, dtype=np.uint32) if jc.flag_req is None else np.asarray(jc.flag_req, dtype=np.uint32)
     forbid = np.zeros(j, dtype=np.uint32) if jc.flag_forbid is None else np.asarray(jc.flag_forbid, dtype=np.uint32)
-    bwords = np.stack([
-        np.asarray(jc.src_backend_mask, dtype=np.uint32),
-        np.asarray(jc.off_backend_mask, dtype=np.uint32),
-        spot_mask | (st_mask << np.uint32(8)),
-        req | (forbid << np.uint32(16)),
-    ], axis=1)
-    add(bwords, KIND_BK, t.columns[c("bk")].card)
+    src_m = np.asarray(jc.src_backend_mask, dtype=np.uint32)
+    off_m = np.asarray(jc.off_backend_mask, dtype=np.uint32)
+    bwords = np.stack([src_m, off_m, spot_mask | (st_mask << np.uint32(8)), req | (forbid << np.uint32(16))], axis=1)
+    bk_triv = ((src_m == 0xFFFFFFFF) & (off_m == 0xFFFFFFFF) & (spot_mask == 3) & (st_mask == 0xFF)
+               & (req == 0) & (forbid == 0))
+    put("bk", bwords, KIND_BK, t.columns[t.col("bk")].card, bk_triv)
 
-    add_set(c("region"), jc.region_any, jc.region_ptr, jc.region_ids, unknown_passes=False)
-    add_set(c("itype"), jc.itype_any, jc.itype_ptr, jc.itype_ids, unknown_passes=True)
+    put_set("region", jc.region_any, jc.region_ptr, jc.region_ids, unknown_passes=False)
+    put_set("itype", jc.itype_any, jc.itype_ptr, jc.itype_ids, unknown_passes=True)
     if t.is_pool:
         ar = np.arange(j + 1)
         fany = np.ones(j, bool) if jc.fleet_any is None else jc.fleet_any
         fids = np.full(j, -1, np.int64) if jc.fleet_ids is None else jc.fleet_ids
-        add_set(c("fleet"), fany, ar, fids, unknown_passes=False)
+        put_set("fleet", fany, ar, fids, unknown_passes=False)
         nany = np.ones(j, bool) if jc.name_any is None else jc.name_any
         nids = np.full(j, -1, np.int64) if jc.name_ids is None else jc.name_ids
-        add_set(c("name"), nany, ar, nids, unknown_passes=False)
+        put_set("name", nany, ar, nids, unknown_passes=False)
         zany = np.ones(j, bool) if jc.zone_any is None else jc.zone_any
         zptr = np.zeros(j + 1, np.int64) if jc.zone_ptr is None else jc.zone_ptr
         zids = np.zeros(0, np.int64) if jc.zone_ids is None else jc.zone_ids
-        add_set(c("zone"), zany, zptr, zids, unknown_passes=True)
+        put_set("zone", zany, zptr, zids, unknown_passes=True)
 
+    # ---- records in table-column order; trailing columns on which no job of this call filters
+    # are not part of the call at all
+    names = [c.name for c in t.columns]
+    last_needed = np.zeros(j, dtype=np.int64)  # per job: 1 + index of the last column that rejects anything
+    for ci, name in enumerate(names):
+        last_needed = np.where(preds[name][5], last_needed, ci + 1)
+    n_used = max(1, int(last_needed.max()) if j else 1)
+    for ci in list(luts):
+        if ci >= n_used:
+            luts.pop(ci)
+    kinds, cards, cflags, aux, offs, parts = [], [], [], [], [], [cuts]
+    pos = 2
+    for name in names[:n_used]:
+        words, kind, card, flags, ax, _ = preds[name]
+        kinds.append(kind); cards.append(card); cflags.append(flags); aux.append(ax); offs.append(pos)
+        parts.append(words)
+        pos += words.shape[1]
     rec_words = (pos + 3) // 4 * 4
     rec = np.zeros((j, rec_words), dtype=np.uint32)
     o = 0
-    for p in parts:
-        rec[:, o:o + p.shape[1]] = p
-        o += p.shape[1]
-    # trailing columns on which no job of this call filters need not be gathered at all
-    n_used = len(kinds)
-    while n_used > c("bk") + 1 and trivial[n_used - 1]:
-        n_used -= 1
-        luts.pop(n_used, None)
-    kinds, cards, cflags, aux, offs = (x[:n_used] for x in (kinds, cards, cflags, aux, offs))
+    for part in parts:
+        rec[:, o:o + part.shape[1]] = part
+        o += part.shape[1]
+    # ---- evaluation order: jobs that need the same leading columns side by side, so that whole
+    # groups of 128 skip the gathers of the columns behind (only worth it beyond one group)
+    order = None
+    if j > 128 and (last_needed != last_needed[0]).any():
+        order = np.argsort(last_needed, kind="stable").astype(np.uint32)
     layout = dict(n_used=len(kinds), kind=kinds, card=cards, flags=cflags, aux=aux, rec_off=offs,
                   rec_words=rec_words)
-    return PackedJobs(records=rec, layout=layout, luts=luts)
+    return PackedJobs(records=rec, layout=layout, luts=luts, order=order)

@@ -37,6 +37,10 @@ class Matcher:
         native.check(self._lib.dsm_ctx_create(device, C.c_void_p(stream or 0), C.byref(h)))
         self._h = h
         self.device = device
+        # One shared Matcher serves every drop-in function of a process (default_matcher), and the
+        # reference calls this path from a thread pool: the per-call remap upload and the match that
+        # reads it must not interleave with another thread's.
+        self._call_lock = threading.Lock()
 
     # -- lifecycle
     def close(self) -> None:
@@ -67,14 +71,16 @@ class Matcher:
         return DeviceTable(self, table)
 
     # -- helpers
-    def _layout(self, packed: PackedJobs) -> native.Layout:
+    def _layout(self, packed: PackedJobs, job_order: Optional[int] = None) -> native.Layout:
+        """Upload the per-call remaps and describe the records.  ``job_order``: address of the
+        evaluation order where the records of the call will live (see ``native.make_layout``)."""
         lut_ptrs: Dict[int, int] = {}
         for col, lut in packed.luts.items():
             lut = np.ascontiguousarray(lut, dtype=np.uint16)
             out = C.c_void_p()
             native.check(self._lib.dsm_lut_upload(self.handle, col, native.ptr(lut), len(lut), C.byref(out)))
             lut_ptrs[col] = out.value
-        return native.make_layout(packed.layout, lut_ptrs)
+        return native.make_layout(packed.layout, lut_ptrs, job_order)
 
     def plan(self, dt: "DeviceTable", packed: PackedJobs, k: int = 16) -> Dict[str, int]:
         """Launch geometry the library would pick for this batch (``k=0``: bitmap mode)."""
@@ -93,18 +99,22 @@ class Matcher:
         rec = np.ascontiguousarray(packed.records, dtype=np.uint32)
         if out is None:
             out = (np.empty((j, k), np.uint32), np.empty(j, np.uint32), np.empty(j, np.uint32))
-        lay = self._layout(packed)
-        native.check(self._lib.dsm_match_topk(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j, k,
-                                              native.ptr(out[0]), native.ptr(out[1]), native.ptr(out[2])))
+        order = None if packed.order is None else np.ascontiguousarray(packed.order, dtype=np.uint32)
+        with self._call_lock:  # the remaps live in per-context buffers until the match has run
+            lay = self._layout(packed, native.ptr(order))
+            native.check(self._lib.dsm_match_topk(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j, k,
+                                                  native.ptr(out[0]), native.ptr(out[1]), native.ptr(out[2])))
         return out
 
     def bitmap_rows(self, dt: "DeviceTable", packed: PackedJobs) -> np.ndarray:
         j = len(packed.records)
         rec = np.ascontiguousarray(packed.records, dtype=np.uint32)
         bits = np.empty((j, dt.table.n_rows // 32), np.uint32)
-        lay = self._layout(packed)
-        native.check(self._lib.dsm_match_bitmap(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j,
-                                                native.ptr(bits)))
+        order = None if packed.order is None else np.ascontiguousarray(packed.order, dtype=np.uint32)
+        with self._call_lock:
+            lay = self._layout(packed, native.ptr(order))
+            native.check(self._lib.dsm_match_bitmap(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j,
+                                                    native.ptr(bits)))
         return bits
 
     # -- results in source space
@@ -137,15 +147,18 @@ class DeviceTable:
         self.table = table
         self._lib = native.lib()
         self._matcher = matcher
+        n_pairs = 0 if table.pair_entries is None else len(table.pair_entries)
         desc = native.TableDesc(table.n_rows, table.split_row, table.n_cols,
-                                len(table.gpu_entries), len(table.bk_entries))
+                                len(table.gpu_entries), len(table.bk_entries), n_pairs,
+                                table.n_avail, table.n_rest)
         rows = np.ascontiguousarray(table.rows, dtype=np.uint16)
         price = np.ascontiguousarray(table.price, dtype=np.float64)
         ge = np.ascontiguousarray(table.gpu_entries, dtype=np.uint32)
         be = np.ascontiguousarray(table.bk_entries, dtype=np.uint32)
+        pe = None if table.pair_entries is None else np.ascontiguousarray(table.pair_entries, dtype=np.uint32)
         h = C.c_void_p()
         native.check(self._lib.dsm_table_create(matcher.handle, C.byref(desc), native.ptr(rows), native.ptr(price),
-                                                native.ptr(ge), native.ptr(be), C.byref(h)))
+                                                native.ptr(ge), native.ptr(be), native.ptr(pe), C.byref(h)))
         self._h = h
 
     @property

@@ -25,7 +25,7 @@ EXPORTS = [
     "dsm_match_topk_dev", "dsm_match_bitmap_dev", "dsm_merge_shards_dev", "dsm_gather_price_dev",
     "dsm_sync", "dsm_host_alloc", "dsm_host_free", "dsm_launch_count", "dsm_plan_query",
     "dsm_timing_enable", "dsm_timing_read", "dsm_match_bitmap_static", "dsm_merge_shards_strided_dev",
-    "dsm_merge_shards_interleaved_dev",
+    "dsm_merge_shards_interleaved_dev", "dsm_timing_read_parts",
 ]
 STATIC_SCRATCH_BYTES = 2 << 20  # DSM_STATIC_SCRATCH_BYTES
 
@@ -38,7 +38,8 @@ class DsmError(RuntimeError):
 
 class TableDesc(C.Structure):
     _fields_ = [("n_rows", C.c_uint32), ("split_row", C.c_uint32), ("n_cols", C.c_uint32),
-                ("n_gpu_entries", C.c_uint32), ("n_bk_entries", C.c_uint32)]
+                ("n_gpu_entries", C.c_uint32), ("n_bk_entries", C.c_uint32), ("n_pair_entries", C.c_uint32),
+                ("n_live_a", C.c_uint32), ("n_live_b", C.c_uint32)]
 
 
 class Layout(C.Structure):
@@ -46,7 +47,7 @@ class Layout(C.Structure):
                 ("kind", C.c_uint32 * MAX_COLS), ("card", C.c_uint32 * MAX_COLS),
                 ("flags", C.c_uint32 * MAX_COLS), ("aux", C.c_uint32 * MAX_COLS),
                 ("rec_off", C.c_uint32 * MAX_COLS), ("rec_words", C.c_uint32),
-                ("lut", C.c_void_p * MAX_COLS)]
+                ("lut", C.c_void_p * MAX_COLS), ("job_order", C.c_void_p)]
 
 
 _lib: Optional[C.CDLL] = None
@@ -69,7 +70,7 @@ def lib() -> C.CDLL:
     L.dsm_launch_count.argtypes = [vp]
     L.dsm_ctx_create.argtypes = [C.c_int, vp, C.POINTER(vp)]
     L.dsm_ctx_destroy.argtypes = [vp]
-    L.dsm_table_create.argtypes = [vp, C.POINTER(TableDesc), vp, vp, vp, vp, C.POINTER(vp)]
+    L.dsm_table_create.argtypes = [vp, C.POINTER(TableDesc), vp, vp, vp, vp, vp, C.POINTER(vp)]
     L.dsm_table_destroy.argtypes = [vp]
     L.dsm_lut_upload.argtypes = [vp, u32, vp, u32, C.POINTER(vp)]
     L.dsm_match_topk.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, u32, vp, vp, vp]
@@ -87,6 +88,7 @@ def lib() -> C.CDLL:
     L.dsm_host_free.argtypes = [vp]
     L.dsm_timing_enable.argtypes = [vp, C.c_int]
     L.dsm_timing_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
+    L.dsm_timing_read_parts.argtypes = [vp, C.POINTER(C.c_double * 3), C.POINTER(u32)]
     L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, u32, C.POINTER(u32 * 8)]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -105,8 +107,12 @@ def ptr(a: Optional[np.ndarray]) -> Optional[int]:
     return None if a is None else a.ctypes.data
 
 
-def make_layout(d: Dict[str, Any], lut_ptrs: Optional[Dict[int, int]] = None) -> Layout:
+def make_layout(d: Dict[str, Any], lut_ptrs: Optional[Dict[int, int]] = None,
+                job_order: Optional[int] = None) -> Layout:
+    """``job_order``: address of the evaluation order (u32 [n_jobs]) in the memory space of the
+    call's job records (host for the host-buffer entry points, device for ``*_dev``), or None."""
     L = Layout()
+    L.job_order = job_order
     L.n_used = d["n_used"]
     L.rec_words = d["rec_words"]
     for i in range(d["n_used"]):

@@ -128,8 +128,12 @@ class ShardedMatcher:
         torch = self.torch
         j = len(packed.records)
         dev = self.dev
-        b = dict(j=j, k=k, lay=self.matcher._layout(packed))
+        b = dict(j=j, k=k)
         b["rec"] = torch.from_numpy(np.ascontiguousarray(packed.records).view(np.int32)).to(dev)
+        # the evaluation order lives where the records live: on the device
+        b["order"] = None if packed.order is None else \
+            torch.from_numpy(np.ascontiguousarray(packed.order, dtype=np.uint32).view(np.int32)).to(dev)
+        b["lay"] = self.matcher._layout(packed, None if b["order"] is None else b["order"].data_ptr())
         # one record per shard: [idx J*k | cnt J | max J | (pad) | max price J f64], so that a
         # single all_gather moves everything
         w_idx, w_cnt = j * k, j

@@ -72,10 +72,17 @@ enum dsm_col_kind {
    *   w0 serving-backend mask  w1 offer-backend mask  w2 spot mask | status mask<<8
    *   w3 required flags | forbidden flags<<16.  App. A.1 item 3 and
    *   server/services/offers.py:81-94, pools.py:460-488. */
-  DSM_COL_BK = 4
+  DSM_COL_BK = 4,
+  /* two range attributes stored as ONE code: the id of the (ordinal A, ordinal B) pair the row
+   * carries, so that one table gather tests both (cpu and memory: App. A.1 items 4, 5).  The
+   * table holds the pair dictionary (dsm_table_create: pair_entries, A | B<<16 per entry).
+   * Record = aux words for member A -- one range word, or with DSM_COLF_PAIR_A_BITSET a bitset
+   * over A's ordinals -- followed by member B's range word. */
+  DSM_COL_PAIR = 5
 };
 
 #define DSM_COLF_NULL_PASSES 1u
+#define DSM_COLF_PAIR_A_BITSET 2u
 
 #define DSM_GPUF_MEM_BOUNDED 1u
 #define DSM_GPUF_CC_BOUNDED 2u
@@ -100,6 +107,10 @@ typedef struct dsm_table_desc {
   uint32_t n_cols;     /* codes per row: 8 (16-byte rows) or 16 (32-byte rows) */
   uint32_t n_gpu_entries; /* entries of the DSM_COL_GPU dictionary (0 if none) */
   uint32_t n_bk_entries;  /* entries of the DSM_COL_BK dictionary (0 if none) */
+  uint32_t n_pair_entries;/* entries of the DSM_COL_PAIR dictionary (0 if none) */
+  uint32_t n_live_a;      /* real rows of the first segment: rows [n_live_a, split_row) are padding */
+  uint32_t n_live_b;      /* real rows of the second: rows [split_row + n_live_b, n_rows) are padding.
+                             Padding rows never match, whatever a record's cut-offs say. */
 } dsm_table_desc;
 
 /* Per-call description of the job records and of the acceptance tables built from them. */
@@ -117,6 +128,14 @@ typedef struct dsm_layout {
    * values, or NULL): lets a high-cardinality column be looked up through the few classes
    * the jobs of this call mention.  Set by dsm_lut_upload. */
   const uint16_t* lut[DSM_MAX_COLS];
+  /* optional evaluation order of the jobs: a permutation of 0..n_jobs-1 (u32), NULL = as given.
+   * Jobs are evaluated 128 at a time; a group whose jobs all leave the trailing columns open
+   * (no region filter, default disk, ...) skips those columns' gathers, so a host that puts
+   * similar jobs next to each other in this order gets a faster match.  Results are always
+   * returned in the caller's job order.  The array lives where the call's job records live:
+   * host memory for dsm_match_topk / dsm_match_bitmap, device memory for the *_dev and
+   * *_static entry points. */
+  const uint32_t* job_order;
 } dsm_layout;
 
 typedef struct dsm_ctx dsm_ctx;
@@ -134,11 +153,12 @@ const char* dsm_build_info(void);
 
 /* Upload an encoded table.  rows: n_rows*n_cols u16 (host).  price: n_rows f64 (host), used
  * only to pick the max-price match; may be NULL.  gpu_entries / bk_entries: dictionaries of
- * the composite columns (host).  Replaces the per-(job,offer) offer_to_catalog_item walk
- * (core/backends/base/offers.py:86-109): attributes are encoded once per table. */
+ * the composite columns (host); pair_entries: n_pair_entries u32 (NULL if none).  Replaces the
+ * per-(job,offer) offer_to_catalog_item walk (core/backends/base/offers.py:86-109): attributes
+ * are encoded once per table. */
 int dsm_table_create(dsm_ctx* ctx, const dsm_table_desc* desc, const uint16_t* rows,
                      const double* price, const uint32_t* gpu_entries,
-                     const uint32_t* bk_entries, dsm_table** out);
+                     const uint32_t* bk_entries, const uint32_t* pair_entries, dsm_table** out);
 int dsm_table_destroy(dsm_table* t);
 
 /* Copy a per-call code->class remap to the device (see dsm_layout.lut).  The returned device
@@ -246,11 +266,15 @@ int dsm_host_alloc(size_t bytes, void** out);
 int dsm_host_free(void* p);
 /* Kernel launches issued by this context since creation (bench.py's gpu_launches). */
 uint64_t dsm_launch_count(const dsm_ctx* ctx);
-/* Time the match kernel alone: while enabled, a CUDA event pair brackets every k_match launch
+/* Time the kernels of a call: while enabled, CUDA events bracket every launch of a match call
  * on the context's stream; dsm_timing_read synchronises, returns the summed kernel time and
  * the number of launches since the last read, and resets the counter. */
 int dsm_timing_enable(dsm_ctx* ctx, int on);
 int dsm_timing_read(dsm_ctx* ctx, double* total_ms, uint32_t* n_launches);
+/* The same events, per kernel of a call: parts_ms = summed time of k_build_tables, k_match and
+ * k_extract (0 for bitmap calls) over the n_calls calls since the last read (bench.py's
+ * step_breakdown_ms).  Resets the counter like dsm_timing_read; use one or the other. */
+int dsm_timing_read_parts(dsm_ctx* ctx, double parts_ms[3], uint32_t* n_calls);
 /* Launch geometry chosen for a call (k = 0: bitmap mode): grid CTAs, work items, row ranges per
  * job group in the two segments, slots, shared memory, dictionary entries, job groups. */
 int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,

@@ -10,8 +10,9 @@ from __future__ import annotations
 
 import numpy as np
 
-from dstack_b200.encode import (COLF_NULL_PASSES, GPUF_CC_BOUNDED, GPUF_MEM_BOUNDED, GPUF_NAME_ANY, KIND_BITSET,
-                                KIND_BK, KIND_GPU, KIND_RANGE, NO_ROW, EncodedTable, PackedJobs)
+from dstack_b200.encode import (COLF_NULL_PASSES, COLF_PAIR_A_BITSET, GPUF_CC_BOUNDED, GPUF_MEM_BOUNDED,
+                                GPUF_NAME_ANY, KIND_BITSET, KIND_BK, KIND_GPU, KIND_PAIR, KIND_RANGE, NO_ROW,
+                                EncodedTable, PackedJobs)
 
 
 def acceptance(table: EncodedTable, packed: PackedJobs):
@@ -31,6 +32,19 @@ def acceptance(table: EncodedTable, packed: PackedJobs):
             nw = (card + 31) // 32
             words = rec[:, off:off + nw]
             ok = ((words[:, (e[0] >> 5).astype(np.int64)] >> (e & 31)) & 1).astype(bool)
+        elif kind == KIND_PAIR:
+            ent = table.pair_entries.astype(np.uint64)
+            a, b = (ent & 0xFFFF)[None, :], (ent >> 16)[None, :]
+            aw = lay["aux"][c]
+            if lay["flags"][c] & COLF_PAIR_A_BITSET:
+                words = rec[:, off:off + aw]
+                ai = a[0].astype(np.int64)
+                ok = ((words[:, ai >> 5] >> (a & 31)) & 1).astype(bool)
+            else:
+                w = rec[:, off][:, None]
+                ok = (a >= (w & 0xFFFF)) & (a <= (w >> 16))
+            wb = rec[:, off + aw][:, None]
+            ok = ok & (b >= (wb & 0xFFFF)) & (b <= (wb >> 16))
         elif kind == KIND_GPU:
             ent = table.gpu_entries.astype(np.uint64)
             cnt, mem = (ent[:, 0] & 0xFFFF)[None, :], (ent[:, 0] >> 16)[None, :]
@@ -76,8 +90,9 @@ def match_matrix(table: EncodedTable, packed: PackedJobs) -> np.ndarray:
     acc = acceptance(table, packed)
     j = len(packed.records)
     rows = np.arange(table.n_rows)
-    cut_a = packed.records[:, 0].astype(np.int64)[:, None]
-    cut_b = packed.records[:, 1].astype(np.int64)[:, None]
+    # padding rows never pass, whatever the cut-offs say (k_match clamps them to the live rows)
+    cut_a = np.minimum(packed.records[:, 0].astype(np.int64), table.n_avail)[:, None]
+    cut_b = np.minimum(packed.records[:, 1].astype(np.int64), table.split_row + table.n_rest)[:, None]
     m = np.where(rows[None, :] < table.split_row, rows[None, :] < cut_a, rows[None, :] < cut_b)
     for c, ok in enumerate(acc):
         codes = table.rows[:, c].astype(np.int64)

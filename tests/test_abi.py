@@ -30,6 +30,6 @@ def test_build_info_names_the_target():
 def test_struct_sizes_match_header():
     import ctypes as C
 
-    assert C.sizeof(native.TableDesc) == 5 * 4
-    # u32 n_used + 5 arrays of 16 u32 + u32 rec_words (+4 padding) + 16 pointers
-    assert C.sizeof(native.Layout) == 4 + 5 * 64 + 4 + 16 * 8
+    assert C.sizeof(native.TableDesc) == 8 * 4
+    # u32 n_used + 5 arrays of 16 u32 + u32 rec_words (+4 padding) + 16 + 1 pointers
+    assert C.sizeof(native.Layout) == 4 + 5 * 64 + 4 + 17 * 8

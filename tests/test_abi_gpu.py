@@ -40,7 +40,9 @@ def test_bad_arguments_return_error_codes(matcher):
                                   cnt.ctypes.data, mx.ctypes.data) == DSM_E_ARG
         # a dictionary that cannot fit in shared memory is refused, not truncated
         huge = matcher._layout(packed)
-        huge.card[5] = 60000
+        ranges = [c for c in range(huge.n_used) if huge.kind[c] == 1]  # a range predicate is one word whatever the card
+        assert ranges, "the batch is expected to filter on disk"
+        huge.card[ranges[0]] = 60000
         assert lib.dsm_match_topk(matcher.handle, dt.handle, C.byref(huge), rec.ctypes.data, j, 16, idx.ctypes.data,
                                   cnt.ctypes.data, mx.ctypes.data) == DSM_E_DICT_TOO_LARGE
         bad_kind = matcher._layout(packed)
@@ -50,9 +52,20 @@ def test_bad_arguments_return_error_codes(matcher):
         # and the context still works afterwards
         native.check(lib.dsm_match_topk(*args, j, 16, idx.ctypes.data, cnt.ctypes.data, mx.ctypes.data))
         assert cnt.sum() > 0
-        desc = native.TableDesc(33, 32, 8, 0, 0)  # rows not a multiple of 32
+        # a predicate that would reach past the end of the record is refused (not read out of bounds)
+        bad_off = matcher._layout(packed)
+        bad_off.rec_off[bad_off.n_used - 1] = bad_off.rec_words
+        assert lib.dsm_match_topk(matcher.handle, dt.handle, C.byref(bad_off), rec.ctypes.data, j, 16,
+                                  idx.ctypes.data, cnt.ctypes.data, mx.ctypes.data) == DSM_E_ARG
+        # so is an evaluation order that is not a permutation
+        bad_order = np.zeros(j, np.uint32)
+        bad_lay = matcher._layout(packed, bad_order.ctypes.data)
+        assert lib.dsm_match_topk(matcher.handle, dt.handle, C.byref(bad_lay), rec.ctypes.data, j, 16,
+                                  idx.ctypes.data, cnt.ctypes.data, mx.ctypes.data) == DSM_E_ARG
+        desc = native.TableDesc(33, 32, 8, 0, 0, 0, 32, 1)  # rows not a multiple of 32
         h = C.c_void_p()
-        assert lib.dsm_table_create(matcher.handle, C.byref(desc), rec.ctypes.data, None, None, None, C.byref(h)) == DSM_E_ARG
+        assert lib.dsm_table_create(matcher.handle, C.byref(desc), rec.ctypes.data, None, None, None, None,
+                                    C.byref(h)) == DSM_E_ARG
     finally:
         dt.close()
 

@@ -43,9 +43,9 @@ def test_topk_ragged_sizes(matcher, n_offers, n_jobs):
 
 @pytest.mark.parametrize("n_jobs", [1, 5, 130])
 def test_small_batch_over_many_pieces(matcher, n_jobs):
-    """A scheduler tick: a handful of jobs against a large table is cut into thousands of row
-    pieces, whose counts k_extract then sums with a whole CTA per job."""
-    cat = synth.make_catalog(400_000, seed=31, n_shapes=1024)
+    """A scheduler tick: a handful of jobs against a large table is cut into more than a thousand
+    one-window slots, whose counts k_extract then sums with a whole CTA per job."""
+    cat = synth.make_catalog(600_000, seed=31, n_shapes=1024)
     table = encode_table(cat.columns)
     sj = synth.make_jobs(cat, table, n_jobs, seed=32)
     dt = matcher.upload(table)
@@ -74,14 +74,17 @@ def test_large_k_stays_exact(matcher):
     assert (got.count > 2048).any()
 
 
-def test_long_slots_with_many_windows(matcher, monkeypatch):
+def test_long_slots_with_many_windows(monkeypatch):
     """Few, long row pieces (what a 16k-job batch over tens of millions of offers gets): every
     slot holds more than 32 windows, so k_extract pages through a slot's window records.
     Checked like the benchmark does at full size: sampled jobs against the oracle, properties
     for every job."""
     import bench
 
-    monkeypatch.setenv("DSM_UNITS_PER_CTA", "1")  # read by the library at call time
+    from dstack_b200.engine import Matcher
+
+    monkeypatch.setenv("DSM_UNITS_PER_CTA", "1")  # tuning knobs are read when a context is created
+    matcher = Matcher(0)
     cat = synth.make_catalog(2_000_000, seed=71, n_shapes=1024)
     table = encode_table(cat.columns)
     sj = synth.make_jobs(cat, table, 4096, seed=72)
@@ -93,6 +96,7 @@ def test_long_slots_with_many_windows(matcher, monkeypatch):
         got = matcher.match_topk(dt, sj.columns, 16)
     finally:
         dt.close()
+        matcher.close()
     n = bench.verify(cat.columns, sj, 16, got.index, got.count, got.max_price, np.random.default_rng(5), n_sample=12)
     assert n == 12 and (got.count > 16).any() and ((got.count > 0) & (got.count < 16)).any()
 

@@ -23,6 +23,7 @@ import pytest
 
 from dstack_b200 import native, synth
 from dstack_b200.encode import encode_table, pack_jobs
+from oracle import columnar
 
 pytestmark = pytest.mark.gpu
 
@@ -39,7 +40,10 @@ def _bitmaps(lib, matcher, dt, packed, entry):
     words = dt.table.n_rows // 32
     d_rec = torch.from_numpy(rec.view(np.int32)).to(dev)
     d_bits = torch.full((n_jobs, words), -1, dtype=torch.int32, device=dev)  # poison
-    lay = matcher._layout(packed)
+    # the evaluation order (if the packer chose one) lives where the records live: on the device
+    d_order = None if packed.order is None else \
+        torch.from_numpy(np.ascontiguousarray(packed.order, dtype=np.uint32).view(np.int32)).to(dev)
+    lay = matcher._layout(packed, None if d_order is None else d_order.data_ptr())
     torch.cuda.synchronize(dev)
     rc = entry(matcher.handle, dt.handle, C.byref(lay), d_rec.data_ptr(), n_jobs, d_bits.data_ptr())
     native.check(rc)
@@ -53,14 +57,21 @@ def test_static_scratch_matches_allocating_entry_point_twice_in_a_row(matcher):
     table = encode_table(cat.columns)
     dt = matcher.upload(table)
     try:
-        first = pack_jobs(table, synth.make_jobs(cat, table, 300, seed=42).columns)
-        second = pack_jobs(table, synth.make_jobs(cat, table, 70, seed=43).columns)
-        for packed in (first, second):  # two calls in a row on the shared array
+        jobs = [synth.make_jobs(cat, table, 300, seed=42), synth.make_jobs(cat, table, 70, seed=43)]
+        for sj in jobs:  # two calls in a row on the shared array
+            packed = pack_jobs(table, sj.columns)
             got = _bitmaps(lib, matcher, dt, packed, lib.dsm_match_bitmap_static)
             want = _bitmaps(lib, matcher, dt, packed, lib.dsm_match_bitmap_dev)
             assert got.shape == want.shape
             assert np.array_equal(got, want)  # integer work: bit-exact
             assert want.any(), "vacuous comparison: no job matched anything"
+            # and against the CPU oracle directly, so this file stands on its own: bit l of word b
+            # of job j = physical row 32 b + l matches; the oracle answers in source positions
+            oracle = columnar.match_matrix(cat.columns, sj.columns)
+            rows = np.unpackbits(got.view(np.uint8), axis=1, bitorder="little").astype(bool)
+            live = table.perm >= 0
+            assert not rows[:, ~live].any(), "a padding row matched"
+            assert np.array_equal(rows[:, live], oracle[:, table.perm[live]])
     finally:
         dt.close()
 
