@@ -128,7 +128,7 @@ class CpuBaseline:
     def __init__(self, wl, cores: int, n_offers: int = 20_000, jobs_per_core: int = 48):
         import multiprocessing as mp
 
-        from dstack_b200 import synth
+        from workloads import synth
         from dstack_b200.encode import encode_table
         from oracle import reference_path as ref
 
@@ -248,7 +248,8 @@ def run_ours(args, wl, rank: int, world: int, local_rank: int):
 
     import torch
 
-    from dstack_b200 import native, synth
+    from dstack_b200 import native
+    from workloads import synth
     from dstack_b200.sharded import ShardedMatcher, rank_order
 
     if not torch.cuda.is_available():

@@ -865,6 +865,13 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
 }
 
 #ifdef DSM_CTA_TIMING
+// debug builds only: start / end globaltimer of every job of the last k_extract
+int dsm_debug_job_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_jobs) {
+  USE_DEVICE(ctx->device);
+  CK(cudaStreamSynchronize(ctx->stream));
+  CK(cudaMemcpyFromSymbol(out, g_job_times, (size_t)n_jobs * 2 * 8));
+  return 0;
+}
 // debug builds only: copy the per-CTA (start ns, end ns, SM id) triples of the last k_match
 int dsm_debug_cta_times(dsm_ctx* ctx, unsigned long long* out, uint32_t n_ctas) {
   USE_DEVICE(ctx->device);

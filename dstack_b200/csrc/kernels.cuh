@@ -340,6 +340,7 @@ __global__ void __launch_bounds__(256) k_build_tables(const BuildParams p) {
 #ifdef DSM_CTA_TIMING
 // debug builds only (tools/cta_times.py): start / end globaltimer and SM id of every CTA
 __device__ unsigned long long g_cta_times[4096 * 3];
+__device__ unsigned long long g_job_times[65536 * 2];  // k_extract: start / end per job
 #endif
 
 template <int NC>
@@ -804,6 +805,10 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   const uint32_t n_slots = p.slots;
   const uint32_t n_chunks = (n_slots + 31u) / 32u;
   const uint32_t* cnt = p.part_cnt + (size_t)(live ? es : 0u) * p.slots;
+#ifdef DSM_CTA_TIMING
+  unsigned long long dbg_j0 = 0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(dbg_j0));
+#endif
   uint32_t* csum = chunk_sums + jl * n_chunks;
 
   {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
@@ -1069,6 +1074,14 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
       else if (p.price != nullptr && p.price[last_b] > p.price[last_a]) best = last_b;
     }
     p.out_max[job] = best;
+#ifdef DSM_CTA_TIMING
+    if (job < 65536u) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      g_job_times[job * 2 + 0] = dbg_j0;
+      g_job_times[job * 2 + 1] = t1;
+    }
+#endif
   }
 }
 

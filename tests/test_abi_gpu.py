@@ -6,7 +6,8 @@ import threading
 import numpy as np
 import pytest
 
-from dstack_b200 import native, synth
+from dstack_b200 import native
+from workloads import synth
 from dstack_b200.encode import encode_table, pack_jobs
 from dstack_b200.engine import Matcher
 

@@ -5,7 +5,7 @@ import numpy as np
 import pytest
 
 import device_emulator as emu
-from dstack_b200 import synth
+from workloads import synth
 from dstack_b200.encode import NO_ROW, encode_table, pack_jobs
 from dstack_b200.ingest import columns_from_offers, job_columns
 from dstack_b200.services import job_filter

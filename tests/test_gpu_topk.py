@@ -3,7 +3,7 @@
 import numpy as np
 import pytest
 
-from dstack_b200 import synth
+from workloads import synth
 from dstack_b200.encode import NO_ROW, encode_table, pack_jobs
 from oracle import columnar
 

@@ -3,7 +3,7 @@
 import numpy as np
 import pytest
 
-from dstack_b200 import synth
+from workloads import synth
 from dstack_b200.encode import encode_table
 from oracle import columnar
 from oracle import reference_path as ref

@@ -7,7 +7,8 @@ import dataclasses
 import numpy as np
 import pytest
 
-from dstack_b200 import models as M, synth
+from dstack_b200 import models as M
+from workloads import synth
 from dstack_b200.ingest import PoolParseCache, columns_from_pool_instances
 
 

@@ -15,7 +15,7 @@ import pytest
 from dstack_b200 import models as M
 from dstack_b200 import pools as PP
 from dstack_b200 import services as S
-from dstack_b200 import synth
+from workloads import synth
 from oracle import reference_path as ref
 
 BT = M.BackendType

@@ -7,7 +7,8 @@ import numpy as np
 import pytest
 
 from dstack_b200 import models as M
-from dstack_b200 import scheduler, services as S, synth
+from dstack_b200 import scheduler, services as S
+from workloads import synth
 from oracle import reference_path as ref
 
 pytestmark = pytest.mark.gpu

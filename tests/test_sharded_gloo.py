@@ -31,7 +31,8 @@ def _worker(rank, world, port, n_offers, n_jobs, k, chunk_rows, out):
     import torch.distributed as dist
 
     import device_emulator as emu
-    from dstack_b200 import sharded, synth
+    from dstack_b200 import sharded
+    from workloads import synth
     from dstack_b200.encode import encode_table, pack_jobs
     from oracle import columnar
 

@@ -21,7 +21,8 @@ import ctypes as C
 import numpy as np
 import pytest
 
-from dstack_b200 import native, synth
+from dstack_b200 import native
+from workloads import synth
 from dstack_b200.encode import encode_table, pack_jobs
 from oracle import columnar
 

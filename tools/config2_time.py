@@ -1,7 +1,8 @@
 import sys, time
 sys.path.insert(0, "/root/repo"); sys.path.insert(0, "/root/repo/tests")
 import numpy as np
-from dstack_b200 import synth, pools as PP
+from dstack_b200 import pools as PP
+from workloads import synth
 from dstack_b200.engine import Matcher
 from dstack_b200.ingest import PoolParseCache
 import test_configs as T

@@ -12,7 +12,8 @@ import sys
 import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from dstack_b200 import native, synth  # noqa: E402
+from dstack_b200 import native  # noqa: E402
+from workloads import synth  # noqa: E402
 from dstack_b200.encode import encode_table, pack_jobs  # noqa: E402
 from dstack_b200.engine import Matcher  # noqa: E402
 

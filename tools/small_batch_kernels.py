@@ -3,7 +3,8 @@ import os
 import sys
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
-from dstack_b200 import models as M, synth  # noqa: E402
+from dstack_b200 import models as M  # noqa: E402
+from workloads import synth  # noqa: E402
 from dstack_b200.encode import encode_table, pack_jobs  # noqa: E402
 from dstack_b200.engine import Matcher  # noqa: E402
 from dstack_b200.ingest import job_columns  # noqa: E402

@@ -18,10 +18,10 @@ from typing import Any, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
-from . import models as M
-from ._gpuhunt import QueryFilter
-from .encode import BACKEND_CODES, VENDOR_CODES, JobColumns, OfferColumns, ShapeTable
-from .ingest import JobFilter
+from dstack_b200 import models as M
+from dstack_b200._gpuhunt import QueryFilter
+from dstack_b200.encode import BACKEND_CODES, VENDOR_CODES, JobColumns, OfferColumns, ShapeTable
+from dstack_b200.ingest import JobFilter
 
 # provider weights of App. D, in project-backend order
 PROVIDERS: List[Tuple[str, float]] = [
