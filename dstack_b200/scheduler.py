@@ -10,6 +10,12 @@ the mutable state), and only the cheap part -- walking the jobs in order and ski
 that an earlier job took -- stays sequential on the host.  The result is exactly what the
 sequential reference loop produces for the same job order.
 
+``process_submitted_batch`` is the whole pass over SUBMITTED jobs
+(``process_submitted_jobs.py:115-260, 418-490``): waiting rules for followers, the pool step, and
+for the jobs the pool could not take the ``offers[:15]`` of ``_run_job_on_new_instance`` from ONE
+batched catalog match, tried in order through the caller's ``launch``; followers of a master
+placed in this pass are matched in a second phase against the master's backend and region.
+
 ``plan_slice`` is the ``get_plan`` aggregation (``server/services/runs.py:336-349``): pool offers
 first, stable re-partition by availability, first ``k`` / total / max price, computed from the
 catalog's device top-k instead of the full offer list.
@@ -18,7 +24,7 @@ catalog's device top-k instead of the full offer list.
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Any, List, Optional, Sequence, Tuple
+from typing import Any, Callable, Dict, List, Optional, Sequence, Tuple
 
 import numpy as np
 
@@ -140,3 +146,138 @@ def plan_slice(pool_offers: Sequence[Any], catalog: Any, top: TopK, job: int, k:
     if not np.isnan(top.max_price[job]):
         prices.append(float(top.max_price[job]))
     return first, total, (max(prices) if prices else None)
+
+
+# ---------------------------------------------------------------------------- the whole pass
+
+
+@dataclass
+class SubmittedJob:
+    """What ``_process_submitted_job`` reads of a SUBMITTED job and its run
+    (``process_submitted_jobs.py:115-260``)."""
+
+    run_id: Any
+    profile: Any
+    requirements: Any
+    job_num: int = 0
+    replica_num: int = 0
+    jobs_per_replica: int = 1               # > 1: a multinode task
+    fleet_model: Optional[Any] = None       # run_model.fleet (its ``id`` is read); None: the run has no fleet yet
+    cluster_placement: bool = False         # the fleet asks for InstanceGroupPlacement.CLUSTER
+    master_job_provisioning_data: Optional[Any] = None  # of a master provisioned in an earlier pass
+    volumes: Optional[List[List[Any]]] = None
+    privileged: bool = False
+    instance_mounts: bool = False
+
+
+@dataclass
+class JobOutcome:
+    status: str                       # "provisioning" | "terminating" | "waiting"
+    instance: Optional[Any] = None    # the pool row taken (None: a new instance, or nothing)
+    offer: Optional[Any] = None
+    job_provisioning_data: Optional[Any] = None
+
+
+def _open_to_jobs(pool_instances: Sequence[Any]) -> List[Any]:
+    # ``deleted == False and total_blocks > busy_blocks`` (process_submitted_jobs.py:186-193)
+    return [r for r in pool_instances
+            if not getattr(r, "deleted", False) and r.total_blocks is not None
+            and r.total_blocks > (r.busy_blocks or 0)]
+
+
+def process_submitted_batch(pool_instances: Sequence[Any], catalog: Any, jobs: Sequence[SubmittedJob],
+                            launch: Callable[[SubmittedJob, Any, Any], Any], *, k: int = 15,
+                            max_ticks: int = 2, matcher: Optional[Matcher] = None,
+                            parse_cache: Optional[Any] = None) -> List[JobOutcome]:
+    """One scheduler pass over ``jobs`` (in order) with both matching steps batched on the GPU.
+
+    Per tick: the jobs that need not wait (followers need their master's provisioning data, known
+    at the start of the tick; non-first jobs need the run's fleet) go through
+    :func:`assign_jobs_to_pool`; those left without an instance -- unless their profile says
+    REUSE, which ends them -- get ``offers[:k]`` from one ``catalog.match_topk`` call
+    (``exclude_not_available=True`` and each job's multinode / master / volumes / privileged /
+    instance-mount restrictions) and ``launch(job, backend, offer)`` is tried on them in order; an
+    exception means "next offer".  Jobs that waited run in the next tick (``max_ticks`` in all),
+    so the followers of a master placed in tick 1 are matched in tick 2 against the master's
+    backend and region.  Outcomes equal those of the sequential reference loop for the same job
+    order (``oracle/reference_path.py:process_submitted_jobs``)."""
+    from . import services as S
+
+    out = [JobOutcome("waiting") for _ in jobs]
+    master_jpd: Dict[Tuple[Any, int], Any] = {}
+    pending = list(range(len(jobs)))
+    for _ in range(max_ticks):
+        ready: List[int] = []
+        jpds: Dict[int, Any] = {}
+        waiting: List[int] = []
+        for i in pending:
+            job = jobs[i]
+            jpd = job.master_job_provisioning_data
+            if job.job_num != 0:
+                if jpd is None:
+                    jpd = master_jpd.get((job.run_id, job.replica_num))
+                if jpd is None:
+                    waiting.append(i)
+                    continue
+            if (job.job_num != 0 or job.replica_num != 0) and job.fleet_model is None:
+                waiting.append(i)
+                continue
+            ready.append(i)
+            jpds[i] = jpd
+        if ready:
+            # step 1: the pool, for every ready job at once
+            requests = [JobRequest(profile=jobs[i].profile, requirements=jobs[i].requirements,
+                                   fleet_model=jobs[i].fleet_model, multinode=jobs[i].jobs_per_replica > 1,
+                                   master_job_provisioning_data=jpds[i], volumes=jobs[i].volumes) for i in ready]
+            assigned = assign_jobs_to_pool(_open_to_jobs(pool_instances), requests, matcher=matcher,
+                                           parse_cache=parse_cache)
+            need_new: List[int] = []
+            for i, a in zip(ready, assigned):
+                if a.instance is not None:
+                    raw = a.instance.job_provisioning_data
+                    out[i] = JobOutcome("provisioning", a.instance, a.offer,
+                                        None if raw is None else M.JobProvisioningData.parse_raw(raw))
+                elif jobs[i].profile.creation_policy == M.CreationPolicy.REUSE:
+                    out[i] = JobOutcome("terminating")
+                else:
+                    need_new.append(i)
+            # step 2: a new instance, offers[:k] of every such job from one catalog match
+            if need_new:
+                filters = [S.job_filter(jobs[i].profile, jobs[i].requirements, exclude_not_available=True,
+                                        multinode=jobs[i].jobs_per_replica > 1 or jobs[i].cluster_placement,
+                                        master_job_provisioning_data=jpds[i], volumes=jobs[i].volumes,
+                                        privileged=jobs[i].privileged, instance_mounts=jobs[i].instance_mounts)
+                           for i in need_new]
+                top = catalog.match_topk(filters, k)
+                for row, i in enumerate(need_new):
+                    out[i] = JobOutcome("terminating")
+                    for backend, offer in catalog.pairs(top.index[row]):
+                        try:
+                            new_jpd = launch(jobs[i], backend, offer)
+                        except Exception:  # BackendError or anything else: next offer
+                            continue
+                        out[i] = JobOutcome("provisioning", None, offer, new_jpd)
+                        break
+            for i in ready:
+                if jobs[i].job_num == 0 and out[i].status == "provisioning":
+                    master_jpd[(jobs[i].run_id, jobs[i].replica_num)] = out[i].job_provisioning_data
+        pending = waiting
+        if not pending:
+            break
+    return out
+
+
+def placement_group_keys(offers: Sequence[Any], existing: Sequence[Tuple[Any, str]] = ()) -> List[Tuple[Any, str]]:
+    """The ``(backend, region)`` pairs for which trying ``offers`` in order creates a placement group
+    (``process_instances.py:523-544, 910-932``): one per pair not seen before, only for backends
+    with placement-group support.  The cloud call that creates the group is the caller's."""
+    seen = set(existing)
+    new: List[Tuple[Any, str]] = []
+    for o in offers:
+        if o.backend not in M.BACKENDS_WITH_PLACEMENT_GROUPS_SUPPORT:
+            continue
+        key = (o.backend, o.region)
+        if key not in seen:
+            seen.add(key)
+            new.append(key)
+    return new

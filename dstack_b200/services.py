@@ -225,6 +225,7 @@ class OfferCatalog:
         self.matcher = matcher or default_matcher()
         self.backends: List[Any] = []
         self.offers: List[Any] = []
+        self._materialize = None
         src = []
         for backend, offers in offers_by_backend:
             for o in offers:
@@ -233,6 +234,27 @@ class OfferCatalog:
                 src.append(backend.TYPE)
         self.table: EncodedTable = encode_table(columns_from_offers(self.offers, src))
         self.device_table: DeviceTable = self.matcher.upload(self.table)
+
+    @classmethod
+    def from_columns(cls, columns: Any, materialize, *, matcher: Optional[Matcher] = None) -> "OfferCatalog":
+        """A catalog that never existed as Python objects: ``columns`` is an
+        :class:`~dstack_b200.encode.OfferColumns` in source order (per-backend lists concatenated in
+        project-backend order, each price-sorted) and ``materialize(i) -> (backend, offer)`` builds
+        the objects of source position ``i`` on demand -- only the few rows a job's top-k names are
+        ever turned into objects (tens of millions of offers stay columnar)."""
+        self = cls.__new__(cls)
+        self.matcher = matcher or default_matcher()
+        self.backends, self.offers = None, None
+        self._materialize = materialize
+        self.table = encode_table(columns)
+        self.device_table = self.matcher.upload(self.table)
+        return self
+
+    def pair_at(self, i: int) -> Tuple[Any, Any]:
+        """``(backend, offer)`` of source position ``i``."""
+        if self._materialize is not None:
+            return self._materialize(int(i))
+        return self.backends[i], self.offers[i]
 
     def close(self) -> None:
         self.device_table.close()
@@ -248,7 +270,7 @@ class OfferCatalog:
         hits = self.matcher.match_all(self.device_table, self.jobs(filters), order="rank")
         out = []
         for f, rows in zip(filters, hits):
-            pairs = [(self.backends[i], self.offers[i]) for i in rows]
+            pairs = [self.pair_at(i) for i in rows]
             if f.require_auto_divisible or f.blocks > 1:  # offers.py:116 writes the count back
                 for _, o in pairs:
                     o.total_blocks = _blocks_of_offer(o, "auto" if f.require_auto_divisible else f.blocks)[1]
@@ -256,7 +278,7 @@ class OfferCatalog:
         return out
 
     def pairs(self, index_row: np.ndarray) -> List[Tuple[Any, Any]]:
-        return [(self.backends[i], self.offers[i]) for i in index_row if i >= 0]
+        return [self.pair_at(i) for i in index_row if i >= 0]
 
 
 class OfferCatalogCache:

@@ -102,6 +102,7 @@ class ShardedMatcher:
         self.rank, self.world = rank, world
         self.dev = torch.device("cuda", device)
         self.order = rank_order(full) if order is None else order
+        self.full = full
         self.chunk_rows = chunk_rows
         self.positions = shard_positions(self.order, rank, world, chunk_rows) if world > 1 else None
         cols = subset_columns(full, self.positions) if world > 1 else full
@@ -156,16 +157,22 @@ class ShardedMatcher:
         self._bufs = b
         return b
 
-    def step(self) -> None:
-        """One batch on the resident buffers; asynchronous on ``self.stream`` (call under it)."""
+    def step(self, marks=None) -> None:
+        """One batch on the resident buffers; asynchronous on ``self.stream`` (call under it).
+        ``marks``: four CUDA events recorded after the local match, the price gather, the
+        all-gather and the merge (bench.py's step breakdown)."""
         b, lib, h = self._bufs, self.native.lib(), self.matcher.handle
         check = self.native.check
+        mark = (lambda i: marks[i].record(self.stream)) if marks is not None else (lambda i: None)
         check(lib.dsm_match_topk_dev(h, self.device_table.handle, C.byref(b["lay"]), b["rec"].data_ptr(), b["j"], b["k"],
                                      b["idx"].data_ptr(), b["cnt"].data_ptr(), b["max"].data_ptr()))
+        mark(0)
         if self.world > 1:
             dist = self.dist
             check(lib.dsm_gather_price_dev(h, self.device_table.handle, b["max"].data_ptr(), b["j"], b["mp"].data_ptr()))
+            mark(1)
             dist.all_gather_into_tensor(b["g_out"], b["out"])  # the one exchange of the step
+            mark(2)
             g = b["g_out"]
             w_idx, w_cnt = b["j"] * b["k"], b["j"]
             base_ptr = g.data_ptr()
@@ -178,6 +185,7 @@ class ShardedMatcher:
             else:
                 check(lib.dsm_merge_shards_strided_dev(h, self.world, b["j"], b["k"], *fields,
                                                        self.base.data_ptr(), *outs))
+            mark(3)
 
     def result_in_source_space(self) -> Tuple[np.ndarray, np.ndarray, np.ndarray]:
         """(index [J,k] source positions, count [J], max_price [J]) of the last step, on every rank."""

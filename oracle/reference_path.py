@@ -414,3 +414,100 @@ def get_pool_offers(pool_instances: Sequence[Any], profile, requirements, *, mul
         pool_offers.append(offer)
     pool_offers.sort(key=lambda o: o.price)
     return pool_offers
+
+
+# --------------------------------------------------------------------------- the scheduler pass
+
+
+def pool_rows_open_to_jobs(pool_instances: Sequence[Any]) -> List[Any]:
+    """The rows ``_process_submitted_job`` fetches for a job:
+    ``deleted == False and total_blocks > busy_blocks``
+    (server/background/tasks/process_submitted_jobs.py:186-193; a NULL ``total_blocks`` fails the
+    SQL comparison, so such rows are not fetched at all)."""
+    return [r for r in pool_instances
+            if not getattr(r, "deleted", False) and r.total_blocks is not None
+            and r.total_blocks > (r.busy_blocks or 0)]
+
+
+def process_submitted_jobs(pool_instances: Sequence[Any], backends: Sequence[Any], jobs: Sequence[Any],
+                           launch: Callable[[Any, Any, Any], Any], *, max_ticks: int = 2, k: int = 15):
+    """The reference's one-job-at-a-time pass over SUBMITTED jobs
+    (server/background/tasks/process_submitted_jobs.py:115-260, 347-400, 418-490) without the DB:
+
+    * a follower (``job_num != 0``) waits until its master has provisioning data (:138-143), any
+      non-first job waits until the run has a fleet (:148-153);
+    * step 1 tries the pool (``assign_job_to_pool_instance``); the chosen row turns BUSY;
+    * step 2: no instance and ``creation_policy == REUSE`` -> terminating (:244-250); otherwise
+      ``get_offers_by_requirements(exclude_not_available=True, ...)[:15]`` are tried in order with
+      ``launch(job, backend, offer)``, a ``BackendError``-like exception moves on to the next offer
+      (:436-488); none left -> terminating (no capacity).
+
+    The reference spreads the two steps of a job over two passes of its background task; here a
+    *tick* runs both.  Whether a job waits is decided from the state at the START of a tick (what a
+    pass that fetched the job rows up front would see); jobs that waited are tried again in the
+    next tick, in their original order, for ``max_ticks`` ticks.  ``jobs`` carry the attributes of
+    ``dstack_b200.scheduler.SubmittedJob``.  Returns one ``(status, instance, offer, jpd)`` tuple
+    per job: status "provisioning" / "terminating" / "waiting"; ``instance`` is the pool row
+    (None for a new instance)."""
+    out: List[Any] = [("waiting", None, None, None)] * len(jobs)
+    master_jpd = {}
+    pending = list(range(len(jobs)))
+    for _ in range(max_ticks):
+        known = dict(master_jpd)  # state at the start of the tick
+        waiting = []
+        for i in pending:
+            job = jobs[i]
+            jpd = job.master_job_provisioning_data
+            if job.job_num != 0:
+                if jpd is None:
+                    jpd = known.get((job.run_id, job.replica_num))
+                if jpd is None:
+                    waiting.append(i)
+                    continue
+            if (job.job_num != 0 or job.replica_num != 0) and job.fleet_model is None:
+                waiting.append(i)
+                continue
+            multinode = job.jobs_per_replica > 1
+            res = assign_job_to_pool_instance(pool_rows_open_to_jobs(pool_instances), job.profile, job.requirements,
+                                              fleet_model=job.fleet_model, multinode=multinode,
+                                              master_job_provisioning_data=jpd, volumes=job.volumes)
+            if res is not None:
+                inst, offer = res
+                out[i] = ("provisioning", inst, offer, _jpd_of(inst))
+            elif job.profile.creation_policy == M.CreationPolicy.REUSE:
+                out[i] = ("terminating", None, None, None)
+            else:
+                offers = get_offers_by_requirements(
+                    backends, job.profile, job.requirements, exclude_not_available=True,
+                    multinode=multinode or job.cluster_placement, master_job_provisioning_data=jpd,
+                    volumes=job.volumes, privileged=job.privileged, instance_mounts=job.instance_mounts)
+                out[i] = ("terminating", None, None, None)
+                for backend, offer in offers[:k]:
+                    try:
+                        new_jpd = launch(job, backend, offer)
+                    except Exception:  # BackendError and anything else: next offer (:463-488)
+                        continue
+                    out[i] = ("provisioning", None, offer, new_jpd)
+                    break
+            if job.job_num == 0 and out[i][0] == "provisioning":
+                master_jpd[(job.run_id, job.replica_num)] = out[i][3]
+        pending = waiting
+        if not pending:
+            break
+    return out
+
+
+def placement_group_keys(offers: Sequence[Any], existing: Sequence[Tuple[Any, str]] = ()):
+    """``(backend, region)`` pairs for which trying ``offers`` in order creates a placement group
+    (server/background/tasks/process_instances.py:523-544, 910-932): the first offer of every
+    pair not seen before, for backends that support placement groups."""
+    seen = set(existing)
+    new = []
+    for o in offers:
+        if o.backend not in M.BACKENDS_WITH_PLACEMENT_GROUPS_SUPPORT:
+            continue
+        key = (o.backend, o.region)
+        if key not in seen:
+            seen.add(key)
+            new.append(key)
+    return new

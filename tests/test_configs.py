@@ -44,31 +44,7 @@ def test_config1_single_task_10k_offers(matcher):
     assert top.count[0] == total and top.max_price[0] == top_price
 
 
-def _config2_jobs(rows, n_jobs, seed=2):
-    """30% same-fleet, 20% multinode with a master node, 10% reuse by instance name."""
-    rng = np.random.Generator(np.random.PCG64(seed))
-    fleets = sorted({r.fleet_id for r in rows if r.fleet_id is not None}, key=str)
-    with_jpd = [r for r in rows if r.job_provisioning_data is not None]
-    specs = ["", "16GB..:1..8", "A100", "H100:8", "24GB..80GB:1..8", "T4,L4:1..4"]
-    calls = []
-    for j in range(n_jobs):
-        gpu = specs[int(rng.integers(0, len(specs)))]
-        req = M.Requirements(resources=M.ResourcesSpec(gpu=gpu or None, cpu=f"{int(rng.choice([1, 2, 4, 8]))}.."),
-                             max_price=None if rng.random() < 0.5 else float(np.round(rng.lognormal(1.0, 1.0), 2)),
-                             spot=None)
-        kw = dict(requirements=req, status=M.InstanceStatus.IDLE, shared=False)
-        profile = M.Profile(name="p")
-        u = rng.random()
-        if u < 0.3:
-            kw["fleet_model"] = types.SimpleNamespace(id=fleets[int(rng.integers(0, len(fleets)))])
-        elif u < 0.5:
-            jpd = M.JobProvisioningData.parse_raw(with_jpd[int(rng.integers(0, len(with_jpd)))].job_provisioning_data)
-            kw.update(multinode=True, master_job_provisioning_data=jpd)
-        elif u < 0.6:
-            profile = M.Profile(name="p", instance_name=rows[int(rng.integers(0, len(rows)))].name,
-                                creation_policy=M.CreationPolicy.REUSE)
-        calls.append((profile, kw))
-    return calls
+from workloads.configs import config2_jobs as _config2_jobs  # noqa: E402
 
 
 def test_config2_pool_1k_jobs_50k_instances(matcher):

@@ -11,7 +11,7 @@ from dstack_b200 import scheduler, services as S
 from workloads import synth
 from oracle import reference_path as ref
 
-pytestmark = pytest.mark.gpu
+gpu = pytest.mark.gpu
 
 
 def _requests(rows, n, seed):
@@ -33,6 +33,7 @@ def _requests(rows, n, seed):
     return out
 
 
+@gpu
 def test_batched_assignment_equals_sequential_reference(matcher):
     rows = synth.make_pool(4000, seed=31, n_fleets=25)
     jobs = _requests(rows, 300, seed=32)
@@ -58,6 +59,7 @@ def test_batched_assignment_equals_sequential_reference(matcher):
     assert [(r.status, r.busy_blocks) for r in rows] == [(r.status, r.busy_blocks) for r in seq_rows]
 
 
+@gpu
 def test_plan_slice_equals_reference_get_plan(matcher):
     cat = synth.make_catalog(3000, seed=33, n_shapes=200)
     per_backend = synth.catalog_objects(cat, filter_fn=ref.match_requirements)
@@ -85,3 +87,53 @@ def test_plan_slice_equals_reference_get_plan(matcher):
         assert len(kinds) >= 2
     finally:
         catalog.close()
+
+
+@gpu
+def test_process_submitted_batch_equals_sequential_reference(matcher):
+    """The whole pass -- waiting rules, pool step, offers[:15] of new instances with launch
+    failures, REUSE-only jobs, followers pinned to their master in the second tick -- against the
+    sequential restatement of process_submitted_jobs.py:115-260, 418-490."""
+    from workloads import configs
+
+    rows = synth.make_pool(1500, seed=61, n_fleets=12)
+    cat = synth.make_catalog(6000, seed=62, n_shapes=300)
+    per_backend = synth.catalog_objects(cat, filter_fn=ref.match_requirements)
+    backends = [b for b, _ in per_backend]
+    jobs = configs.scheduler_jobs(rows, 240, seed=63)
+    launch = configs.fake_launch(fail_every=3)
+    seq_rows = copy.deepcopy(rows)
+    want = ref.process_submitted_jobs(seq_rows, backends, jobs, launch)
+    catalog = S.OfferCatalog(per_backend, matcher=matcher)
+    try:
+        got = scheduler.process_submitted_batch(rows, catalog, jobs, launch, matcher=matcher)
+    finally:
+        catalog.close()
+    kinds = {"pool": 0, "new": 0, "terminating": 0, "waiting": 0, "follower_new": 0, "reuse_failed": 0}
+    for j, (g, w) in enumerate(zip(got, want)):
+        status, inst, offer, jpd = w
+        assert g.status == status, j
+        if status != "provisioning":
+            kinds[status] += 1
+            kinds["reuse_failed"] += jobs[j].profile.creation_policy == M.CreationPolicy.REUSE
+            continue
+        if inst is not None:
+            assert g.instance is rows[seq_rows.index(inst)], j
+            assert g.offer.json() == offer.json(), j
+            kinds["pool"] += 1
+        else:
+            assert g.instance is None and g.offer.json() == offer.json(), j
+            assert g.job_provisioning_data.json() == jpd.json(), j
+            kinds["new"] += 1
+            kinds["follower_new"] += jobs[j].job_num != 0
+    assert [(r.status, r.busy_blocks) for r in rows] == [(r.status, r.busy_blocks) for r in seq_rows]
+    assert kinds["pool"] > 40 and kinds["new"] > 40 and kinds["reuse_failed"] > 3 and kinds["follower_new"] > 5, kinds
+
+
+def test_placement_group_keys_first_offer_of_each_backend_region():
+    mk = lambda b, r: __import__("types").SimpleNamespace(backend=b, region=r)
+    offers = [mk(M.BackendType.AWS, "us-east-1"), mk(M.BackendType.GCP, "us-central1"), mk(M.BackendType.AWS, "us-east-1"),
+              mk(M.BackendType.AWS, "eu-west-1"), mk(M.BackendType.AWS, "us-west-2")]
+    existing = [(M.BackendType.AWS, "us-west-2")]
+    want = [(M.BackendType.AWS, "us-east-1"), (M.BackendType.AWS, "eu-west-1")]
+    assert scheduler.placement_group_keys(offers, existing) == want == ref.placement_group_keys(offers, existing)

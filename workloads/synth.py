@@ -154,29 +154,50 @@ class FakeBackend:
         return f"FakeBackend({self.TYPE.value})"
 
 
+_VENDOR_OF = {v: k for k, v in VENDOR_CODES.items()}
+
+
+def offer_object(cat: SynthCatalog, i: int) -> M.InstanceOfferWithAvailability:
+    """Offer ``i`` (source position) of a synthetic catalog as an object."""
+    oc, sh = cat.columns, cat.columns.shapes
+    sid = int(oc.shape_id[i])
+    n_gpu = int(sh.gpu_count[sid])
+    gpus = []
+    if n_gpu:
+        gpus = [M.Gpu(name=sh.gpu_name[sid], vendor=_VENDOR_OF[int(sh.gpu_vendor[sid])],
+                      memory_mib=int(round(sh.gpu_memory_gib[sid] * 1024)))] * n_gpu
+    res = M.Resources(cpus=int(sh.cpus[sid]), memory_mib=int(round(sh.memory_gib[sid] * 1024)),
+                      gpus=gpus, spot=bool(oc.spot[i]),
+                      disk=M.Disk(size_mib=int(round(sh.disk_gib[sid] * 1024))))
+    pname = cat.providers[provider_of(cat, i)]
+    return M.InstanceOfferWithAvailability(
+        backend=M.BackendType(pname), region=oc.regions[int(oc.region_id[i])], price=float(oc.price[i]),
+        instance=M.InstanceType(name=oc.itypes[int(oc.itype_id[i])], resources=res),
+        availability=AVAILABILITY[int(cat.availability[i])])
+
+
+def provider_of(cat: SynthCatalog, i: int) -> int:
+    """Index of the provider whose price-sorted list holds source position ``i``."""
+    for p, (s, e) in enumerate(cat.backend_slices):
+        if s <= i < e:
+            return p
+    raise IndexError(i)
+
+
 def catalog_objects(cat: SynthCatalog, filter_fn=None) -> List[Tuple[FakeBackend, List[M.InstanceOfferWithAvailability]]]:
     """Materialise a (small) synthetic catalog as per-backend offer lists."""
-    oc, sh = cat.columns, cat.columns.shapes
-    vendor_of = {v: k for k, v in VENDOR_CODES.items()}
     out = []
     for pname, (s, e) in zip(cat.providers, cat.backend_slices):
-        offers = []
-        for i in range(s, e):
-            sid = int(oc.shape_id[i])
-            n_gpu = int(sh.gpu_count[sid])
-            gpus = []
-            if n_gpu:
-                gpus = [M.Gpu(name=sh.gpu_name[sid], vendor=vendor_of[int(sh.gpu_vendor[sid])],
-                              memory_mib=int(round(sh.gpu_memory_gib[sid] * 1024)))] * n_gpu
-            res = M.Resources(cpus=int(sh.cpus[sid]), memory_mib=int(round(sh.memory_gib[sid] * 1024)),
-                              gpus=gpus, spot=bool(oc.spot[i]),
-                              disk=M.Disk(size_mib=int(round(sh.disk_gib[sid] * 1024))))
-            offers.append(M.InstanceOfferWithAvailability(
-                backend=M.BackendType(pname), region=oc.regions[int(oc.region_id[i])], price=float(oc.price[i]),
-                instance=M.InstanceType(name=oc.itypes[int(oc.itype_id[i])], resources=res),
-                availability=AVAILABILITY[int(cat.availability[i])]))
+        offers = [offer_object(cat, i) for i in range(s, e)]
         out.append((FakeBackend(M.BackendType(pname), offers, filter_fn), offers))
     return out
+
+
+def lazy_catalog(cat: SynthCatalog):
+    """``(backends, materialize)`` for :meth:`dstack_b200.services.OfferCatalog.from_columns`: one
+    :class:`FakeBackend` per provider (no offer objects) and ``materialize(i) -> (backend, offer)``."""
+    backends = [FakeBackend(M.BackendType(p), []) for p in cat.providers]
+    return backends, (lambda i: (backends[provider_of(cat, i)], offer_object(cat, i)))
 
 
 # ---------------------------------------------------------------------------- jobs
