@@ -70,6 +70,11 @@ struct dsm_table {
   uint32_t* gpu_entries;
   uint32_t* bk_entries;
   uint32_t* pair_entries;
+  double* dicts;                          // the DSM_N_PACK_DICTS value lists, one after the other
+  uint32_t dict_n[DSM_N_PACK_DICTS];
+  uint32_t dict_off[DSM_N_PACK_DICTS];
+  int32_t* row_to_source;                 // [n_rows], -1 on padding rows
+  uint32_t n_source;
 };
 
 // events around the launches of one call: build | match | extract (n = events used)
@@ -102,6 +107,11 @@ struct dsm_ctx {
   size_t timing_used = 0;
   DevBuf tabs, counter, part_cnt, win_rows, slot_start, group_nact, d_jobs, d_order, d_idx, d_cnt, d_max, d_bits;
   DevBuf lut[DSM_MAX_COLS];
+  DevBuf d_raw, d_ids, d_keys, d_sbits, d_cnt64, d_ptr64, d_out_ids;
+  void* h_out_ids = nullptr;  // pinned, dsm_match_indices' result
+  size_t h_out_cap = 0;
+  void* h_stage = nullptr;    // pinned, raw jobs + ids laid out by dsm_match_topk_cols
+  size_t h_stage_cap = 0;
 };
 
 // Every entry point makes the context's device current for its own work and puts the caller's
@@ -228,9 +238,9 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   // Units per resident CTA: many short units balance the SMs (8 per CTA measured best on a
   // 128-group batch over 8 M rows: 3.73 ms against 3.84 with 4 and 4.10 with 2), but every unit
   // stages its group's table first, so a warp's share of a unit is kept at MIN_WPW windows or more
-  // (4096 jobs x 1 M rows: 0.146 ms with 10 windows per warp against 0.154 with 5 and 0.168 with 2)
+  // (4096 jobs x 1 M rows: 0.146 ms with 10 windows per warp, 0.154 with 5, 0.168 with 2)
   // -- unless that would leave CTAs without any unit.
-  const uint32_t MIN_WPW = 10;
+  const uint32_t MIN_WPW = 8;  // k_extract reads the records of slots of up to 8 windows a chunk of slots at a time
   const uint32_t units_per_cta = ctx->units_per_cta ? ctx->units_per_cta : 8u;
   const uint32_t a_blocks = pl.split_block, b_blocks = pl.n_blocks - pl.split_block;
   const unsigned long long n_win = (unsigned long long)Pieces::windows(a_blocks) + Pieces::windows(b_blocks);
@@ -415,8 +425,18 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     gp.out_max = d_max;
     // few slots per job: a warp per job; thousands (small batches): a CTA per job
     const uint32_t chunk_bytes = (pl.slots + 31u) / 32u * 4u;
-    if (pl.slots >= 1024u) k_extract<8><<<n_jobs, 256, chunk_bytes, ctx->stream>>>(gp);
-    else k_extract<1><<<(n_jobs + 7) / 8, 256, 8u * chunk_bytes, ctx->stream>>>(gp);
+    const bool wide = pl.slots >= 1024u;
+    const dim3 grid(wide ? n_jobs : (n_jobs + 7) / 8);
+    const uint32_t sm_bytes = wide ? chunk_bytes : 8u * chunk_bytes;
+#define EXTRACT(W, R, L) k_extract<W, R, L><<<grid, 256, sm_bytes, ctx->stream>>>(gp)
+    if (wide) {
+      if (row32) { if (has_lut) EXTRACT(8, true, true); else EXTRACT(8, true, false); }
+      else       { if (has_lut) EXTRACT(8, false, true); else EXTRACT(8, false, false); }
+    } else {
+      if (row32) { if (has_lut) EXTRACT(1, true, true); else EXTRACT(1, true, false); }
+      else       { if (has_lut) EXTRACT(1, false, true); else EXTRACT(1, false, false); }
+    }
+#undef EXTRACT
     CK(cudaGetLastError());
     ctx->launches++;
     if (tev) CK(cudaEventRecord(tev->e[3], ctx->stream));
@@ -485,7 +505,10 @@ int dsm_ctx_destroy(dsm_ctx* ctx) {
   DeviceGuard guard_(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   DevBuf* bufs[] = {&ctx->tabs, &ctx->counter, &ctx->part_cnt, &ctx->win_rows, &ctx->slot_start, &ctx->group_nact,
-                    &ctx->d_jobs, &ctx->d_order, &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits};
+                    &ctx->d_jobs, &ctx->d_order, &ctx->d_idx, &ctx->d_cnt, &ctx->d_max, &ctx->d_bits,
+                    &ctx->d_raw, &ctx->d_ids, &ctx->d_keys, &ctx->d_sbits, &ctx->d_cnt64, &ctx->d_ptr64, &ctx->d_out_ids};
+  if (ctx->h_out_ids) cudaFreeHost(ctx->h_out_ids);
+  if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
   for (DevBuf* b : bufs) if (b->p) cudaFree(b->p);
   for (int c = 0; c < DSM_MAX_COLS; ++c) if (ctx->lut[c].p) cudaFree(ctx->lut[c].p);
   for (auto& ev : ctx->timing_events) for (cudaEvent_t e : ev.e) cudaEventDestroy(e);
@@ -559,11 +582,48 @@ int dsm_table_destroy(dsm_table* t) {
   if (!t) return 0;
   DeviceGuard guard_(t->device);
   if (t->pair_entries) cudaFree(t->pair_entries);
+  if (t->dicts) cudaFree(t->dicts);
+  if (t->row_to_source) cudaFree(t->row_to_source);
   if (t->rows) cudaFree(t->rows);
   if (t->price) cudaFree(t->price);
   if (t->gpu_entries) cudaFree(t->gpu_entries);
   if (t->bk_entries) cudaFree(t->bk_entries);
   delete t;
+  return 0;
+}
+
+int dsm_table_set_pack_dicts(dsm_ctx* ctx, dsm_table* t, const double* values,
+                             const uint32_t counts[DSM_N_PACK_DICTS]) {
+  if (!ctx || !t || !values || !counts) return fail(DSM_E_ARG, "NULL argument");
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  size_t total = 0;
+  for (int i = 0; i < DSM_N_PACK_DICTS; ++i) {
+    if (counts[i] > 65536) return fail(DSM_E_ARG, "a value list has more than 65536 entries");
+    t->dict_off[i] = (uint32_t)total;
+    t->dict_n[i] = counts[i];
+    total += counts[i];
+  }
+  if (t->dicts) { CK(cudaFree(t->dicts)); t->dicts = nullptr; }
+  CK(cudaMalloc((void**)&t->dicts, (total + 1) * 8));
+  if (total) CK(cudaMemcpyAsync(t->dicts, values, total * 8, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int dsm_table_set_source_map(dsm_ctx* ctx, dsm_table* t, const int32_t* row_to_source, uint32_t n_source) {
+  if (!ctx || !t || !row_to_source) return fail(DSM_E_ARG, "NULL argument");
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  for (uint32_t r = 0; r < t->desc.n_rows; ++r)
+    if (row_to_source[r] >= (int64_t)n_source) return fail(DSM_E_ARG, "row_to_source entry >= n_source");
+  if (t->row_to_source) { CK(cudaFree(t->row_to_source)); t->row_to_source = nullptr; }
+  CK(cudaMalloc((void**)&t->row_to_source, (size_t)t->desc.n_rows * 4));
+  CK(cudaMemcpyAsync(t->row_to_source, row_to_source, (size_t)t->desc.n_rows * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  t->n_source = n_source;
   return 0;
 }
 
@@ -577,6 +637,309 @@ int dsm_lut_upload(dsm_ctx* ctx, uint32_t column, const uint16_t* lut, uint32_t 
   CK(cudaMemcpyAsync(ctx->lut[column].p, lut, (size_t)n * 2, cudaMemcpyHostToDevice, ctx->stream));
   CK(cudaStreamSynchronize(ctx->stream));
   *dev_out = (const uint16_t*)ctx->lut[column].p;
+  return 0;
+}
+
+// k_pack_jobs (+ k_order_jobs) on the context's stream.  Caller holds ctx->mu, device current.
+static int run_pack(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, const dsm_raw_job* d_raw, uint32_t n_jobs,
+                    const int32_t* d_ids, uint32_t* d_records, uint32_t* d_order) {
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  if (!t->dicts) return fail(DSM_E_ARG, "the table has no value lists: call dsm_table_set_pack_dicts first");
+  if (L->job_order) return fail(DSM_E_ARG, "layout.job_order must be NULL when the records are built on the device");
+  Plan pl;
+  int rc = make_plan(ctx, t, L, n_jobs, pl);  // validates the layout
+  if (rc) return rc;
+  PackParams pp;
+  memset(&pp, 0, sizeof pp);
+  pp.raw = d_raw;
+  pp.ids = d_ids;
+  pp.n_jobs = n_jobs;
+  pp.lay = pl.lay;
+  for (uint32_t c = 0; c < L->n_used; ++c) {
+    if (L->lut[c]) return fail(DSM_E_ARG, "columns with a per-call remap cannot be packed on the device");
+    const uint32_t role = L->role[c], kind = L->kind[c];
+    const bool ok = (role == DSM_ROLE_CPU && (kind == DSM_COL_RANGE || kind == DSM_COL_BITSET)) ||
+                    ((role == DSM_ROLE_MEMORY || role == DSM_ROLE_DISK) && kind == DSM_COL_RANGE) ||
+                    (role == DSM_ROLE_CPU_MEMORY && kind == DSM_COL_PAIR) || (role == DSM_ROLE_GPU && kind == DSM_COL_GPU) ||
+                    (role == DSM_ROLE_BK && kind == DSM_COL_BK) ||
+                    (role >= DSM_ROLE_REGION && role <= DSM_ROLE_ZONE && kind == DSM_COL_BITSET);
+    if (!ok) return fail(DSM_E_ARG, "layout.role does not fit the column's kind");
+    if (role == DSM_ROLE_CPU && kind == DSM_COL_BITSET && L->card[c] != t->dict_n[DSM_DICT_CPU])
+      return fail(DSM_E_ARG, "cpu bitset column: card != number of cpu values");
+    pp.role[c] = role;
+  }
+  for (int i = 0; i < DSM_N_PACK_DICTS; ++i) {
+    pp.dict[i] = t->dicts + t->dict_off[i];
+    pp.dict_n[i] = t->dict_n[i];
+  }
+  if (!t->price) return fail(DSM_E_ARG, "the table has no prices (needed for max_price cut-offs)");
+  pp.price = t->price;
+  pp.n_live_a = t->desc.n_live_a;
+  pp.split_row = t->desc.split_row;
+  pp.n_live_b = t->desc.n_live_b;
+  pp.recs = d_records;
+  pp.keys = nullptr;
+  if (d_order) {
+    if ((rc = ensure(ctx->d_keys, (size_t)n_jobs * 4))) return rc;
+    pp.keys = (uint32_t*)ctx->d_keys.p;
+  }
+  k_pack_jobs<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(pp);
+  CK(cudaGetLastError());
+  ctx->launches++;
+  if (d_order) {
+    k_order_jobs<<<1, 1024, 0, ctx->stream>>>(pp.keys, n_jobs, d_order);
+    CK(cudaGetLastError());
+    ctx->launches++;
+  }
+  return 0;
+}
+
+int dsm_jobs_pack_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_raw_job* d_jobs,
+                      uint32_t n_jobs, const int32_t* d_ids, uint32_t* d_records, uint32_t* d_order) {
+  if (!ctx || !t || !layout || !d_jobs || !d_records) return fail(DSM_E_ARG, "NULL argument");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  return run_pack(ctx, t, layout, d_jobs, n_jobs, d_ids, d_records, d_order);
+}
+
+static int match_topk_raw_locked(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_raw_job* jobs,
+                                 uint32_t n_jobs, const int32_t* ids, uint32_t n_ids, uint32_t k, uint32_t* out_idx,
+                                 uint32_t* out_cnt, uint32_t* out_max, int32_t* out_src, double* out_max_price);
+
+// Shared by the two raw-job entry points.  src != NULL: answer in source positions / prices.
+static int match_topk_raw(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_raw_job* jobs,
+                          uint32_t n_jobs, const int32_t* ids, uint32_t n_ids, uint32_t k, uint32_t* out_idx,
+                          uint32_t* out_cnt, uint32_t* out_max, int32_t* out_src, double* out_max_price) {
+  if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
+  if (k == 0 || k > 4096) return fail(DSM_E_ARG, "k must be in 1..4096");
+  if (layout->rec_words < 3 || layout->rec_words > 65536) return fail(DSM_E_ARG, "layout.rec_words out of range");
+  if (out_src && !t->row_to_source)
+    return fail(DSM_E_ARG, "the table has no source map: call dsm_table_set_source_map first");
+  // the id ranges of every job must lie inside the id array (the kernel would read outside it)
+  for (uint32_t j = 0; j < n_jobs; ++j) {
+    const dsm_raw_job& r = jobs[j];
+    const unsigned long long ends[4] = {(unsigned long long)r.gpu_name_off + r.gpu_name_cnt,
+                                        (unsigned long long)r.region_off + r.region_cnt,
+                                        (unsigned long long)r.itype_off + r.itype_cnt,
+                                        (unsigned long long)r.zone_off + r.zone_cnt};
+    for (unsigned long long e : ends)
+      if (e > n_ids) return fail(DSM_E_ARG, "a raw job's id range reaches past the id array");
+  }
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  return match_topk_raw_locked(ctx, t, layout, jobs, n_jobs, ids, n_ids, k, out_idx, out_cnt, out_max, out_src,
+                               out_max_price);
+}
+
+// Caller holds ctx->mu, device current, arguments validated.
+static int match_topk_raw_locked(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_raw_job* jobs,
+                                 uint32_t n_jobs, const int32_t* ids, uint32_t n_ids, uint32_t k, uint32_t* out_idx,
+                                 uint32_t* out_cnt, uint32_t* out_max, int32_t* out_src, double* out_max_price) {
+  int rc;
+  if ((rc = ensure(ctx->d_raw, (size_t)n_jobs * sizeof(dsm_raw_job)))) return rc;
+  if ((rc = ensure(ctx->d_ids, (size_t)(n_ids + 1) * 4))) return rc;
+  if ((rc = ensure(ctx->d_jobs, (size_t)n_jobs * layout->rec_words * 4))) return rc;
+  if ((rc = ensure(ctx->d_order, (size_t)n_jobs * 4))) return rc;
+  if ((rc = ensure(ctx->d_idx, (size_t)n_jobs * k * 4))) return rc;
+  if ((rc = ensure(ctx->d_cnt, (size_t)n_jobs * 4))) return rc;
+  if ((rc = ensure(ctx->d_max, (size_t)n_jobs * 4))) return rc;
+  CK(cudaMemcpyAsync(ctx->d_raw.p, jobs, (size_t)n_jobs * sizeof(dsm_raw_job), cudaMemcpyHostToDevice, ctx->stream));
+  if (n_ids) CK(cudaMemcpyAsync(ctx->d_ids.p, ids, (size_t)n_ids * 4, cudaMemcpyHostToDevice, ctx->stream));
+  uint32_t* d_order = n_jobs > JPG ? (uint32_t*)ctx->d_order.p : nullptr;  // one group: nothing to order
+  rc = run_pack(ctx, t, layout, (const dsm_raw_job*)ctx->d_raw.p, n_jobs, (const int32_t*)ctx->d_ids.p,
+                (uint32_t*)ctx->d_jobs.p, d_order);
+  if (rc) return rc;
+  rc = run_match(ctx, t, layout, (const uint32_t*)ctx->d_jobs.p, d_order, n_jobs, k, false,
+                 (uint32_t*)ctx->d_idx.p, (uint32_t*)ctx->d_cnt.p, (uint32_t*)ctx->d_max.p, nullptr);
+  if (rc) return rc;
+  if (out_src) {
+    // rows -> source positions and the max row's price, on the device: [src J*k | price J]
+    const size_t n = (size_t)n_jobs * k;
+    if ((rc = ensure(ctx->d_out_ids, n * 4 + (size_t)n_jobs * 8 + 8))) return rc;
+    int32_t* d_src = (int32_t*)ctx->d_out_ids.p;
+    double* d_price = (double*)((char*)ctx->d_out_ids.p + (n * 4 + 7) / 8 * 8);
+    k_rows_to_source<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>((const uint32_t*)ctx->d_idx.p, (uint32_t)n,
+                                                                          t->row_to_source, d_src);
+    k_gather_price<<<(n_jobs + 255) / 256, 256, 0, ctx->stream>>>(t->price, (const uint32_t*)ctx->d_max.p, n_jobs, d_price);
+    CK(cudaGetLastError());
+    ctx->launches += 2;
+    CK(cudaMemcpyAsync(out_src, d_src, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(out_max_price, d_price, (size_t)n_jobs * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  } else {
+    CK(cudaMemcpyAsync(out_idx, ctx->d_idx.p, (size_t)n_jobs * k * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(out_max, ctx->d_max.p, (size_t)n_jobs * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CK(cudaMemcpyAsync(out_cnt, ctx->d_cnt.p, (size_t)n_jobs * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
+int dsm_match_topk_raw(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_raw_job* jobs,
+                       uint32_t n_jobs, const int32_t* ids, uint32_t n_ids, uint32_t k, uint32_t* out_idx,
+                       uint32_t* out_cnt, uint32_t* out_max) {
+  if (!ctx || !t || !layout || !jobs || !out_idx || !out_cnt || !out_max || (n_ids && !ids))
+    return fail(DSM_E_ARG, "NULL argument");
+  return match_topk_raw(ctx, t, layout, jobs, n_jobs, ids, n_ids, k, out_idx, out_cnt, out_max, nullptr, nullptr);
+}
+
+int dsm_match_topk_raw_src(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_raw_job* jobs,
+                           uint32_t n_jobs, const int32_t* ids, uint32_t n_ids, uint32_t k, int32_t* out_src,
+                           uint32_t* out_cnt, double* out_max_price) {
+  if (!ctx || !t || !layout || !jobs || !out_src || !out_cnt || !out_max_price || (n_ids && !ids))
+    return fail(DSM_E_ARG, "NULL argument");
+  return match_topk_raw(ctx, t, layout, jobs, n_jobs, ids, n_ids, k, nullptr, out_cnt, nullptr, out_src, out_max_price);
+}
+
+int dsm_match_topk_cols(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const dsm_job_columns* c,
+                        uint32_t n_jobs, uint32_t k, int32_t* out_src, uint32_t* out_cnt, double* out_max_price) {
+  if (!ctx || !t || !layout || !c || !out_src || !out_cnt || !out_max_price) return fail(DSM_E_ARG, "NULL argument");
+  if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
+  if (k == 0 || k > 4096) return fail(DSM_E_ARG, "k must be in 1..4096");
+  if (layout->rec_words < 3 || layout->rec_words > 65536) return fail(DSM_E_ARG, "layout.rec_words out of range");
+  if (!t->row_to_source) return fail(DSM_E_ARG, "the table has no source map: call dsm_table_set_source_map first");
+  if (!c->max_price || !c->cpu || !c->memory || !c->disk || !c->gpu_count || !c->gpu_memory || !c->gpu_total ||
+      !c->cc_min || !c->src_backend_mask || !c->off_backend_mask || !c->spot || !c->gpu_vendor)
+    return fail(DSM_E_ARG, "dsm_job_columns: a required column is NULL");
+  struct Csr { const int64_t* ptr; const int64_t* ids; } sets[4] = {
+      {c->gpu_name_ptr, c->gpu_name_ids}, {c->region_ptr, c->region_ids}, {c->itype_ptr, c->itype_ids},
+      {c->zone_ptr, c->zone_ids}};
+  unsigned long long n_ids = 0;
+  for (const Csr& s : sets) {
+    if (!s.ptr) continue;
+    if (s.ptr[0] != 0 || s.ptr[n_jobs] < 0 || (s.ptr[n_jobs] > 0 && !s.ids))
+      return fail(DSM_E_ARG, "dsm_job_columns: malformed CSR set");
+    for (uint32_t j = 0; j < n_jobs; ++j)
+      if (s.ptr[j + 1] < s.ptr[j]) return fail(DSM_E_ARG, "dsm_job_columns: CSR pointers must not decrease");
+    n_ids += (unsigned long long)s.ptr[n_jobs];
+  }
+  if (n_ids > 0x7FFFFFFFull) return fail(DSM_E_TOO_LARGE, "more than 2^31 set members in one call");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  const size_t raw_bytes = (size_t)n_jobs * sizeof(dsm_raw_job);
+  const size_t need = raw_bytes + (size_t)(n_ids + 1) * 4;
+  if (need > ctx->h_stage_cap) {
+    if (ctx->h_stage) CK(cudaFreeHost(ctx->h_stage));
+    ctx->h_stage = nullptr;
+    ctx->h_stage_cap = 0;
+    CK(cudaHostAlloc(&ctx->h_stage, need + need / 4 + 4096, cudaHostAllocDefault));
+    ctx->h_stage_cap = need + need / 4 + 4096;
+  }
+  dsm_raw_job* raw = (dsm_raw_job*)ctx->h_stage;
+  int32_t* ids = (int32_t*)((char*)ctx->h_stage + raw_bytes);
+  uint32_t base[4], at = 0;
+  for (int s = 0; s < 4; ++s) {
+    base[s] = at;
+    if (!sets[s].ptr) continue;
+    const int64_t n = sets[s].ptr[n_jobs];
+    for (int64_t i = 0; i < n; ++i) ids[at + i] = (int32_t)sets[s].ids[i];
+    at += (uint32_t)n;
+  }
+  for (uint32_t j = 0; j < n_jobs; ++j) {
+    dsm_raw_job& r = raw[j];
+    r.max_price = c->max_price[j];
+    r.cpu[0] = c->cpu[2 * j]; r.cpu[1] = c->cpu[2 * j + 1];
+    r.memory[0] = c->memory[2 * j]; r.memory[1] = c->memory[2 * j + 1];
+    r.disk[0] = c->disk[2 * j]; r.disk[1] = c->disk[2 * j + 1];
+    r.gpu_count[0] = c->gpu_count[2 * j]; r.gpu_count[1] = c->gpu_count[2 * j + 1];
+    r.gpu_memory[0] = c->gpu_memory[2 * j]; r.gpu_memory[1] = c->gpu_memory[2 * j + 1];
+    r.gpu_total[0] = c->gpu_total[2 * j]; r.gpu_total[1] = c->gpu_total[2 * j + 1];
+    r.cc_min = (int32_t)c->cc_min[j];
+    const int64_t b = c->blocks ? c->blocks[j] : 0;
+    if (b > 0xFFFF) return fail(DSM_E_ARG, "block counts above 65535 are not supported");
+    r.blocks = (int32_t)b;
+    r.src_backend_mask = c->src_backend_mask[j];
+    r.off_backend_mask = c->off_backend_mask[j];
+    r.flag_req = c->flag_req ? c->flag_req[j] : 0;
+    r.flag_forbid = c->flag_forbid ? c->flag_forbid[j] : 0;
+    r.status_mask = c->status_mask ? c->status_mask[j] : 0xFF;
+    r.spot = c->spot[j];
+    r.gpu_vendor = c->gpu_vendor[j];
+    uint8_t fl = 0;
+    if (c->exclude_not_available && c->exclude_not_available[j]) fl |= DSM_RAWF_EXCLUDE_NOT_AVAILABLE;
+    if (!c->gpu_name_any || c->gpu_name_any[j]) fl |= DSM_RAWF_GPU_NAME_ANY;
+    if (!c->region_any || c->region_any[j]) fl |= DSM_RAWF_REGION_ANY;
+    if (!c->itype_any || c->itype_any[j]) fl |= DSM_RAWF_ITYPE_ANY;
+    if (!c->fleet_any || c->fleet_any[j]) fl |= DSM_RAWF_FLEET_ANY;
+    if (!c->name_any || c->name_any[j]) fl |= DSM_RAWF_NAME_ANY;
+    if (!c->zone_any || c->zone_any[j]) fl |= DSM_RAWF_ZONE_ANY;
+    r.flags = fl;
+    r.fleet_id = c->fleet_ids ? (int32_t)c->fleet_ids[j] : -1;
+    r.name_id = c->name_ids ? (int32_t)c->name_ids[j] : -1;
+    uint32_t* oc[4][2] = {{&r.gpu_name_off, &r.gpu_name_cnt}, {&r.region_off, &r.region_cnt},
+                          {&r.itype_off, &r.itype_cnt}, {&r.zone_off, &r.zone_cnt}};
+    for (int s = 0; s < 4; ++s) {
+      *oc[s][0] = base[s] + (sets[s].ptr ? (uint32_t)sets[s].ptr[j] : 0u);
+      *oc[s][1] = sets[s].ptr ? (uint32_t)(sets[s].ptr[j + 1] - sets[s].ptr[j]) : 0u;
+    }
+  }
+  return match_topk_raw_locked(ctx, t, layout, raw, n_jobs, ids, (uint32_t)n_ids, k, nullptr, out_cnt, nullptr, out_src,
+                               out_max_price);
+}
+
+int dsm_match_indices(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const uint32_t* jobs,
+                      uint32_t n_jobs, int by_source, uint64_t* out_ptr, const uint32_t** out_ids) {
+  if (!ctx || !t || !layout || !jobs || !out_ptr || !out_ids) return fail(DSM_E_ARG, "NULL argument");
+  if (n_jobs == 0) return fail(DSM_E_ARG, "n_jobs must be > 0");
+  if (layout->rec_words < 3 || layout->rec_words > 65536) return fail(DSM_E_ARG, "layout.rec_words out of range");
+  if (!t->row_to_source) return fail(DSM_E_ARG, "the table has no source map: call dsm_table_set_source_map first");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  int rc;
+  const uint32_t n_words = t->desc.n_rows / 32u;
+  const uint32_t s_words = (t->n_source + 31u) / 32u;
+  const size_t jb = (size_t)n_jobs * layout->rec_words * 4;
+  if ((rc = ensure(ctx->d_jobs, jb))) return rc;
+  if ((rc = ensure(ctx->d_bits, (size_t)n_jobs * n_words * 4))) return rc;
+  if ((rc = ensure(ctx->d_cnt64, (size_t)n_jobs * 8))) return rc;
+  if ((rc = ensure(ctx->d_ptr64, ((size_t)n_jobs + 1) * 8))) return rc;
+  CK(cudaMemcpyAsync(ctx->d_jobs.p, jobs, jb, cudaMemcpyHostToDevice, ctx->stream));
+  const uint32_t* d_order = nullptr;
+  if ((rc = upload_order(ctx, layout, n_jobs, &d_order))) return rc;
+  rc = run_match(ctx, t, layout, (const uint32_t*)ctx->d_jobs.p, d_order, n_jobs, 1, true, nullptr, nullptr, nullptr,
+                 (uint32_t*)ctx->d_bits.p);
+  if (rc) return rc;
+  const uint32_t* bits = (const uint32_t*)ctx->d_bits.p;
+  uint32_t words = n_words;
+  const int32_t* map = t->row_to_source;
+  if (by_source) {  // re-file every match under its source position, then list the set bits in order
+    if ((rc = ensure(ctx->d_sbits, (size_t)n_jobs * s_words * 4 + 4))) return rc;
+    CK(cudaMemsetAsync(ctx->d_sbits.p, 0, (size_t)n_jobs * s_words * 4, ctx->stream));
+    const size_t total = (size_t)n_jobs * n_words;
+    k_scatter_to_source<<<(unsigned)((total + 255) / 256), 256, 0, ctx->stream>>>(
+        bits, n_jobs, n_words, t->row_to_source, (uint32_t*)ctx->d_sbits.p, s_words);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    bits = (const uint32_t*)ctx->d_sbits.p;
+    words = s_words;
+    map = nullptr;
+  }
+  k_count_bits<<<(n_jobs + 7) / 8, 256, 0, ctx->stream>>>(bits, n_jobs, words, (unsigned long long*)ctx->d_cnt64.p);
+  k_prefix_u64<<<1, 1024, 0, ctx->stream>>>((const unsigned long long*)ctx->d_cnt64.p, n_jobs,
+                                             (unsigned long long*)ctx->d_ptr64.p);
+  CK(cudaGetLastError());
+  ctx->launches += 2;
+  CK(cudaMemcpyAsync(out_ptr, ctx->d_ptr64.p, ((size_t)n_jobs + 1) * 8, cudaMemcpyDeviceToHost, ctx->stream));
+  CK(cudaStreamSynchronize(ctx->stream));
+  const size_t total_ids = (size_t)out_ptr[n_jobs];
+  if ((rc = ensure(ctx->d_out_ids, (total_ids + 1) * 4))) return rc;
+  if (total_ids * 4 > ctx->h_out_cap) {
+    if (ctx->h_out_ids) CK(cudaFreeHost(ctx->h_out_ids));
+    ctx->h_out_ids = nullptr;
+    ctx->h_out_cap = 0;
+    const size_t want = total_ids * 4 + total_ids + 4096;
+    CK(cudaHostAlloc(&ctx->h_out_ids, want, cudaHostAllocDefault));
+    ctx->h_out_cap = want;
+  }
+  if (total_ids) {
+    k_fill_indices<<<(n_jobs + 7) / 8, 256, 0, ctx->stream>>>(bits, n_jobs, words, map,
+                                                              (const unsigned long long*)ctx->d_ptr64.p,
+                                                              (uint32_t*)ctx->d_out_ids.p);
+    CK(cudaGetLastError());
+    ctx->launches++;
+    CK(cudaMemcpyAsync(ctx->h_out_ids, ctx->d_out_ids.p, total_ids * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+  }
+  *out_ids = (const uint32_t*)ctx->h_out_ids;
   return 0;
 }
 

@@ -787,7 +787,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 // all 8 warps; the rest is done by the first of them).
 // ------------------------------------------------------------------------------------------
 
-template <int WPJ>
+template <int WPJ, bool ROW32, bool HAS_LUT>
 __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
   constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -857,34 +857,25 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   const uint32_t n_act = min(p.n_used, p.group_nact[group]);  // the columns k_match gathered for this group
   auto eval_row = [&](const uint32_t row, const uint32_t cut) -> uint32_t {
     // the row's codes come with one (16-byte rows) or two 128-bit loads, then the table words of
-    // all columns are fetched side by side: two dependent round trips per candidate.  A rolled
-    // loop on purpose: this body is inlined at every flush site and k_extract is bound by
-    // instruction fetch and load latency, not by instruction count
-    const uint4* rp = p.rows + (size_t)row * (p.n_cols >> 3);
+    // the group's n_act columns are fetched side by side: two dependent round trips per
+    // candidate.  n_act is the same for the whole warp, so the unrolled column loop leaves at
+    // the first column the group does not need
+    const uint4* rp = p.rows + (size_t)row * (ROW32 ? 2u : 1u);
     const uint4 v0 = __ldg(rp);
-    uint32_t w[8] = {v0.x, v0.y, v0.z, v0.w, 0, 0, 0, 0};
-    if (n_act > 8u) {
+    uint32_t w[ROW32 ? 8 : 4] = {v0.x, v0.y, v0.z, v0.w};
+    if constexpr (ROW32) {
       const uint4 v1 = __ldg(rp + 1);
       w[4] = v1.x; w[5] = v1.y; w[6] = v1.z; w[7] = v1.w;
     }
     uint32_t ok = row < cut ? 1u : 0u;
 #pragma unroll
-    for (uint32_t c = 0; c < 8u; ++c) {
-      if (c < n_act) {
-        uint32_t code = (c & 1u) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
+    for (uint32_t c = 0; c < (ROW32 ? 16u : 8u); ++c) {
+      if (c >= n_act) break;
+      uint32_t code = (c & 1u) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
+      if constexpr (HAS_LUT) {
         if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-        ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
       }
-    }
-    if (n_act > 8u) {  // 32-byte rows (pool tables)
-#pragma unroll
-      for (uint32_t c = 8u; c < 16u; ++c) {
-        if (c < n_act) {
-          uint32_t code = (c & 1u) ? (w[c >> 1] >> 16) : (w[c >> 1] & 0xFFFFu);
-          if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
-          ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
-        }
-      }
+      ok &= __ldg(tab + (size_t)(p.base[c] + code) * 4u) >> bit;
     }
     return ok & 1u;
   };
@@ -894,6 +885,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   auto candidate = [&](const uint32_t i, const uint32_t bs, const uint32_t R) -> uint32_t {
     const uint32_t nR = __popc(R);
     if (nR == 1u) return (bs + i) * 32u + (__ffs(R) - 1);  // the usual case of a sparse job
+    if (nR == 32u) return bs * 32u + i;                    // and of a dense one
     const uint32_t b = (i * (65535u / nR + 1u)) >> 16;  // i / nR, exact for i < 512
     uint32_t r = i - b * nR, m = R, l = 0;              // l = position of the r-th set bit of R
 #pragma unroll
@@ -942,8 +934,10 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
         ok[u] = 0;
         if (qi < q_total) {
           const uint32_t q = backward ? q_total - 1u - qi : qi;
-          uint32_t e = 0;
-          for (uint32_t i = 1; i < n_pend; ++i) e = q >= pend[i][3] ? i : e;  // starts ascend
+          uint32_t e = 0;  // the queued window that holds candidate q: starts ascend, at most 16 entries
+#pragma unroll
+          for (uint32_t s = EXTRACT_PENDING / 2; s >= 1u; s >>= 1)
+            if (e + s < n_pend && q >= pend[e + s][3]) e += s;
           row[u] = candidate(q - pend[e][3], pend[e][0], pend[e][1]);
           ok[u] = eval_row(row[u], pend[e][2]);
         }
@@ -1198,4 +1192,282 @@ __global__ void k_merge_shards_interleaved(uint32_t n_shards, uint32_t n_jobs, u
   cnt_out[job] = total;
   max_out[job] = best;
   maxprice_out[job] = (best == ~0ull) ? __longlong_as_double(0x7FF8000000000000LL) : best_price;
+}
+
+// ------------------------------------------------------------------------------------------
+// k_pack_jobs: raw jobs -> predicate records (one thread per job).  The translation
+// dstack_b200/encode.py:pack_jobs does with numpy, with the same double comparisons:
+// bound -> ordinal by binary search in the table's sorted value lists (searchsorted left for a
+// minimum, right for a maximum), max_price -> cut-off rows by binary search in the prices.
+// ------------------------------------------------------------------------------------------
+
+struct PackParams {
+  const dsm_raw_job* raw;
+  const int32_t* ids;
+  uint32_t n_jobs;
+  LayoutDev lay;
+  uint32_t role[DSM_MAX_COLS];
+  const double* dict[DSM_N_PACK_DICTS];
+  uint32_t dict_n[DSM_N_PACK_DICTS];
+  const double* price;  // physical rows: [0, n_live_a) and [split_row, split_row + n_live_b) ascending
+  uint32_t n_live_a, split_row, n_live_b;
+  uint32_t* recs;
+  uint32_t* keys;  // per job: 1 + index of the last column that rejects anything (for the evaluation order)
+};
+
+__device__ __forceinline__ uint32_t lower_bound_f64(const double* v, uint32_t n, double x) {  // first i: v[i] >= x
+  uint32_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (v[mid] < x) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+__device__ __forceinline__ uint32_t upper_bound_f64(const double* v, uint32_t n, double x) {  // first i: v[i] > x
+  uint32_t lo = 0, hi = n;
+  while (lo < hi) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (x < v[mid]) hi = mid; else lo = mid + 1;
+  }
+  return lo;
+}
+// inclusive ordinal range lo | hi<<16 of the values inside [b[0], b[1]] (NaN = open); empty -> (1, 0)
+__device__ __forceinline__ uint32_t range_word_f64(const double* v, uint32_t n, const double* b) {
+  const long long lo = isnan(b[0]) ? 0ll : (long long)lower_bound_f64(v, n, b[0]);
+  const long long hi = isnan(b[1]) ? (long long)n - 1ll : (long long)upper_bound_f64(v, n, b[1]) - 1ll;
+  if (lo > hi || n == 0) return 1u;
+  return (uint32_t)lo | ((uint32_t)hi << 16);
+}
+__device__ __forceinline__ bool range_word_trivial(uint32_t w, uint32_t n) {
+  return n == 0 || ((w & 0xFFFFu) == 0u && (w >> 16) >= n - 1u);
+}
+
+__global__ void __launch_bounds__(128) k_pack_jobs(const PackParams p) {
+  const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= p.n_jobs) return;
+  const dsm_raw_job& r = p.raw[j];
+  uint32_t* rec = p.recs + (size_t)j * p.lay.rec_words;
+  for (uint32_t w = 0; w < p.lay.rec_words; ++w) rec[w] = 0u;
+
+  // words 0, 1: cut-off rows
+  const bool no_mp = isnan(r.max_price);
+  uint32_t cut_a = p.n_live_a, cut_b = p.split_row + p.n_live_b;
+  if (!no_mp) {
+    cut_a = upper_bound_f64(p.price, p.n_live_a, r.max_price);
+    cut_b = p.split_row + upper_bound_f64(p.price + p.split_row, p.n_live_b, r.max_price);
+  }
+  if (r.flags & DSM_RAWF_EXCLUDE_NOT_AVAILABLE) cut_b = p.split_row;
+  rec[0] = cut_a;
+  rec[1] = cut_b;
+
+  const double* cpu_v = p.dict[DSM_DICT_CPU];
+  const uint32_t cpu_n = p.dict_n[DSM_DICT_CPU];
+  const uint32_t cpu_w = range_word_f64(cpu_v, cpu_n, r.cpu);
+  const uint32_t mem_w = range_word_f64(p.dict[DSM_DICT_MEMORY], p.dict_n[DSM_DICT_MEMORY], r.memory);
+  const bool cpu_triv = range_word_trivial(cpu_w, cpu_n) && r.blocks == 0;
+  const bool mem_triv = range_word_trivial(mem_w, p.dict_n[DSM_DICT_MEMORY]);
+  // cpu as a set: in range and (blocks > 1: divisible by blocks; blocks == 0: any; else nothing)
+  auto cpu_bitset = [&](uint32_t* out) {
+    for (uint32_t e = 0; e < cpu_n; ++e) {
+      bool ok = e >= (cpu_w & 0xFFFFu) && e <= (cpu_w >> 16);
+      if (r.blocks > 1) ok = ok && ((long long)cpu_v[e] % (long long)r.blocks == 0ll);
+      else ok = ok && r.blocks == 0;
+      if (ok) out[e >> 5] |= 1u << (e & 31u);
+    }
+  };
+  auto put_ids = [&](uint32_t* out, uint32_t off, uint32_t cnt) {
+    for (uint32_t i = 0; i < cnt; ++i) {
+      const int32_t id = p.ids[off + i];
+      if (id >= 0) out[(uint32_t)id >> 5] |= 1u << ((uint32_t)id & 31u);
+    }
+  };
+
+  uint32_t last_needed = 0;
+  for (uint32_t c = 0; c < p.lay.n_used; ++c) {
+    uint32_t* w = rec + p.lay.rec_off[c];
+    const uint32_t card = p.lay.card[c];
+    bool triv = false;
+    switch (p.role[c]) {
+      case DSM_ROLE_CPU:
+        if (p.lay.kind[c] == DSM_COL_BITSET) cpu_bitset(w); else w[0] = cpu_w;
+        triv = cpu_triv;
+        break;
+      case DSM_ROLE_MEMORY:
+        w[0] = mem_w;
+        triv = mem_triv;
+        break;
+      case DSM_ROLE_CPU_MEMORY:
+        if (p.lay.flags[c] & DSM_COLF_PAIR_A_BITSET) cpu_bitset(w); else w[0] = cpu_w;
+        w[p.lay.aux[c]] = mem_w;
+        triv = cpu_triv && mem_triv;
+        break;
+      case DSM_ROLE_DISK: {
+        const uint32_t n = p.dict_n[DSM_DICT_DISK];
+        w[0] = range_word_f64(p.dict[DSM_DICT_DISK], n, r.disk);
+        triv = range_word_trivial(w[0], n);
+        break;
+      }
+      case DSM_ROLE_GPU: {
+        const uint32_t n_cnt = p.dict_n[DSM_DICT_GPU_COUNT], n_tot = p.dict_n[DSM_DICT_GPU_TOTAL];
+        w[0] = range_word_f64(p.dict[DSM_DICT_GPU_COUNT], n_cnt, r.gpu_count);
+        w[1] = range_word_f64(p.dict[DSM_DICT_GPU_MEMORY], p.dict_n[DSM_DICT_GPU_MEMORY], r.gpu_memory);
+        w[2] = range_word_f64(p.dict[DSM_DICT_GPU_TOTAL], n_tot, r.gpu_total);
+        uint32_t gflags = 0;
+        if (!(isnan(r.gpu_memory[0]) && isnan(r.gpu_memory[1]))) gflags |= DSM_GPUF_MEM_BOUNDED;
+        if (r.cc_min >= 0) gflags |= DSM_GPUF_CC_BOUNDED;
+        if (r.flags & DSM_RAWF_GPU_NAME_ANY) gflags |= DSM_GPUF_NAME_ANY;
+        const uint32_t cc_ord = lower_bound_f64(p.dict[DSM_DICT_CC], p.dict_n[DSM_DICT_CC], (double)max(r.cc_min, 0));
+        w[3] = min(cc_ord, 0xFFFEu) | (gflags << 16);
+        const uint32_t vmask = r.gpu_vendor == 0 ? 0xFFu : (1u << r.gpu_vendor);
+        w[4] = vmask | ((r.blocks > 1 ? (uint32_t)r.blocks : 0u) << 16);
+        put_ids(w + 5, r.gpu_name_off, r.gpu_name_cnt);
+        triv = range_word_trivial(w[0], n_cnt) && range_word_trivial(w[2], n_tot) &&
+               gflags == DSM_GPUF_NAME_ANY && r.gpu_vendor == 0 && r.blocks <= 1;
+        break;
+      }
+      case DSM_ROLE_BK: {
+        const uint32_t spot_mask = r.spot < 0 ? 3u : (r.spot == 0 ? 1u : 2u);
+        w[0] = r.src_backend_mask;
+        w[1] = r.off_backend_mask;
+        w[2] = spot_mask | ((uint32_t)r.status_mask << 8);
+        w[3] = (uint32_t)r.flag_req | ((uint32_t)r.flag_forbid << 16);
+        triv = r.src_backend_mask == 0xFFFFFFFFu && r.off_backend_mask == 0xFFFFFFFFu && spot_mask == 3u &&
+               r.status_mask == 0xFFu && r.flag_req == 0 && r.flag_forbid == 0;
+        break;
+      }
+      case DSM_ROLE_REGION:
+      case DSM_ROLE_ITYPE:
+      case DSM_ROLE_FLEET:
+      case DSM_ROLE_NAME:
+      case DSM_ROLE_ZONE: {
+        const uint32_t role = p.role[c];
+        const uint32_t any_bit = role == DSM_ROLE_REGION ? DSM_RAWF_REGION_ANY
+                               : role == DSM_ROLE_ITYPE ? DSM_RAWF_ITYPE_ANY
+                               : role == DSM_ROLE_FLEET ? DSM_RAWF_FLEET_ANY
+                               : role == DSM_ROLE_NAME  ? DSM_RAWF_NAME_ANY : DSM_RAWF_ZONE_ANY;
+        const uint32_t nw = (card + 31u) / 32u;
+        triv = (r.flags & any_bit) != 0;
+        if (triv) {
+          for (uint32_t i = 0; i < nw; ++i) w[i] = 0xFFFFFFFFu;
+        } else {
+          if (role == DSM_ROLE_REGION) put_ids(w, r.region_off, r.region_cnt);
+          else if (role == DSM_ROLE_ITYPE) put_ids(w, r.itype_off, r.itype_cnt);
+          else if (role == DSM_ROLE_ZONE) put_ids(w, r.zone_off, r.zone_cnt);
+          else {
+            const int32_t id = role == DSM_ROLE_FLEET ? r.fleet_id : r.name_id;
+            if (id >= 0) w[(uint32_t)id >> 5] |= 1u << ((uint32_t)id & 31u);
+          }
+          // the entry of rows whose value is unknown (last) passes an instance-type / zone filter
+          if (role == DSM_ROLE_ITYPE || role == DSM_ROLE_ZONE) w[(card - 1u) >> 5] |= 1u << ((card - 1u) & 31u);
+        }
+        break;
+      }
+      default:
+        break;
+    }
+    if (!triv) last_needed = c + 1u;
+  }
+  if (p.keys) p.keys[j] = last_needed;
+}
+
+// Evaluation order: jobs grouped by key (counting sort, keys <= DSM_MAX_COLS; the order inside a
+// key is whatever the atomics give -- results do not depend on it).  One CTA.
+__global__ void __launch_bounds__(1024) k_order_jobs(const uint32_t* keys, uint32_t n_jobs, uint32_t* order) {
+  __shared__ uint32_t hist[DSM_MAX_COLS + 2];
+  if (threadIdx.x < DSM_MAX_COLS + 2) hist[threadIdx.x] = 0u;
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < n_jobs; j += blockDim.x) atomicAdd(&hist[min(keys[j], (uint32_t)DSM_MAX_COLS) + 1u], 1u);
+  __syncthreads();
+  if (threadIdx.x == 0)
+    for (uint32_t i = 1; i < DSM_MAX_COLS + 2; ++i) hist[i] += hist[i - 1];  // hist[k] = first slot of key k
+  __syncthreads();
+  for (uint32_t j = threadIdx.x; j < n_jobs; j += blockDim.x)
+    order[atomicAdd(&hist[min(keys[j], (uint32_t)DSM_MAX_COLS)], 1u)] = j;
+}
+
+// ------------------------------------------------------------------------------------------
+// match bitmaps -> per-job index lists
+// ------------------------------------------------------------------------------------------
+
+// bits [n_jobs][n_words] over physical rows -> sbits [n_jobs][s_words] over source positions
+__global__ void k_scatter_to_source(const uint32_t* bits, uint32_t n_jobs, uint32_t n_words, const int32_t* row_to_source,
+                                    uint32_t* sbits, uint32_t s_words) {
+  const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (size_t)n_jobs * n_words) return;
+  uint32_t m = bits[i];
+  const uint32_t job = (uint32_t)(i / n_words), word = (uint32_t)(i % n_words);
+  while (m) {
+    const uint32_t b = __ffs(m) - 1;
+    m &= m - 1;
+    const int32_t s = row_to_source[word * 32u + b];
+    if (s >= 0) atomicOr(&sbits[(size_t)job * s_words + ((uint32_t)s >> 5)], 1u << ((uint32_t)s & 31u));
+  }
+}
+
+// one warp per job: matches of the job
+__global__ void __launch_bounds__(256) k_count_bits(const uint32_t* bits, uint32_t n_jobs, uint32_t n_words,
+                                                    unsigned long long* cnt) {
+  const uint32_t job = blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+  if (job >= n_jobs) return;
+  const uint32_t* b = bits + (size_t)job * n_words;
+  uint32_t c = 0;
+  for (uint32_t w = lane; w < n_words; w += 32u) c += __popc(b[w]);
+  c = __reduce_add_sync(0xFFFFFFFFu, c);
+  if (lane == 0) cnt[job] = c;
+}
+
+// exclusive prefix of cnt[n] into ptr[n + 1]; one CTA
+__global__ void __launch_bounds__(1024) k_prefix_u64(const unsigned long long* cnt, uint32_t n, unsigned long long* ptr) {
+  __shared__ unsigned long long part[1024];
+  const uint32_t per = (n + blockDim.x - 1) / blockDim.x;
+  const uint32_t lo = min(n, threadIdx.x * per), hi = min(n, lo + per);
+  unsigned long long s = 0;
+  for (uint32_t i = lo; i < hi; ++i) s += cnt[i];
+  part[threadIdx.x] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    unsigned long long run = 0;
+    for (uint32_t t = 0; t < blockDim.x; ++t) { const unsigned long long v = part[t]; part[t] = run; run += v; }
+    ptr[n] = run;
+  }
+  __syncthreads();
+  unsigned long long run = part[threadIdx.x];
+  for (uint32_t i = lo; i < hi; ++i) { ptr[i] = run; run += cnt[i]; }
+}
+
+// one warp per job: the set bits of its bitmap in ascending order; value = the bit's index, or
+// (map != nullptr) map[index]
+__global__ void __launch_bounds__(256) k_fill_indices(const uint32_t* bits, uint32_t n_jobs, uint32_t n_words,
+                                                      const int32_t* map, const unsigned long long* ptr, uint32_t* out) {
+  const uint32_t job = blockIdx.x * 8u + (threadIdx.x >> 5), lane = threadIdx.x & 31u;
+  if (job >= n_jobs) return;
+  const uint32_t* b = bits + (size_t)job * n_words;
+  unsigned long long at = ptr[job];
+  for (uint32_t w0 = 0; w0 < n_words; w0 += 32u) {
+    const uint32_t w = w0 + lane;
+    uint32_t m = w < n_words ? b[w] : 0u;
+    const uint32_t c = __popc(m);
+    uint32_t incl = c;  // inclusive scan of the lanes' popcounts
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t y = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+      if (lane >= (uint32_t)d) incl += y;
+    }
+    unsigned long long o = at + (incl - c);
+    while (m) {
+      const uint32_t bit = __ffs(m) - 1;
+      m &= m - 1;
+      const uint32_t idx = w * 32u + bit;
+      out[o++] = map ? (uint32_t)map[idx] : idx;
+    }
+    at += __shfl_sync(0xFFFFFFFFu, incl, 31);
+  }
+}
+
+// rows [n] (DSM_NO_ROW = none) -> source positions (-1 = none)
+__global__ void k_rows_to_source(const uint32_t* rows, uint32_t n, const int32_t* row_to_source, int32_t* out) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint32_t r = rows[i];
+  out[i] = r == DSM_NO_ROW ? -1 : row_to_source[r];
 }

@@ -27,6 +27,8 @@ import numpy as np
 
 from ._gpuhunt import AcceleratorVendor, compute_capability_of
 from .models import BackendType, InstanceStatus
+from .native import (RAW_JOB, RAWF_EXCLUDE_NOT_AVAILABLE, RAWF_FLEET_ANY, RAWF_GPU_NAME_ANY, RAWF_ITYPE_ANY,
+                     RAWF_NAME_ANY, RAWF_REGION_ANY, RAWF_ZONE_ANY, ROLES)
 
 # codes -------------------------------------------------------------------------------------
 
@@ -455,7 +457,9 @@ def _range_trivial(words: np.ndarray, n_values: int) -> np.ndarray:
     return ((words & 0xFFFF) == 0) & ((words >> 16) >= n_values - 1)
 
 
-def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
+def pack_jobs(t: EncodedTable, jc: JobColumns, n_used: Optional[int] = None) -> PackedJobs:
+    """``n_used``: keep exactly that many leading columns (at least the ones some job filters on);
+    default: up to the last column any job filters on."""
     j = jc.n
     luts: Dict[int, np.ndarray] = {}
     # per table column: (record words [J, w], kind, card, flags, aux, jobs that accept every entry)
@@ -593,7 +597,11 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     last_needed = np.zeros(j, dtype=np.int64)  # per job: 1 + index of the last column that rejects anything
     for ci, name in enumerate(names):
         last_needed = np.where(preds[name][5], last_needed, ci + 1)
-    n_used = max(1, int(last_needed.max()) if j else 1)
+    needed = max(1, int(last_needed.max()) if j else 1)
+    if n_used is None:
+        n_used = needed
+    elif not needed <= n_used <= len(names):
+        raise ValueError(f"n_used={n_used}: the batch filters on {needed} columns, the table has {len(names)}")
     for ci in list(luts):
         if ci >= n_used:
             luts.pop(ci)
@@ -616,5 +624,147 @@ def pack_jobs(t: EncodedTable, jc: JobColumns) -> PackedJobs:
     if j > 128 and (last_needed != last_needed[0]).any():
         order = np.argsort(last_needed, kind="stable").astype(np.uint32)
     layout = dict(n_used=len(kinds), kind=kinds, card=cards, flags=cflags, aux=aux, rec_off=offs,
-                  rec_words=rec_words)
+                  rec_words=rec_words, role=[ROLES[n] for n in names[:n_used]])
     return PackedJobs(records=rec, layout=layout, luts=luts, order=order)
+
+
+# raw jobs: the same translation on the device ------------------------------------------------
+
+
+def _column_shapes(t: EncodedTable, cpu_as_set: bool):
+    """Per table column: (kind, card, flags, aux, record words) of its predicate."""
+    out = []
+    n_cpu_words = (len(t.cpu_values) + 31) // 32
+    for col in t.columns:
+        if col.name == "cpu_memory":
+            aux = n_cpu_words if cpu_as_set else 1
+            out.append((KIND_PAIR, col.card, COLF_PAIR_A_BITSET if cpu_as_set else 0, aux, aux + 1))
+        elif col.name == "cpu":
+            out.append((KIND_BITSET, col.card, 0, 0, n_cpu_words) if cpu_as_set else (KIND_RANGE, col.card, 0, 0, 1))
+        elif col.name == "memory":
+            out.append((KIND_RANGE, col.card, 0, 0, 1))
+        elif col.name == "disk":
+            out.append((KIND_RANGE, col.card, COLF_NULL_PASSES, 0, 1))
+        elif col.name == "gpu":
+            nwn = (max(1, len(t.gpu_dict["names"])) + 31) // 32
+            out.append((KIND_GPU, col.card, 0, nwn, 5 + nwn))
+        elif col.name == "bk":
+            out.append((KIND_BK, col.card, 0, 0, 4))
+        else:
+            out.append((KIND_BITSET, col.card, 0, 0, (col.card + 31) // 32))
+    return out
+
+
+def raw_layout(t: EncodedTable, jc: JobColumns):
+    """The record layout of a batch whose records the device builds (``dsm_match_topk_raw`` /
+    ``dsm_match_topk_cols``), or ``None`` when the batch filters on a column that needs a per-call
+    remap (more than ``LUT_THRESHOLD`` dictionary entries: instance types or instance names) --
+    those batches are packed on the host.  Trailing set columns no job filters on are left out;
+    whether the remaining columns reject anything is found out on the device, per job group."""
+    j = jc.n
+    any_of = {"region": jc.region_any, "itype": jc.itype_any, "fleet": jc.fleet_any, "name": jc.name_any,
+              "zone": jc.zone_any}
+    names = [c.name for c in t.columns]
+    n_used = len(names)
+    while n_used > 1 and names[n_used - 1] in any_of and \
+            (any_of[names[n_used - 1]] is None or bool(np.asarray(any_of[names[n_used - 1]]).all())):
+        n_used -= 1
+    if any(c.card > LUT_THRESHOLD for c in t.columns[:n_used]):
+        return None
+    cpu_as_set = False
+    if jc.blocks is not None:
+        blocks = np.asarray(jc.blocks)
+        cpu_as_set = bool((blocks != 0).any())
+        if (blocks > 0xFFFF).any():
+            raise ValueError("block counts above 65535 are not supported")
+        if (blocks > 1).any() and len(t.gpu_entries) and int((t.gpu_entries[:, 2] >> 25).max()) >= 127:
+            raise ValueError("an instance with more than 126 GPUs cannot be matched against an explicit block count")
+    shapes = _column_shapes(t, cpu_as_set)[:n_used]
+    offs, pos = [], 2
+    for s in shapes:
+        offs.append(pos)
+        pos += s[4]
+    return dict(n_used=n_used, kind=[s[0] for s in shapes], card=[s[1] for s in shapes],
+                flags=[s[2] for s in shapes], aux=[s[3] for s in shapes], rec_off=offs,
+                rec_words=(pos + 3) // 4 * 4, role=[ROLES[n] for n in names[:n_used]])
+
+
+def raw_jobs(t: EncodedTable, jc: JobColumns):
+    """Job filters as ``dsm_raw_job`` records for ``dsm_match_topk_raw`` (the device does what
+    :func:`pack_jobs` does: bounds -> ordinals, max_price -> cut-off rows, sets -> bitsets, and the
+    evaluation order).  Returns ``(raw, ids, layout)`` or ``None`` (see :func:`raw_layout`).  The
+    product path hands the columns to ``dsm_match_topk_cols`` instead, which lays these records out
+    in C; this function is the same layout in numpy (tests, callers of the raw entry point)."""
+    layout = raw_layout(t, jc)
+    if layout is None:
+        return None
+    j = jc.n
+    ones = np.ones(j, bool)
+    any_of = {"region": np.asarray(jc.region_any, bool), "itype": np.asarray(jc.itype_any, bool),
+              "fleet": ones if jc.fleet_any is None else np.asarray(jc.fleet_any, bool),
+              "name": ones if jc.name_any is None else np.asarray(jc.name_any, bool),
+              "zone": ones if jc.zone_any is None else np.asarray(jc.zone_any, bool)}
+    blocks = np.zeros(j, dtype=np.int64) if jc.blocks is None else np.asarray(jc.blocks, dtype=np.int64)
+
+    # dsm_raw_job is 13 doubles followed by 16 32-bit words; both blocks are filled column-wise in
+    # contiguous scratch arrays and transposed into the records in two copies (assigning the
+    # fields of a structured array one by one costs 4x as much for a few thousand jobs)
+    f = np.empty((13, j), dtype=np.float64)
+    f[0] = jc.max_price
+    for i, name in enumerate(("cpu", "memory", "disk", "gpu_count", "gpu_memory", "gpu_total")):
+        f[1 + 2 * i:3 + 2 * i] = getattr(jc, name).T
+    u = np.empty((16, j), dtype=np.uint32)
+    i32 = u.view(np.int32)
+    i32[0] = jc.cc_min
+    i32[1] = blocks
+    u[2] = jc.src_backend_mask
+    u[3] = jc.off_backend_mask
+    if jc.flag_req is None and jc.flag_forbid is None:
+        u[4] = 0
+    else:
+        req = 0 if jc.flag_req is None else np.asarray(jc.flag_req, dtype=np.uint32)
+        forbid = 0 if jc.flag_forbid is None else np.asarray(jc.flag_forbid, dtype=np.uint32)
+        u[4] = req | (forbid << np.uint32(16))
+    # byte 0 status mask, 1 spot, 2 vendor, 3 flags
+    b4 = u[5].view(np.uint8).reshape(j, 4)
+    b4[:, 0] = 0xFF if jc.status_mask is None else jc.status_mask
+    b4[:, 1] = np.asarray(jc.spot).view(np.uint8) if np.asarray(jc.spot).dtype == np.int8 else np.asarray(jc.spot, np.int8).view(np.uint8)
+    b4[:, 2] = jc.gpu_vendor
+    fl = np.asarray(jc.exclude_not_available, bool).view(np.uint8) * np.uint8(RAWF_EXCLUDE_NOT_AVAILABLE)
+    fl = fl | np.asarray(jc.gpu_name_any, bool).view(np.uint8) * np.uint8(RAWF_GPU_NAME_ANY)
+    for name, bit in (("region", RAWF_REGION_ANY), ("itype", RAWF_ITYPE_ANY), ("fleet", RAWF_FLEET_ANY),
+                      ("name", RAWF_NAME_ANY), ("zone", RAWF_ZONE_ANY)):
+        a = any_of[name]
+        fl = fl | (np.uint8(bit) if a is ones else a.view(np.uint8) * np.uint8(bit))
+    b4[:, 3] = fl
+    i32[6] = -1 if jc.fleet_ids is None else jc.fleet_ids
+    i32[7] = -1 if jc.name_ids is None else jc.name_ids
+    parts, base = [], 0
+    zptr = None if jc.zone_ptr is None else np.asarray(jc.zone_ptr)
+    for i, (ptr, ids) in enumerate(((jc.gpu_name_ptr, jc.gpu_name_ids), (jc.region_ptr, jc.region_ids),
+                                    (jc.itype_ptr, jc.itype_ids), (zptr, jc.zone_ids))):
+        if ptr is None or len(ids) == 0:
+            u[8 + 2 * i] = base
+            u[9 + 2 * i] = 0
+            continue
+        u[8 + 2 * i] = ptr[:-1]
+        if base:
+            u[8 + 2 * i] += np.uint32(base)
+        u[9 + 2 * i] = ptr[1:] - ptr[:-1]
+        parts.append(ids)
+        base += len(ids)
+    words = np.empty((j, RAW_JOB.itemsize // 4), dtype=np.uint32)
+    words[:, :26].view(np.float64)[:] = f.T  # 8-byte aligned: rows are 168 bytes
+    words[:, 26:] = u.T
+    raw = words.view(RAW_JOB).reshape(j)
+    ids_all = np.concatenate(parts).astype(np.int32) if base else np.zeros(0, np.int32)
+    return raw, ids_all, layout
+
+
+def pack_dicts(t: EncodedTable) -> Tuple[np.ndarray, List[int]]:
+    """The table's sorted value lists in ``dsm_pack_dict`` order, for ``dsm_table_set_pack_dicts``."""
+    gd = t.gpu_dict
+    lists = [t.cpu_values, t.memory_values, t.columns[t.col("disk")].values, gd["count"], gd["memory"], gd["total"],
+             gd["cc"]]
+    lists = [np.asarray(x, dtype=np.float64) for x in lists]
+    return (np.concatenate(lists) if sum(len(x) for x in lists) else np.zeros(0)), [len(x) for x in lists]

@@ -15,7 +15,8 @@ from typing import Any, Dict, List, Optional, Sequence, Tuple
 import numpy as np
 
 from . import native
-from .encode import EncodedTable, JobColumns, PackedJobs, encode_table, pack_jobs, OfferColumns
+from .encode import (EncodedTable, JobColumns, OfferColumns, PackedJobs, encode_table, pack_dicts, pack_jobs,
+                     raw_jobs, raw_layout)
 
 NO_ROW = native.NO_ROW
 
@@ -106,6 +107,38 @@ class Matcher:
                                                   native.ptr(out[0]), native.ptr(out[1]), native.ptr(out[2])))
         return out
 
+    def topk_rows_raw(self, dt: "DeviceTable", raw, k: int):
+        """``topk_rows`` from raw jobs (``encode.raw_jobs``): records and evaluation order are built
+        on the device (``dsm_match_topk_raw``)."""
+        jobs, ids, layout = raw
+        j = len(jobs)
+        out = (np.empty((j, k), np.uint32), np.empty(j, np.uint32), np.empty(j, np.uint32))
+        lay = native.make_layout(layout)
+        native.check(self._lib.dsm_match_topk_raw(self.handle, dt.handle, C.byref(lay), native.ptr(jobs), j,
+                                                  native.ptr(ids), len(ids), k,
+                                                  native.ptr(out[0]), native.ptr(out[1]), native.ptr(out[2])))
+        return out
+
+    def match_lists(self, dt: "DeviceTable", packed: PackedJobs, by_source: bool) -> List[np.ndarray]:
+        """Per job the source positions of every match, ascending (``by_source``) or in table
+        order; the bitmaps are turned into lists on the device (``dsm_match_indices``)."""
+        j = len(packed.records)
+        rec = np.ascontiguousarray(packed.records, dtype=np.uint32)
+        order = None if packed.order is None else np.ascontiguousarray(packed.order, dtype=np.uint32)
+        ptr = np.empty(j + 1, np.uint64)
+        out = C.c_void_p()
+        with self._call_lock:
+            lay = self._layout(packed, native.ptr(order))
+            native.check(self._lib.dsm_match_indices(self.handle, dt.handle, C.byref(lay), native.ptr(rec), j,
+                                                     1 if by_source else 0, native.ptr(ptr), C.byref(out)))
+            total = int(ptr[j])
+            if total:
+                buf = (C.c_uint32 * total).from_address(out.value)
+                ids = np.frombuffer(buf, dtype=np.uint32).astype(np.int64)  # copy: the buffer is the context's
+            else:
+                ids = np.zeros(0, np.int64)
+        return np.split(ids, ptr[1:-1].astype(np.int64))
+
     def bitmap_rows(self, dt: "DeviceTable", packed: PackedJobs) -> np.ndarray:
         j = len(packed.records)
         rec = np.ascontiguousarray(packed.records, dtype=np.uint32)
@@ -122,6 +155,16 @@ class Matcher:
         t = dt.table
         if t.n_src == 0:
             return TopK(np.full((jobs.n, k), -1, np.int64), np.zeros(jobs.n, np.int64), np.full(jobs.n, np.nan))
+        layout = raw_layout(t, jobs)
+        if layout is not None:  # records, evaluation order and the answer in source terms: all in the library
+            src, cnt, price = np.empty((jobs.n, k), np.int32), np.empty(jobs.n, np.uint32), np.empty(jobs.n, np.float64)
+            lay = native.make_layout(layout)
+            cols, keep = native.job_columns_c(jobs)
+            native.check(self._lib.dsm_match_topk_cols(self.handle, dt.handle, C.byref(lay), C.byref(cols), jobs.n, k,
+                                                       native.ptr(src), native.ptr(cnt), native.ptr(price)))
+            del keep
+            return TopK(src.astype(np.int64), cnt.astype(np.int64), price)
+        # a column needs a per-call remap: packed here
         idx, cnt, mx = self.topk_rows(dt, pack_jobs(t, jobs), k)
         src = np.where(idx == NO_ROW, -1, t.perm[np.minimum(idx, t.n_rows - 1)])
         price = np.where(mx == NO_ROW, np.nan, t.price[np.minimum(mx, t.n_rows - 1)])
@@ -133,13 +176,7 @@ class Matcher:
         t = dt.table
         if t.n_src == 0:
             return [np.zeros(0, np.int64) for _ in range(jobs.n)]
-        bits = self.bitmap_rows(dt, pack_jobs(t, jobs))
-        out = []
-        for j in range(jobs.n):
-            rows = np.flatnonzero(np.unpackbits(bits[j].view(np.uint8), bitorder="little"))
-            src = t.perm[rows]
-            out.append(np.sort(src) if order == "source" else src)
-        return out
+        return self.match_lists(dt, pack_jobs(t, jobs), by_source=(order == "source"))
 
 
 class DeviceTable:
@@ -160,6 +197,13 @@ class DeviceTable:
         native.check(self._lib.dsm_table_create(matcher.handle, C.byref(desc), native.ptr(rows), native.ptr(price),
                                                 native.ptr(ge), native.ptr(be), native.ptr(pe), C.byref(h)))
         self._h = h
+        # what the device needs to build job records itself and to answer in source positions
+        values, counts = pack_dicts(table)
+        values = np.ascontiguousarray(values, dtype=np.float64)
+        native.check(self._lib.dsm_table_set_pack_dicts(matcher.handle, h, native.ptr(values),
+                                                        C.byref((C.c_uint32 * native.N_PACK_DICTS)(*counts))))
+        to_source = np.ascontiguousarray(table.perm, dtype=np.int32)
+        native.check(self._lib.dsm_table_set_source_map(matcher.handle, h, native.ptr(to_source), max(1, table.n_src)))
 
     @property
     def handle(self) -> C.c_void_p:

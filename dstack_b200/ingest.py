@@ -254,116 +254,117 @@ def _pair(lo, hi) -> Tuple[float, float]:
 
 
 def job_columns(table: EncodedTable, filters: Sequence[JobFilter]) -> JobColumns:
+    """Job filters -> columns.  One pass over the filter objects collecting plain Python values
+    (assigning numpy scalars one by one costs several times as much), arrays are built at the end."""
     j = len(filters)
     cols = {c.name: c for c in table.columns}
     names = table.gpu_dict["names"]
-
-    f64 = lambda: np.full((j, 2), np.nan)
-    cpu, mem, disk, gcnt, gmem, gtot = f64(), f64(), f64(), f64(), f64(), f64()
-    max_price = np.full(j, np.nan)
-    spot = np.full(j, -1, np.int8)
-    vendor = np.zeros(j, np.int8)
-    cc_min = np.full(j, -1, np.int64)
-    name_any = np.ones(j, bool)
-    src_mask = np.full(j, 0xFFFFFFFF, np.uint32)
-    off_mask = np.full(j, 0xFFFFFFFF, np.uint32)
-    excl = np.zeros(j, bool)
-    flag_req = np.zeros(j, np.uint16)
-    flag_forbid = np.zeros(j, np.uint16)
-    blocks = np.zeros(j, np.int64)
-    status_mask = np.full(j, 0xFF, np.uint8)
-    fleet_any = np.ones(j, bool)
-    fleet_ids = np.full(j, -1, np.int64)
-    inst_any = np.ones(j, bool)
-    inst_ids = np.full(j, -1, np.int64)
+    nan = math.nan
+    bounds: List[List[float]] = [[] for _ in range(12)]  # cpu lo/hi, memory, disk, gpu count, gpu memory, gpu total
+    max_price, spot, vendor, cc_min, name_any = [], [], [], [], []
+    src_mask, off_mask, excl, flag_req, flag_forbid, blocks, status_mask = [], [], [], [], [], [], []
+    fleet_any, fleet_ids, inst_any, inst_ids = [], [], [], []
+    dstack_bit = 1 << BACKEND_CODES["dstack"]
+    pool_forbid = FLAG_UNREACHABLE | FLAG_BLOCKS_UNKNOWN
 
     class Csr:
         def __init__(self, lookup: Dict[Any, int]):
-            self.lookup, self.any, self.ptr, self.ids = lookup, np.ones(j, bool), [0], []
+            self.lookup, self.any, self.ptr, self.ids = lookup, [], [0], []
 
-        def put(self, i: int, values: Optional[Sequence[Any]]) -> None:
+        def put(self, values: Optional[Sequence[Any]]) -> None:
+            self.any.append(values is None)
             if values is not None:
-                self.any[i] = False
-                self.ids.extend(self.lookup.get(v, -1) for v in values)
+                get = self.lookup.get
+                self.ids.extend(get(v, -1) for v in values)
             self.ptr.append(len(self.ids))
 
         def arrays(self):
-            return self.any, np.array(self.ptr, np.int64), np.array(self.ids, np.int64)
+            return np.array(self.any, bool), np.array(self.ptr, np.int64), np.array(self.ids, np.int64)
 
     gname = Csr(names)
     region = Csr(cols["region"].lookup)
     itype = Csr(cols["itype"].lookup)
     zone = Csr(cols["zone"].lookup) if table.is_pool else None
+    fleet_lookup = cols["fleet"].lookup if table.is_pool else {}
+    name_lookup = cols["name"].lookup if table.is_pool else {}
 
-    for i, f in enumerate(filters):
+    for f in filters:
         q = f.query
         if q.min_price is not None:
             raise ValueError("min_price is not part of the dstack path (offers.py:117 sets max_price only)")
         if q.max_compute_capability is not None:
             raise ValueError("max_compute_capability is never set by dstack (offers.py:143-144)")
-        if q.max_price is not None:
-            max_price[i] = q.max_price
-        if q.spot is not None:
-            spot[i] = 1 if q.spot else 0
-        cpu[i] = _pair(q.min_cpu, q.max_cpu)
-        mem[i] = _pair(q.min_memory, q.max_memory)
-        disk[i] = _pair(q.min_disk_size, q.max_disk_size)
-        gcnt[i] = _pair(q.min_gpu_count, q.max_gpu_count)
-        gmem[i] = _pair(q.min_gpu_memory, q.max_gpu_memory)
-        gtot[i] = _pair(q.min_total_gpu_memory, q.max_total_gpu_memory)
-        vendor[i] = vendor_code(q.gpu_vendor)
-        if q.min_compute_capability is not None:
-            cc_min[i] = int(q.min_compute_capability[0]) * 1000 + int(q.min_compute_capability[1])
-        if q.gpu_name is not None:
-            name_any[i] = False
-        gname.put(i, None if q.gpu_name is None else [n.lower() for n in q.gpu_name])
+        max_price.append(nan if q.max_price is None else q.max_price)
+        spot.append(-1 if q.spot is None else (1 if q.spot else 0))
+        for k, v in enumerate((q.min_cpu, q.max_cpu, q.min_memory, q.max_memory, q.min_disk_size, q.max_disk_size,
+                               q.min_gpu_count, q.max_gpu_count, q.min_gpu_memory, q.max_gpu_memory,
+                               q.min_total_gpu_memory, q.max_total_gpu_memory)):
+            bounds[k].append(nan if v is None else float(v))
+        vendor.append(vendor_code(q.gpu_vendor))
+        cc = q.min_compute_capability
+        cc_min.append(-1 if cc is None else int(cc[0]) * 1000 + int(cc[1]))
+        name_any.append(q.gpu_name is None)
+        gname.put(None if q.gpu_name is None else [n.lower() for n in q.gpu_name])
         if f.backend_types is not None:
             m = 0
             for b in f.backend_types:
                 m |= 1 << backend_code(b)
-            off_mask[i] = m
-            src_mask[i] = m | ((1 << BACKEND_CODES["dstack"]) if f.keep_dstack_backend else 0)
-        excl[i] = f.exclude_not_available
-        region.put(i, f.regions)
-        itype.put(i, f.instance_types)
-        if f.require_auto_divisible:
-            flag_req[i] |= FLAG_AUTO_DIVISIBLE
-        blocks[i] = f.blocks
+            off_mask.append(m)
+            src_mask.append(m | (dstack_bit if f.keep_dstack_backend else 0))
+        else:
+            off_mask.append(0xFFFFFFFF)
+            src_mask.append(0xFFFFFFFF)
+        excl.append(f.exclude_not_available)
+        region.put(f.regions)
+        itype.put(f.instance_types)
+        req = FLAG_AUTO_DIVISIBLE if f.require_auto_divisible else 0
+        forbid = 0
+        blocks.append(f.blocks)
+        st_mask, fl_any, fl_id, in_any, in_id = 0xFF, True, -1, True, -1
         if f.shared is not None:  # pool filter (pools.py:460,484-488)
-            flag_forbid[i] |= FLAG_UNREACHABLE | FLAG_BLOCKS_UNKNOWN
+            forbid |= pool_forbid
             if f.shared:
-                flag_req[i] |= FLAG_SHARED
+                req |= FLAG_SHARED
             else:
-                flag_forbid[i] |= FLAG_SHARED
+                forbid |= FLAG_SHARED
             if f.require_offer:
-                flag_forbid[i] |= FLAG_NO_OFFER
+                forbid |= FLAG_NO_OFFER
             if f.status is not None:
                 st = f.status
-                status_mask[i] = 1 << STATUS_CODES[st.value if hasattr(st, "value") else str(st)]
+                st_mask = 1 << STATUS_CODES[st.value if hasattr(st, "value") else str(st)]
             if not f.any_fleet:
-                fleet_any[i] = False
-                fleet_ids[i] = cols["fleet"].lookup.get(f.fleet_id, -1)
+                fl_any, fl_id = False, fleet_lookup.get(f.fleet_id, -1)
             if f.instance_name is not None:
-                inst_any[i] = False
-                inst_ids[i] = cols["name"].lookup.get(f.instance_name, -1)
-            zone.put(i, f.zones)
+                in_any, in_id = False, name_lookup.get(f.instance_name, -1)
+            zone.put(f.zones)
         elif zone is not None:
-            zone.put(i, None)
+            zone.put(None)
+        flag_req.append(req)
+        flag_forbid.append(forbid)
+        status_mask.append(st_mask)
+        fleet_any.append(fl_any)
+        fleet_ids.append(fl_id)
+        inst_any.append(in_any)
+        inst_ids.append(in_id)
 
+    pair = lambda k: np.array([bounds[2 * k], bounds[2 * k + 1]], dtype=np.float64).T.copy() if j else np.zeros((0, 2))
     gn_any, gn_ptr, gn_ids = gname.arrays()
     r_any, r_ptr, r_ids = region.arrays()
     t_any, t_ptr, t_ids = itype.arrays()
+    blocks_a = np.array(blocks, np.int64)
     jc = JobColumns(
-        n=j, max_price=max_price, spot=spot, cpu=cpu, memory=mem, disk=disk, gpu_count=gcnt, gpu_memory=gmem,
-        gpu_total=gtot, gpu_vendor=vendor, cc_min=cc_min, gpu_name_any=name_any, gpu_name_ptr=gn_ptr,
-        gpu_name_ids=gn_ids, src_backend_mask=src_mask, off_backend_mask=off_mask,
-        exclude_not_available=excl, region_any=r_any, region_ptr=r_ptr, region_ids=r_ids,
-        itype_any=t_any, itype_ptr=t_ptr, itype_ids=t_ids, flag_req=flag_req, flag_forbid=flag_forbid,
-        status_mask=status_mask, blocks=blocks if blocks.any() else None,
+        n=j, max_price=np.array(max_price, np.float64), spot=np.array(spot, np.int8), cpu=pair(0), memory=pair(1),
+        disk=pair(2), gpu_count=pair(3), gpu_memory=pair(4), gpu_total=pair(5), gpu_vendor=np.array(vendor, np.int8),
+        cc_min=np.array(cc_min, np.int64), gpu_name_any=np.array(name_any, bool), gpu_name_ptr=gn_ptr,
+        gpu_name_ids=gn_ids, src_backend_mask=np.array(src_mask, np.uint32), off_backend_mask=np.array(off_mask, np.uint32),
+        exclude_not_available=np.array(excl, bool), region_any=r_any, region_ptr=r_ptr, region_ids=r_ids,
+        itype_any=t_any, itype_ptr=t_ptr, itype_ids=t_ids, flag_req=np.array(flag_req, np.uint16),
+        flag_forbid=np.array(flag_forbid, np.uint16), status_mask=np.array(status_mask, np.uint8),
+        blocks=blocks_a if blocks_a.any() else None,
     )
     if table.is_pool:
         z_any, z_ptr, z_ids = zone.arrays()
-        jc.fleet_any, jc.fleet_ids = fleet_any, fleet_ids
-        jc.name_any, jc.name_ids = inst_any, inst_ids
+        jc.fleet_any, jc.fleet_ids = np.array(fleet_any, bool), np.array(fleet_ids, np.int64)
+        jc.name_any, jc.name_ids = np.array(inst_any, bool), np.array(inst_ids, np.int64)
         jc.zone_any, jc.zone_ptr, jc.zone_ids = z_any, z_ptr, z_ids
     return jc

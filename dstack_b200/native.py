@@ -25,8 +25,25 @@ EXPORTS = [
     "dsm_match_topk_dev", "dsm_match_bitmap_dev", "dsm_merge_shards_dev", "dsm_gather_price_dev",
     "dsm_sync", "dsm_host_alloc", "dsm_host_free", "dsm_launch_count", "dsm_plan_query",
     "dsm_timing_enable", "dsm_timing_read", "dsm_match_bitmap_static", "dsm_merge_shards_strided_dev",
-    "dsm_merge_shards_interleaved_dev", "dsm_timing_read_parts",
+    "dsm_merge_shards_interleaved_dev", "dsm_timing_read_parts", "dsm_table_set_pack_dicts",
+    "dsm_table_set_source_map", "dsm_match_topk_raw", "dsm_jobs_pack_dev", "dsm_match_indices",
+    "dsm_match_topk_raw_src", "dsm_match_topk_cols",
 ]
+N_PACK_DICTS = 7  # cpu, memory, disk, gpu count, gpu memory, gpu total, compute capability
+
+# dsm_raw_job (include/dsmatch.h): little-endian, 168 bytes
+RAW_JOB = np.dtype([
+    ("max_price", "<f8"), ("cpu", "<f8", 2), ("memory", "<f8", 2), ("disk", "<f8", 2), ("gpu_count", "<f8", 2),
+    ("gpu_memory", "<f8", 2), ("gpu_total", "<f8", 2), ("cc_min", "<i4"), ("blocks", "<i4"),
+    ("src_backend_mask", "<u4"), ("off_backend_mask", "<u4"), ("flag_req", "<u2"), ("flag_forbid", "<u2"),
+    ("status_mask", "u1"), ("spot", "i1"), ("gpu_vendor", "i1"), ("flags", "u1"), ("fleet_id", "<i4"),
+    ("name_id", "<i4"), ("gpu_name_off", "<u4"), ("gpu_name_cnt", "<u4"), ("region_off", "<u4"),
+    ("region_cnt", "<u4"), ("itype_off", "<u4"), ("itype_cnt", "<u4"), ("zone_off", "<u4"), ("zone_cnt", "<u4"),
+])
+RAWF_EXCLUDE_NOT_AVAILABLE, RAWF_GPU_NAME_ANY, RAWF_REGION_ANY, RAWF_ITYPE_ANY = 1, 2, 4, 8
+RAWF_FLEET_ANY, RAWF_NAME_ANY, RAWF_ZONE_ANY = 16, 32, 64
+ROLES = {"cpu": 1, "memory": 2, "cpu_memory": 3, "disk": 4, "gpu": 5, "bk": 6, "region": 7, "itype": 8,
+         "fleet": 9, "name": 10, "zone": 11}
 STATIC_SCRATCH_BYTES = 2 << 20  # DSM_STATIC_SCRATCH_BYTES
 
 
@@ -47,7 +64,40 @@ class Layout(C.Structure):
                 ("kind", C.c_uint32 * MAX_COLS), ("card", C.c_uint32 * MAX_COLS),
                 ("flags", C.c_uint32 * MAX_COLS), ("aux", C.c_uint32 * MAX_COLS),
                 ("rec_off", C.c_uint32 * MAX_COLS), ("rec_words", C.c_uint32),
-                ("lut", C.c_void_p * MAX_COLS), ("job_order", C.c_void_p)]
+                ("lut", C.c_void_p * MAX_COLS), ("job_order", C.c_void_p), ("role", C.c_uint32 * MAX_COLS)]
+
+
+class JobColumnsC(C.Structure):
+    """``dsm_job_columns``: one host pointer per attribute of a job batch."""
+
+    FIELDS = [("max_price", "f8"), ("cpu", "f8"), ("memory", "f8"), ("disk", "f8"), ("gpu_count", "f8"),
+              ("gpu_memory", "f8"), ("gpu_total", "f8"), ("cc_min", "i8"), ("blocks", "i8"),
+              ("src_backend_mask", "u4"), ("off_backend_mask", "u4"), ("flag_req", "u2"), ("flag_forbid", "u2"),
+              ("status_mask", "u1"), ("spot", "i1"), ("gpu_vendor", "i1"), ("exclude_not_available", "u1"),
+              ("gpu_name_any", "u1"), ("region_any", "u1"), ("itype_any", "u1"), ("fleet_any", "u1"),
+              ("name_any", "u1"), ("zone_any", "u1"), ("fleet_ids", "i8"), ("name_ids", "i8"),
+              ("gpu_name_ptr", "i8"), ("gpu_name_ids", "i8"), ("region_ptr", "i8"), ("region_ids", "i8"),
+              ("itype_ptr", "i8"), ("itype_ids", "i8"), ("zone_ptr", "i8"), ("zone_ids", "i8")]
+    _fields_ = [(name, C.c_void_p) for name, _ in FIELDS]
+
+
+def job_columns_c(jc: Any):
+    """A ``dsm_job_columns`` over the arrays of a ``JobColumns`` (converted only where the dtype
+    differs; bool arrays are passed as bytes).  Returns the struct and the arrays it points into,
+    which must stay alive for the call."""
+    st, keep = JobColumnsC(), []
+    for name, code in JobColumnsC.FIELDS:
+        v = getattr(jc, name, None)
+        if v is None:
+            continue
+        a = np.asarray(v)
+        if a.dtype == np.bool_ and code == "u1":
+            a = np.ascontiguousarray(a).view(np.uint8)
+        else:
+            a = np.ascontiguousarray(a, dtype=np.dtype(code))
+        keep.append(a)
+        setattr(st, name, a.ctypes.data if a.size else None)
+    return st, keep
 
 
 _lib: Optional[C.CDLL] = None
@@ -89,6 +139,13 @@ def lib() -> C.CDLL:
     L.dsm_timing_enable.argtypes = [vp, C.c_int]
     L.dsm_timing_read.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(u32)]
     L.dsm_timing_read_parts.argtypes = [vp, C.POINTER(C.c_double * 3), C.POINTER(u32)]
+    L.dsm_table_set_pack_dicts.argtypes = [vp, vp, vp, C.POINTER(u32 * N_PACK_DICTS)]
+    L.dsm_table_set_source_map.argtypes = [vp, vp, vp, u32]
+    L.dsm_match_topk_raw.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp, u32, u32, vp, vp, vp]
+    L.dsm_match_topk_raw_src.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp, u32, u32, vp, vp, vp]
+    L.dsm_match_topk_cols.argtypes = [vp, vp, C.POINTER(Layout), C.POINTER(JobColumnsC), u32, u32, vp, vp, vp]
+    L.dsm_jobs_pack_dev.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp, vp, vp]
+    L.dsm_match_indices.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, C.c_int, vp, C.POINTER(vp)]
     L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, u32, C.POINTER(u32 * 8)]
     for name in EXPORTS:
         fn = getattr(L, name)
@@ -115,7 +172,10 @@ def make_layout(d: Dict[str, Any], lut_ptrs: Optional[Dict[int, int]] = None,
     L.job_order = job_order
     L.n_used = d["n_used"]
     L.rec_words = d["rec_words"]
+    roles = d.get("role")
     for i in range(d["n_used"]):
+        if roles is not None:
+            L.role[i] = roles[i]
         L.kind[i] = d["kind"][i]
         L.card[i] = d["card"][i]
         L.flags[i] = d["flags"][i]

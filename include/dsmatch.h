@@ -136,7 +136,61 @@ typedef struct dsm_layout {
    * host memory for dsm_match_topk / dsm_match_bitmap, device memory for the *_dev and
    * *_static entry points. */
   const uint32_t* job_order;
+  /* which attribute of a raw job (dsm_raw_job) feeds the column: DSM_ROLE_*.  Only read by the
+   * entry points that build the records on the device (dsm_jobs_pack_dev, dsm_match_topk_raw). */
+  uint32_t role[DSM_MAX_COLS];
 } dsm_layout;
+
+/* ---- raw jobs: the record building of core/backends/base/offers.py:112-146 on the device ----
+ *
+ * A raw job carries a job's bounds as the reference states them (IEEE doubles, NaN = not set)
+ * and its set filters as ids of the table's dictionaries; the device turns them into the
+ * predicate records above with the same double comparisons the reference makes per offer --
+ * bound -> ordinal by binary search in the table's sorted value lists, max_price -> cut-off row by
+ * binary search in the table's prices.  Little-endian, 8-byte aligned, 168 bytes. */
+typedef struct dsm_raw_job {
+  double max_price;       /* NaN: none */
+  double cpu[2];          /* min, max */
+  double memory[2];       /* GiB */
+  double disk[2];         /* GiB */
+  double gpu_count[2];
+  double gpu_memory[2];   /* GiB */
+  double gpu_total[2];    /* GiB */
+  int32_t cc_min;         /* min compute capability as major*1000+minor, -1: none */
+  int32_t blocks;         /* 0: no block filter, b > 1: cpu and GPU count divisible by b, < 0: nothing is */
+  uint32_t src_backend_mask, off_backend_mask;
+  uint16_t flag_req, flag_forbid;
+  uint8_t status_mask;    /* bit per status code, 0xFF any */
+  int8_t spot;            /* -1 either, 0 on-demand, 1 spot */
+  int8_t gpu_vendor;      /* vendor code, 0 = no filter */
+  uint8_t flags;          /* DSM_RAWF_* */
+  int32_t fleet_id;       /* dictionary id, -1: a fleet the table does not know */
+  int32_t name_id;
+  uint32_t gpu_name_off, gpu_name_cnt;   /* ranges of the call's id array (dictionary ids, -1 = */
+  uint32_t region_off, region_cnt;       /* a value the table does not contain)                 */
+  uint32_t itype_off, itype_cnt;
+  uint32_t zone_off, zone_cnt;
+} dsm_raw_job;
+
+#define DSM_RAWF_EXCLUDE_NOT_AVAILABLE 1u
+#define DSM_RAWF_GPU_NAME_ANY 2u
+#define DSM_RAWF_REGION_ANY 4u
+#define DSM_RAWF_ITYPE_ANY 8u
+#define DSM_RAWF_FLEET_ANY 16u
+#define DSM_RAWF_NAME_ANY 32u
+#define DSM_RAWF_ZONE_ANY 64u
+
+enum dsm_col_role {
+  DSM_ROLE_NONE = 0, DSM_ROLE_CPU = 1, DSM_ROLE_MEMORY = 2, DSM_ROLE_CPU_MEMORY = 3, DSM_ROLE_DISK = 4,
+  DSM_ROLE_GPU = 5, DSM_ROLE_BK = 6, DSM_ROLE_REGION = 7, DSM_ROLE_ITYPE = 8, DSM_ROLE_FLEET = 9,
+  DSM_ROLE_NAME = 10, DSM_ROLE_ZONE = 11
+};
+
+/* sorted distinct values of the table's range attributes, in this order */
+enum dsm_pack_dict {
+  DSM_DICT_CPU = 0, DSM_DICT_MEMORY = 1, DSM_DICT_DISK = 2, DSM_DICT_GPU_COUNT = 3, DSM_DICT_GPU_MEMORY = 4,
+  DSM_DICT_GPU_TOTAL = 5, DSM_DICT_CC = 6, DSM_N_PACK_DICTS = 7
+};
 
 typedef struct dsm_ctx dsm_ctx;
 typedef struct dsm_table dsm_table;
@@ -185,6 +239,94 @@ int dsm_match_topk(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
  * (core/backends/base/offers.py:149-158) and filter_pool_instances (pools.py:409-503). */
 int dsm_match_bitmap(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
                      const uint32_t* jobs, uint32_t n_jobs, uint32_t* out_bits);
+
+/* Give a table the value lists raw jobs are translated with: `values` = the DSM_N_PACK_DICTS
+ * lists one after the other (host, f64, each ascending), counts[i] = entries of list i. */
+int dsm_table_set_pack_dicts(dsm_ctx* ctx, dsm_table* t, const double* values,
+                             const uint32_t counts[DSM_N_PACK_DICTS]);
+
+/* dsm_match_topk with the records built on the device: raw jobs and their id array (host) in,
+ * results (host) out.  layout.role[] names the attribute behind every column; a column whose
+ * kind is DSM_COL_BITSET and role DSM_ROLE_CPU (or a DSM_COL_PAIR with DSM_COLF_PAIR_A_BITSET)
+ * gets the "in range and divisible by blocks" set.  layout.job_order must be NULL: the
+ * evaluation order (jobs that need the same leading columns side by side) is chosen on the
+ * device.  Columns with a per-call remap (layout.lut) are not supported here -- pack those
+ * calls on the host.  Reference: requirements_to_query_filter, offers.py:112-146, once per job. */
+int dsm_match_topk_raw(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                       const dsm_raw_job* jobs, uint32_t n_jobs, const int32_t* ids, uint32_t n_ids,
+                       uint32_t k, uint32_t* out_idx, uint32_t* out_cnt, uint32_t* out_max);
+
+/* The same, answered in the caller's terms: out_src = SOURCE positions of the first k matches
+ * (-1 = none; needs dsm_table_set_source_map), out_cnt = number of matches, out_max_price = the
+ * highest price among them (NaN = none) -- offers[:k], len(offers) and max(offer.price) of
+ * server/services/runs.py:341-348 without a host-side pass over the rows. */
+int dsm_match_topk_raw_src(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                           const dsm_raw_job* jobs, uint32_t n_jobs, const int32_t* ids, uint32_t n_ids,
+                           uint32_t k, int32_t* out_src, uint32_t* out_cnt, double* out_max_price);
+
+/* Job filters as columns (one array per attribute, the layout of a batch of Requirements +
+ * profile filters before any encoding): what dsm_match_topk_cols takes.  Arrays are host memory,
+ * n_jobs long unless noted; a NULL pointer means "not set for any job" (any-flags: every job
+ * accepts everything; exclude_not_available, blocks, flag_req / flag_forbid: zero; status_mask:
+ * 0xFF; fleet_ids / name_ids: -1).  Set filters are CSR: *_ptr has n_jobs + 1 entries into *_ids
+ * (dictionary ids of the table, -1 = a value the table does not contain). */
+typedef struct dsm_job_columns {
+  const double* max_price;      /* NaN: none */
+  const double* cpu;            /* [n_jobs][2] min, max; NaN = not set */
+  const double* memory;
+  const double* disk;
+  const double* gpu_count;
+  const double* gpu_memory;
+  const double* gpu_total;
+  const int64_t* cc_min;        /* major*1000+minor, -1: none */
+  const int64_t* blocks;
+  const uint32_t* src_backend_mask;
+  const uint32_t* off_backend_mask;
+  const uint16_t* flag_req;
+  const uint16_t* flag_forbid;
+  const uint8_t* status_mask;
+  const int8_t* spot;
+  const int8_t* gpu_vendor;
+  const uint8_t* exclude_not_available; /* 0 / 1 */
+  const uint8_t* gpu_name_any;
+  const uint8_t* region_any;
+  const uint8_t* itype_any;
+  const uint8_t* fleet_any;
+  const uint8_t* name_any;
+  const uint8_t* zone_any;
+  const int64_t* fleet_ids;
+  const int64_t* name_ids;
+  const int64_t* gpu_name_ptr; const int64_t* gpu_name_ids;
+  const int64_t* region_ptr;   const int64_t* region_ids;
+  const int64_t* itype_ptr;    const int64_t* itype_ids;
+  const int64_t* zone_ptr;     const int64_t* zone_ids;
+} dsm_job_columns;
+
+/* dsm_match_topk_raw_src from job columns: the library lays the raw jobs out itself (into a
+ * pinned staging buffer of the context), so a Python host passes its arrays as they are. */
+int dsm_match_topk_cols(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                        const dsm_job_columns* cols, uint32_t n_jobs, uint32_t k, int32_t* out_src,
+                        uint32_t* out_cnt, double* out_max_price);
+
+/* The packing step alone, device buffers: d_jobs/d_ids -> d_records [n_jobs][rec_words] and, if
+ * d_order is not NULL, the evaluation order [n_jobs].  Asynchronous on the ctx stream. */
+int dsm_jobs_pack_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
+                      const dsm_raw_job* d_jobs, uint32_t n_jobs, const int32_t* d_ids,
+                      uint32_t* d_records, uint32_t* d_order);
+
+/* ---- every match as an index list (filter_pool_instances, match_requirements) ----------- */
+
+/* Give a table the source position of every physical row (host, i32 [n_rows], -1 = padding). */
+int dsm_table_set_source_map(dsm_ctx* ctx, dsm_table* t, const int32_t* row_to_source, uint32_t n_source);
+
+/* dsm_match_bitmap, with the bitmaps turned into per-job lists of SOURCE positions on the
+ * device: out_ptr[j]..out_ptr[j+1] delimits job j's matches inside *out_ids (n_jobs + 1 u64,
+ * host).  by_source != 0: ascending source position (the reference's "input order",
+ * pools.py:409-503, offers.py:149-158); 0: table order (price rank).  *out_ids points into a
+ * pinned buffer owned by the context, valid until its next call.  Needs
+ * dsm_table_set_source_map. */
+int dsm_match_indices(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, const uint32_t* jobs,
+                      uint32_t n_jobs, int by_source, uint64_t* out_ptr, const uint32_t** out_ids);
 
 /* ---- matching, device buffers (inputs already resident; asynchronous on the ctx stream) - */
 

@@ -31,5 +31,6 @@ def test_struct_sizes_match_header():
     import ctypes as C
 
     assert C.sizeof(native.TableDesc) == 8 * 4
-    # u32 n_used + 5 arrays of 16 u32 + u32 rec_words (+4 padding) + 16 + 1 pointers
-    assert C.sizeof(native.Layout) == 4 + 5 * 64 + 4 + 17 * 8
+    # u32 n_used + 5 arrays of 16 u32 + u32 rec_words (+4 padding) + 16 + 1 pointers + 16 u32 roles
+    assert C.sizeof(native.Layout) == 4 + 5 * 64 + 4 + 17 * 8 + 64
+    assert native.RAW_JOB.itemsize == 168  # dsm_raw_job

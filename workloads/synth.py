@@ -300,6 +300,40 @@ def make_jobs(cat: SynthCatalog, table, n_jobs: int, seed: int = 3) -> SynthJobs
     return SynthJobs(jc, gpu_names, backend_lists, region_lists)
 
 
+def widen_jobs(sj: SynthJobs, table, seed: int = 0) -> SynthJobs:
+    """Perturb a job batch in place so that every kind of bound occurs: maxima as well as minima,
+    bounds exactly equal to values of the table's dictionaries, bounds outside them, no bounds at
+    all, explicit block counts, ``exclude_not_available``.  For tests of the record packers."""
+    rng = np.random.Generator(np.random.PCG64(seed))
+    jc = sj.columns
+    j = jc.n
+    gd = table.gpu_dict
+    lists = {"cpu": table.cpu_values, "memory": table.memory_values,
+             "disk": table.columns[table.col("disk")].values, "gpu_count": gd["count"], "gpu_memory": gd["memory"],
+             "gpu_total": gd["total"]}
+    for name, vals in lists.items():
+        b = getattr(jc, name)
+        vals = np.asarray(vals, dtype=np.float64)
+        if len(vals) == 0:
+            continue
+        for side in (0, 1):
+            u = rng.random(j)
+            exact = vals[rng.integers(0, len(vals), j)]
+            b[:, side] = np.where(u < 0.15, exact, b[:, side])                       # exactly a table value
+            b[:, side] = np.where((u >= 0.15) & (u < 0.20), exact + 1e-9, b[:, side])  # just above one
+            b[:, side] = np.where((u >= 0.20) & (u < 0.25), exact - 1e-9, b[:, side])  # just below one
+            b[:, side] = np.where((u >= 0.25) & (u < 0.30), np.nan, b[:, side])       # not set
+            b[:, side] = np.where((u >= 0.30) & (u < 0.32), vals.max() * 10 + 1, b[:, side])
+            b[:, side] = np.where((u >= 0.32) & (u < 0.34), -1.0, b[:, side])
+    prices = np.concatenate([table.price_a, table.price_b])
+    if len(prices):
+        u = rng.random(j)
+        jc.max_price[:] = np.where(u < 0.2, prices[rng.integers(0, len(prices), j)], jc.max_price)
+        jc.max_price[:] = np.where((u >= 0.2) & (u < 0.25), 0.0, jc.max_price)
+    jc.exclude_not_available[:] = rng.random(j) < 0.3
+    return sj
+
+
 def job_objects(sj: SynthJobs) -> List[Tuple[M.Profile, M.Requirements]]:
     """The same batch as ``(Profile, Requirements)`` pairs for the object-level oracle."""
     jc = sj.columns
