@@ -339,6 +339,25 @@ static void fill_params(const dsm_table* t, const dsm_layout* L, const Plan& pl,
   mp.wps = pl.wps;
 }
 
+// The scratch of one call: acceptance tables, work counter, per-group column counts and, for a
+// top-k call, the counts per slot and the records per window.  Grown on demand (cudaFree +
+// cudaMalloc: a device-wide synchronisation) -- dsm_reserve does it ahead of time.
+static int ensure_match_scratch(dsm_ctx* ctx, const Plan& pl, bool bitmap) {
+  int rc;
+  const size_t jobs_pad = (size_t)pl.n_groups * JPG;
+  if ((rc = ensure(ctx->tabs, (size_t)pl.n_groups * pl.lay.n_entries * 16))) return rc;
+  if ((rc = ensure(ctx->counter, 256))) return rc;
+  if ((rc = ensure(ctx->group_nact, (size_t)pl.n_groups * 4))) return rc;
+  if (!bitmap) {
+    if ((unsigned long long)jobs_pad * pl.slots * pl.wps * 4ull > (64ull << 30))
+      return fail(DSM_E_TOO_LARGE, "per-window match records of this call exceed 64 GiB; split the jobs over several calls");
+    if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
+    if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * pl.wps * 4))) return rc;
+    if ((rc = ensure(ctx->slot_start, ((size_t)pl.slots + 1) * 4))) return rc;
+  }
+  return 0;
+}
+
 // Issue build -> match -> extract on the context's stream.  d_jobs, d_order (may be NULL) and the
 // outputs are device pointers.  Caller holds ctx->mu and has made the context's device current.
 static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, const uint32_t* d_jobs,
@@ -351,17 +370,7 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   if (rc) return rc;
   const bool row32 = t->desc.n_cols == 16;
 
-  const size_t jobs_pad = (size_t)pl.n_groups * JPG;
-  if ((rc = ensure(ctx->tabs, (size_t)pl.n_groups * pl.lay.n_entries * 16))) return rc;
-  if ((rc = ensure(ctx->counter, 256))) return rc;
-  if ((rc = ensure(ctx->group_nact, (size_t)pl.n_groups * 4))) return rc;
-  if (!bitmap) {
-    if ((unsigned long long)jobs_pad * pl.slots * pl.wps * 4ull > (64ull << 30))
-      return fail(DSM_E_TOO_LARGE, "per-window match records of this call exceed 64 GiB; split the jobs over several calls");
-    if ((rc = ensure(ctx->part_cnt, jobs_pad * pl.slots * 4))) return rc;
-    if ((rc = ensure(ctx->win_rows, jobs_pad * pl.slots * pl.wps * 4))) return rc;
-    if ((rc = ensure(ctx->slot_start, ((size_t)pl.slots + 1) * 4))) return rc;
-  }
+  if ((rc = ensure_match_scratch(ctx, pl, bitmap))) return rc;
 
   BuildParams bp;
   MatchParams mp;
@@ -592,6 +601,29 @@ int dsm_table_destroy(dsm_table* t) {
   return 0;
 }
 
+int dsm_table_patch_rows(dsm_ctx* ctx, dsm_table* t, const uint32_t* rows, uint32_t n, const uint16_t* codes) {
+  if (!ctx || !t || (n && (!rows || !codes))) return fail(DSM_E_ARG, "NULL argument");
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  if (n == 0) return 0;
+  for (uint32_t i = 0; i < n; ++i)
+    if (rows[i] >= t->desc.n_rows) return fail(DSM_E_ARG, "row index out of range");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  const size_t row_bytes = (size_t)t->desc.n_cols * 2;
+  int rc;
+  if ((rc = ensure(ctx->d_ids, (size_t)n * 4 + 16))) return rc;
+  if ((rc = ensure(ctx->d_raw, (size_t)n * row_bytes + 16))) return rc;
+  CK(cudaMemcpyAsync(ctx->d_ids.p, rows, (size_t)n * 4, cudaMemcpyHostToDevice, ctx->stream));
+  CK(cudaMemcpyAsync(ctx->d_raw.p, codes, (size_t)n * row_bytes, cudaMemcpyHostToDevice, ctx->stream));
+  const uint32_t row_u4 = t->desc.n_cols / 8;
+  k_patch_rows<<<(n * row_u4 + 255) / 256, 256, 0, ctx->stream>>>(t->rows, (const uint32_t*)ctx->d_ids.p, n,
+                                                                   (const uint4*)ctx->d_raw.p, row_u4);
+  CK(cudaGetLastError());
+  ctx->launches++;
+  CK(cudaStreamSynchronize(ctx->stream));
+  return 0;
+}
+
 int dsm_table_set_pack_dicts(dsm_ctx* ctx, dsm_table* t, const double* values,
                              const uint32_t counts[DSM_N_PACK_DICTS]) {
   if (!ctx || !t || !values || !counts) return fail(DSM_E_ARG, "NULL argument");
@@ -662,7 +694,9 @@ static int run_pack(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, const
                     ((role == DSM_ROLE_MEMORY || role == DSM_ROLE_DISK) && kind == DSM_COL_RANGE) ||
                     (role == DSM_ROLE_CPU_MEMORY && kind == DSM_COL_PAIR) || (role == DSM_ROLE_GPU && kind == DSM_COL_GPU) ||
                     (role == DSM_ROLE_BK && kind == DSM_COL_BK) ||
-                    (role >= DSM_ROLE_REGION && role <= DSM_ROLE_ZONE && kind == DSM_COL_BITSET);
+                    (role >= DSM_ROLE_REGION && role <= DSM_ROLE_ZONE && kind == DSM_COL_BITSET) ||
+                    (role == DSM_ROLE_STATE && kind == DSM_COL_BITSET && L->card[c] <= 256 && L->card[c] % 16 == 0);
+    if (role == DSM_ROLE_STATE) pp.has_state = 1;
     if (!ok) return fail(DSM_E_ARG, "layout.role does not fit the column's kind");
     if (role == DSM_ROLE_CPU && kind == DSM_COL_BITSET && L->card[c] != t->dict_n[DSM_DICT_CPU])
       return fail(DSM_E_ARG, "cpu bitset column: card != number of cpu values");
@@ -1080,6 +1114,33 @@ int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_row
   k_gather_price<<<(n + 255) / 256, 256, 0, ctx->stream>>>(t->price, d_rows, n, d_out);
   CK(cudaGetLastError());
   ctx->launches++;
+  return 0;
+}
+
+int dsm_reserve(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, uint32_t n_jobs, uint32_t k) {
+  if (!ctx || !t || !layout) return fail(DSM_E_ARG, "NULL argument");
+  if (t->device != ctx->device) return fail(DSM_E_ARG, "table and context are on different devices");
+  if (k > 4096) return fail(DSM_E_ARG, "k must be in 0..4096");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  Plan pl;
+  int rc = make_plan(ctx, t, layout, n_jobs, pl);
+  if (rc) return rc;
+  if ((rc = ensure_match_scratch(ctx, pl, k == 0))) return rc;
+  // buffers of the host-buffer and raw-job entry points
+  if ((rc = ensure(ctx->d_jobs, (size_t)n_jobs * layout->rec_words * 4))) return rc;
+  if ((rc = ensure(ctx->d_order, (size_t)n_jobs * 4))) return rc;
+  if ((rc = ensure(ctx->d_raw, (size_t)n_jobs * sizeof(dsm_raw_job)))) return rc;
+  if ((rc = ensure(ctx->d_keys, (size_t)n_jobs * 4))) return rc;
+  if (k) {
+    if ((rc = ensure(ctx->d_idx, (size_t)n_jobs * k * 4))) return rc;
+    if ((rc = ensure(ctx->d_cnt, (size_t)n_jobs * 4))) return rc;
+    if ((rc = ensure(ctx->d_max, (size_t)n_jobs * 4))) return rc;
+    if ((rc = ensure(ctx->d_out_ids, (size_t)n_jobs * k * 4 + (size_t)n_jobs * 8 + 8))) return rc;
+  } else {
+    if ((rc = ensure(ctx->d_bits, (size_t)n_jobs * (t->desc.n_rows / 32) * 4))) return rc;
+  }
+  CK(cudaStreamSynchronize(ctx->stream));
   return 0;
 }
 

@@ -1211,6 +1211,7 @@ struct PackParams {
   uint32_t dict_n[DSM_N_PACK_DICTS];
   const double* price;  // physical rows: [0, n_live_a) and [split_row, split_row + n_live_b) ascending
   uint32_t n_live_a, split_row, n_live_b;
+  uint32_t has_state;  // a DSM_ROLE_STATE column is part of the layout
   uint32_t* recs;
   uint32_t* keys;  // per job: 1 + index of the last column that rejects anything (for the evaluation order)
 };
@@ -1329,10 +1330,14 @@ __global__ void __launch_bounds__(128) k_pack_jobs(const PackParams p) {
         const uint32_t spot_mask = r.spot < 0 ? 3u : (r.spot == 0 ? 1u : 2u);
         w[0] = r.src_backend_mask;
         w[1] = r.off_backend_mask;
-        w[2] = spot_mask | ((uint32_t)r.status_mask << 8);
-        w[3] = (uint32_t)r.flag_req | ((uint32_t)r.flag_forbid << 16);
+        // with a state column (pool tables) status and the four dynamic flags are tested there
+        const uint32_t st = p.has_state ? 0xFFu : (uint32_t)r.status_mask;
+        const uint32_t req = p.has_state ? (r.flag_req & ~15u) : (uint32_t)r.flag_req;
+        const uint32_t forbid = p.has_state ? (r.flag_forbid & ~15u) : (uint32_t)r.flag_forbid;
+        w[2] = spot_mask | (st << 8);
+        w[3] = req | (forbid << 16);
         triv = r.src_backend_mask == 0xFFFFFFFFu && r.off_backend_mask == 0xFFFFFFFFu && spot_mask == 3u &&
-               r.status_mask == 0xFFu && r.flag_req == 0 && r.flag_forbid == 0;
+               st == 0xFFu && req == 0 && forbid == 0;
         break;
       }
       case DSM_ROLE_REGION:
@@ -1359,6 +1364,15 @@ __global__ void __launch_bounds__(128) k_pack_jobs(const PackParams p) {
           }
           // the entry of rows whose value is unknown (last) passes an instance-type / zone filter
           if (role == DSM_ROLE_ITYPE || role == DSM_ROLE_ZONE) w[(card - 1u) >> 5] |= 1u << ((card - 1u) & 31u);
+        }
+        break;
+      }
+      case DSM_ROLE_STATE: {
+        triv = true;
+        const uint32_t dyn_req = r.flag_req & 15u, dyn_forbid = r.flag_forbid & 15u;
+        for (uint32_t e = 0; e < card; ++e) {
+          const bool ok = ((r.status_mask >> (e >> 4)) & 1u) && ((e & 15u) & dyn_req) == dyn_req && ((e & 15u) & dyn_forbid) == 0u;
+          if (ok) w[e >> 5] |= 1u << (e & 31u); else triv = false;
         }
         break;
       }
@@ -1470,4 +1484,11 @@ __global__ void k_rows_to_source(const uint32_t* rows, uint32_t n, const int32_t
   if (i >= n) return;
   const uint32_t r = rows[i];
   out[i] = r == DSM_NO_ROW ? -1 : row_to_source[r];
+}
+
+// rows[i] <- codes[i] (whole rows of `row_u4` uint4): in-place patch of a resident table
+__global__ void k_patch_rows(uint4* table, const uint32_t* rows, uint32_t n, const uint4* codes, uint32_t row_u4) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * row_u4) return;
+  table[(size_t)rows[i / row_u4] * row_u4 + i % row_u4] = codes[i];
 }

@@ -44,6 +44,10 @@ FLAG_BLOCKS_UNKNOWN = 2   # total_blocks is None (still provisioning)
 FLAG_SHARED = 4           # total_blocks > 1
 FLAG_NO_OFFER = 8         # instance.offer is None
 FLAG_AUTO_DIVISIBLE = 16  # is_divisible_into_blocks(cpu, gpu, "auto")[0]
+# Pool tables keep what changes between scheduler passes -- status and these four flags -- in a
+# column of its own ("state", code = status * 16 + flags, every combination enumerated), so an
+# instance that turns BUSY or unreachable is a one-row patch and never a new dictionary entry.
+DYNAMIC_FLAGS = FLAG_UNREACHABLE | FLAG_BLOCKS_UNKNOWN | FLAG_SHARED | FLAG_NO_OFFER
 
 KIND_RANGE, KIND_BITSET, KIND_GPU, KIND_BK, KIND_PAIR = 1, 2, 3, 4, 5
 COLF_NULL_PASSES = 1
@@ -89,6 +93,9 @@ class ShapeTable:
     gpu_vendor: np.ndarray      # int8 vendor code, 0 = none
     gpu_name: List[Optional[str]]  # original casing; None without GPUs
     gpu_memory_gib: np.ndarray  # float64, NaN without GPUs
+    # catalog items without a disk size whose backend lets the job choose one: index into
+    # OfferColumns.disk_conf_ranges (-1 / None: the item has its own size, or passes as it is)
+    disk_conf: Optional[np.ndarray] = None
 
     def __len__(self) -> int:
         return len(self.cpus)
@@ -118,6 +125,10 @@ class OfferColumns:
     names: List[str] = field(default_factory=list)
     zone_id: Optional[np.ndarray] = None     # int32 -> zones, -1 = unknown zone (passes)
     zones: List[str] = field(default_factory=list)
+    # (min, max) GiB of every configurable-disk range shapes refer to (NaN = open end); such an
+    # item matches a job iff the job's disk range and this one overlap (choose_disk_size_mib,
+    # core/backends/base/offers.py:161-175)
+    disk_conf_ranges: List[Tuple[float, float]] = field(default_factory=list)
 
     def __len__(self) -> int:
         return len(self.price)
@@ -172,6 +183,7 @@ class EncodedTable:
     pair_entries: Optional[np.ndarray] = None   # uint32 [n_pairs]
     cpu_values: Optional[np.ndarray] = None
     memory_values: Optional[np.ndarray] = None
+    disk_conf_ranges: List[Tuple[float, float]] = field(default_factory=list)
 
     @property
     def n_rest(self) -> int:
@@ -225,10 +237,15 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
     disk = np.asarray(sh.disk_gib, dtype=np.float64)
     disk_null = np.isnan(disk)
     disk_vals, disk_ord_nn = _ordinals(disk[~disk_null]) if (~disk_null).any() else (np.zeros(0), np.zeros(0, np.int64))
-    disk_ord = np.full(len(sh), len(disk_vals), dtype=np.int64)  # null entry = last
+    n_conf = len(oc.disk_conf_ranges)
+    disk_ord = np.full(len(sh), len(disk_vals) + n_conf, dtype=np.int64)  # null entry = last
     disk_ord[~disk_null] = disk_ord_nn
+    if n_conf and sh.disk_conf is not None:  # entries [n values, n values + n_conf): one per configurable range
+        conf = np.asarray(sh.disk_conf, dtype=np.int64)
+        pick = disk_null & (conf >= 0)
+        disk_ord[pick] = len(disk_vals) + conf[pick]
     for nm, vals in (("cpu", cpu_vals), ("memory", mem_vals), ("disk", disk_vals)):
-        _check_card(nm, len(vals) + 1)
+        _check_card(nm, len(vals) + 1 + (n_conf if nm == "disk" else 0))
 
     # ---- accelerator configuration dictionary
     gcount = np.asarray(sh.gpu_count, dtype=np.int64)
@@ -274,6 +291,11 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
     flags = np.zeros(n, dtype=np.int64) if oc.flags is None else np.asarray(oc.flags, dtype=np.int64).copy()
     flags |= np.where(_auto_divisible(np.asarray(sh.cpus, dtype=np.int64)[sid], gpu_eff), FLAG_AUTO_DIVISIBLE, 0)
     status = np.full(n, NO_STATUS_CODE, dtype=np.int64) if oc.status is None else np.asarray(oc.status, dtype=np.int64)
+    state_code = None
+    if oc.is_pool:  # status and the dynamic flags live in the "state" column
+        state_code = status * 16 + (flags & DYNAMIC_FLAGS)
+        status = np.full(n, NO_STATUS_CODE, dtype=np.int64)
+        flags = flags & ~np.int64(DYNAMIC_FLAGS)
     bkey = (np.asarray(oc.src_backend, dtype=np.int64) | (np.asarray(oc.backend, dtype=np.int64) << 5)
             | (np.asarray(oc.spot, dtype=np.int64) << 10) | (status << 11) | (flags << 14))
     present = np.unique(bkey)
@@ -298,11 +320,14 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
     tail_cols: List[Column] = [
         Column("gpu", KIND_GPU, len(guniq)),
         Column("bk", KIND_BK, len(present) + 1),
-        Column("disk", KIND_RANGE, len(disk_vals) + 1, flags=COLF_NULL_PASSES, values=disk_vals),
+        Column("disk", KIND_BITSET if n_conf else KIND_RANGE, len(disk_vals) + n_conf + 1,
+               flags=0 if n_conf else COLF_NULL_PASSES, values=disk_vals),
         Column("region", KIND_BITSET, reg_card, lookup={r: i for i, r in enumerate(oc.regions)}),
     ]
     tail_rows: List[np.ndarray] = [ginv[sid], bk_code, disk_ord[sid], reg_codes]
     if oc.is_pool:
+        tail_cols.insert(2, Column("state", KIND_BITSET, (NO_STATUS_CODE + 1) * 16))
+        tail_rows.insert(2, state_code)
         fl_codes, fl_card = set_codes(oc.fleet_id, len(oc.fleets), "fleet")
         nm_codes, nm_card = set_codes(oc.name_id, len(oc.names), "name")
         zn_codes, zn_card = set_codes(oc.zone_id, len(oc.zones), "zone")
@@ -361,6 +386,7 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
         gpu_dict=dict(count=cnt_vals, memory=gm_vals, total=tot_vals, cc=cc_vals, names=lower_names),
         price_a=price[order[:n_avail]], price_b=price[order[n_avail:]], is_pool=oc.is_pool,
         pair_entries=pair_entries, cpu_values=cpu_vals, memory_values=mem_vals,
+        disk_conf_ranges=list(oc.disk_conf_ranges),
     )
 
 
@@ -450,6 +476,19 @@ class PackedJobs:
     order: Optional[np.ndarray] = None  # uint32 [J] evaluation order (dsm_layout.job_order), None = as given
 
 
+DEFAULT_DISK_MIN_GIB = 100.0  # DEFAULT_DISK = DiskSpec(size=Range(min=100GB)), core/models/resources.py:250
+
+
+def disk_request_bounds(disk: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+    """(lo, hi) of the disk range a job brings to ``choose_disk_size_mib``: its own range, or
+    ``DEFAULT_DISK.size`` when it states none (offers.py:170); open ends as -inf / +inf."""
+    d = np.asarray(disk, dtype=np.float64)
+    unset = np.isnan(d).all(axis=1)
+    lo = np.where(np.isnan(d[:, 0]), -np.inf, d[:, 0])
+    hi = np.where(np.isnan(d[:, 1]), np.inf, d[:, 1])
+    return np.where(unset, DEFAULT_DISK_MIN_GIB, lo), np.where(unset, np.inf, hi)
+
+
 def _range_trivial(words: np.ndarray, n_values: int) -> np.ndarray:
     """Jobs whose packed range accepts every one of ``n_values`` ordinals."""
     if n_values == 0:
@@ -533,7 +572,25 @@ def pack_jobs(t: EncodedTable, jc: JobColumns, n_used: Optional[int] = None) -> 
         put("memory", mem_w, KIND_RANGE, len(mem_vals), mem_triv)
     dcol = t.columns[t.col("disk")]
     disk_w = _range_words(dcol.values, jc.disk)
-    put("disk", disk_w, KIND_RANGE, dcol.card, _range_trivial(disk_w, len(dcol.values)), COLF_NULL_PASSES)
+    if not t.disk_conf_ranges:
+        put("disk", disk_w, KIND_RANGE, dcol.card, _range_trivial(disk_w, len(dcol.values)), COLF_NULL_PASSES)
+    else:
+        # entries: the real sizes (by range), one per configurable range (the job's disk range --
+        # DEFAULT_DISK when it states none -- must overlap it), the always-passing null entry
+        nv = len(dcol.values)
+        e = np.arange(nv, dtype=np.uint32)[None, :]
+        ok = np.zeros((j, dcol.card), dtype=bool)
+        ok[:, :nv] = (e >= (disk_w & 0xFFFF)[:, None]) & (e <= (disk_w >> 16)[:, None])
+        lo, hi = disk_request_bounds(jc.disk)
+        for ci, (cmin, cmax) in enumerate(t.disk_conf_ranges):
+            start = lo if np.isnan(cmin) else np.maximum(lo, cmin)
+            end = hi if np.isnan(cmax) else np.minimum(hi, cmax)
+            ok[:, nv + ci] = ~(start > end)
+        ok[:, dcol.card - 1] = True
+        bits = np.zeros((j, (dcol.card + 31) // 32), dtype=np.uint32)
+        jj, ee = np.nonzero(ok)
+        np.bitwise_or.at(bits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
+        put("disk", bits, KIND_BITSET, dcol.card, ok.all(axis=1))
 
     # accelerator sub-predicate
     gd = t.gpu_dict
@@ -571,6 +628,17 @@ def pack_jobs(t: EncodedTable, jc: JobColumns, n_used: Optional[int] = None) -> 
     forbid = np.zeros(j, dtype=np.uint32) if jc.flag_forbid is None else np.asarray(jc.flag_forbid, dtype=np.uint32)
     src_m = np.asarray(jc.src_backend_mask, dtype=np.uint32)
     off_m = np.asarray(jc.off_backend_mask, dtype=np.uint32)
+    if t.is_pool:
+        # status and the dynamic flags are tested on the "state" column: entry = status * 16 + flags
+        e = np.arange((NO_STATUS_CODE + 1) * 16, dtype=np.uint32)[None, :]
+        dyn_req, dyn_forbid = (req & DYNAMIC_FLAGS)[:, None], (forbid & DYNAMIC_FLAGS)[:, None]
+        ok = (((st_mask[:, None] >> (e >> 4)) & 1) != 0) & (((e & 15) & dyn_req) == dyn_req) & (((e & 15) & dyn_forbid) == 0)
+        sbits = np.zeros((j, ok.shape[1] // 32 + (ok.shape[1] % 32 != 0)), dtype=np.uint32)
+        jj, ee = np.nonzero(ok)
+        np.bitwise_or.at(sbits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
+        put("state", sbits, KIND_BITSET, ok.shape[1], ok.all(axis=1))
+        st_mask = np.full(j, 0xFF, dtype=np.uint32)
+        req, forbid = req & ~np.uint32(DYNAMIC_FLAGS), forbid & ~np.uint32(DYNAMIC_FLAGS)
     bwords = np.stack([src_m, off_m, spot_mask | (st_mask << np.uint32(8)), req | (forbid << np.uint32(16))], axis=1)
     bk_triv = ((src_m == 0xFFFFFFFF) & (off_m == 0xFFFFFFFF) & (spot_mask == 3) & (st_mask == 0xFF)
                & (req == 0) & (forbid == 0))
@@ -643,7 +711,7 @@ def _column_shapes(t: EncodedTable, cpu_as_set: bool):
             out.append((KIND_BITSET, col.card, 0, 0, n_cpu_words) if cpu_as_set else (KIND_RANGE, col.card, 0, 0, 1))
         elif col.name == "memory":
             out.append((KIND_RANGE, col.card, 0, 0, 1))
-        elif col.name == "disk":
+        elif col.name == "disk":  # (a table with configurable-disk entries is packed on the host: raw_layout)
             out.append((KIND_RANGE, col.card, COLF_NULL_PASSES, 0, 1))
         elif col.name == "gpu":
             nwn = (max(1, len(t.gpu_dict["names"])) + 31) // 32
@@ -669,7 +737,7 @@ def raw_layout(t: EncodedTable, jc: JobColumns):
     while n_used > 1 and names[n_used - 1] in any_of and \
             (any_of[names[n_used - 1]] is None or bool(np.asarray(any_of[names[n_used - 1]]).all())):
         n_used -= 1
-    if any(c.card > LUT_THRESHOLD for c in t.columns[:n_used]):
+    if any(c.card > LUT_THRESHOLD for c in t.columns[:n_used]) or t.disk_conf_ranges:
         return None
     cpu_as_set = False
     if jc.blocks is not None:
@@ -768,3 +836,8 @@ def pack_dicts(t: EncodedTable) -> Tuple[np.ndarray, List[int]]:
              gd["cc"]]
     lists = [np.asarray(x, dtype=np.float64) for x in lists]
     return (np.concatenate(lists) if sum(len(x) for x in lists) else np.zeros(0)), [len(x) for x in lists]
+
+
+def state_code(status_code: int, flags: int) -> int:
+    """Code of a pool table's "state" column for an instance status and its FLAG_* bits."""
+    return int(status_code) * 16 + (int(flags) & DYNAMIC_FLAGS)

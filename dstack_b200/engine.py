@@ -211,6 +211,16 @@ class DeviceTable:
             raise RuntimeError("table is closed")
         return self._h
 
+    def patch_rows(self, rows: np.ndarray) -> None:
+        """Copy the host table's current codes of physical rows ``rows`` to the device (after they
+        were changed in ``self.table.rows``): an in-place update, no re-upload of the table."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint32)
+        if len(rows) == 0:
+            return
+        codes = np.ascontiguousarray(self.table.rows[rows], dtype=np.uint16)
+        native.check(self._lib.dsm_table_patch_rows(self._matcher.handle, self.handle, native.ptr(rows), len(rows),
+                                                    native.ptr(codes)))
+
     def close(self) -> None:
         if self._h is not None:
             self._lib.dsm_table_destroy(self._h)

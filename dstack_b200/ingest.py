@@ -43,8 +43,8 @@ class _Shapes:
     def __init__(self):
         self.intern = _Interner()
 
-    def add(self, cpus, memory_gib, disk_gib, gpu_count, vendor, name, gpu_gib) -> int:
-        return self.intern((cpus, memory_gib, disk_gib, gpu_count, vendor, name, gpu_gib))
+    def add(self, cpus, memory_gib, disk_gib, gpu_count, vendor, name, gpu_gib, disk_conf=-1) -> int:
+        return self.intern((cpus, memory_gib, disk_gib, gpu_count, vendor, name, gpu_gib, disk_conf))
 
     def table(self) -> ShapeTable:
         v = self.intern.values
@@ -56,6 +56,7 @@ class _Shapes:
             gpu_vendor=np.array([s[4] for s in v], dtype=np.int8),
             gpu_name=[s[5] for s in v],
             gpu_memory_gib=np.array([math.nan if s[6] is None else s[6] for s in v], dtype=np.float64),
+            disk_conf=np.array([s[7] if len(s) > 7 else -1 for s in v], dtype=np.int64),
         )
 
 
@@ -162,6 +163,49 @@ def columns_from_catalog_items(items: Sequence[Any]) -> OfferColumns:
     return OfferColumns(shapes=shapes.table(), shape_id=shape_id, price=price, spot=spot,
                         available=np.ones(n, bool), backend=z, src_backend=z, region_id=region_id,
                         regions=regions.values, itype_id=itype_id, itypes=itypes.values)
+
+
+def _range_gib(rng: Any) -> Tuple[float, float]:
+    return (math.nan if rng is None or rng.min is None else float(rng.min),
+            math.nan if rng is None or rng.max is None else float(rng.max))
+
+
+def columns_from_backend_items(items_by_backend: Sequence[Tuple[Any, Sequence[Any], Any]]) -> OfferColumns:
+    """``[(backend_type, CatalogItem rows, configurable_disk_size), ...]`` in project-backend
+    order, each list price-sorted: what every backend's ``get_catalog_offers`` reads from gpuhunt
+    BEFORE a job's requirements are applied (``core/backends/base/offers.py:18-43``).  An item
+    without a disk size keeps none: whether a job can have it -- its disk range must overlap the
+    backend's configurable range (``:161-175``) -- is part of the device predicate, and its size
+    is chosen when a result row is turned into an offer."""
+    shapes, regions, itypes = _Shapes(), _Interner(), _Interner()
+    ranges = _Interner()
+    n = sum(len(items) for _, items, _ in items_by_backend)
+    shape_id = np.empty(n, np.int32)
+    price = np.empty(n, np.float64)
+    spot = np.empty(n, bool)
+    backend = np.empty(n, np.int8)
+    region_id = np.empty(n, np.int32)
+    itype_id = np.empty(n, np.int32)
+    i = 0
+    for btype, items, conf in items_by_backend:
+        code = backend_code(btype)
+        conf_id = ranges(_range_gib(conf))
+        for it in items:
+            no_disk = not it.disk_size  # choose_disk_size_mib tests truthiness (:166)
+            shape_id[i] = shapes.add(it.cpu, float(it.memory), None if no_disk else float(it.disk_size),
+                                     it.gpu_count, vendor_code(it.gpu_vendor), it.gpu_name,
+                                     None if it.gpu_memory is None else float(it.gpu_memory),
+                                     conf_id if no_disk else -1)
+            price[i] = it.price
+            spot[i] = it.spot
+            backend[i] = code
+            region_id[i] = regions(it.location)
+            itype_id[i] = itypes(it.instance_name)
+            i += 1
+    return OfferColumns(shapes=shapes.table(), shape_id=shape_id, price=price, spot=spot,
+                        available=np.ones(n, bool), backend=backend, src_backend=backend.copy(),
+                        region_id=region_id, regions=regions.values, itype_id=itype_id, itypes=itypes.values,
+                        disk_conf_ranges=list(ranges.values))
 
 
 def columns_from_pool_instances(instances: Sequence[Any], *, blocks_of: Optional[Sequence[int]] = None,

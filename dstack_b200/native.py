@@ -27,7 +27,8 @@ EXPORTS = [
     "dsm_timing_enable", "dsm_timing_read", "dsm_match_bitmap_static", "dsm_merge_shards_strided_dev",
     "dsm_merge_shards_interleaved_dev", "dsm_timing_read_parts", "dsm_table_set_pack_dicts",
     "dsm_table_set_source_map", "dsm_match_topk_raw", "dsm_jobs_pack_dev", "dsm_match_indices",
-    "dsm_match_topk_raw_src", "dsm_match_topk_cols",
+    "dsm_match_topk_raw_src", "dsm_match_topk_cols", "dsm_reserve",
+    "dsm_table_patch_rows",
 ]
 N_PACK_DICTS = 7  # cpu, memory, disk, gpu count, gpu memory, gpu total, compute capability
 
@@ -43,7 +44,7 @@ RAW_JOB = np.dtype([
 RAWF_EXCLUDE_NOT_AVAILABLE, RAWF_GPU_NAME_ANY, RAWF_REGION_ANY, RAWF_ITYPE_ANY = 1, 2, 4, 8
 RAWF_FLEET_ANY, RAWF_NAME_ANY, RAWF_ZONE_ANY = 16, 32, 64
 ROLES = {"cpu": 1, "memory": 2, "cpu_memory": 3, "disk": 4, "gpu": 5, "bk": 6, "region": 7, "itype": 8,
-         "fleet": 9, "name": 10, "zone": 11}
+         "fleet": 9, "name": 10, "zone": 11, "state": 12}
 STATIC_SCRATCH_BYTES = 2 << 20  # DSM_STATIC_SCRATCH_BYTES
 
 
@@ -144,6 +145,8 @@ def lib() -> C.CDLL:
     L.dsm_match_topk_raw.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp, u32, u32, vp, vp, vp]
     L.dsm_match_topk_raw_src.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp, u32, u32, vp, vp, vp]
     L.dsm_match_topk_cols.argtypes = [vp, vp, C.POINTER(Layout), C.POINTER(JobColumnsC), u32, u32, vp, vp, vp]
+    L.dsm_table_patch_rows.argtypes = [vp, vp, vp, u32, vp]
+    L.dsm_reserve.argtypes = [vp, vp, C.POINTER(Layout), u32, u32]
     L.dsm_jobs_pack_dev.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, vp, vp, vp]
     L.dsm_match_indices.argtypes = [vp, vp, C.POINTER(Layout), vp, u32, C.c_int, vp, C.POINTER(vp)]
     L.dsm_plan_query.argtypes = [vp, vp, C.POINTER(Layout), u32, u32, C.POINTER(u32 * 8)]

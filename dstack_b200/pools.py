@@ -15,7 +15,8 @@ from typing import Any, List, Optional, Sequence, Tuple
 import numpy as np
 
 from . import models as M
-from .encode import EncodedTable, encode_table
+from .encode import (FLAG_BLOCKS_UNKNOWN, FLAG_NO_OFFER, FLAG_SHARED, FLAG_UNREACHABLE, STATUS_CODES, EncodedTable,
+                     encode_table, state_code)
 from .engine import DeviceTable, Matcher, default_matcher
 from .ingest import JobFilter, PoolParseCache, columns_from_pool_instances, job_columns
 from .offers import requirements_to_query_filter
@@ -50,6 +51,40 @@ def _pool_filter(profile: Any, *, requirements: Optional[Any], status: Optional[
     )
 
 
+def patch_pool_rows(t: EncodedTable, instances: Sequence[Any], changed: Sequence[int], row_of: np.ndarray,
+                    offers: Optional[Sequence[Any]] = None) -> Optional[np.ndarray]:
+    """Host half of :meth:`PoolIndex.refresh`: re-encode status / reachability / block state / fleet
+    of the instances at ``changed`` into ``t.rows``.  Returns the physical rows that changed, or
+    ``None`` -- nothing written -- when an instance moved to a fleet the table's dictionary does not
+    hold (status and flags are a closed dictionary: every combination has its code)."""
+    state_col, fleet_col = t.col("state"), t.col("fleet")
+    fleet_lookup = t.columns[fleet_col].lookup
+    unknown_fleet = t.columns[fleet_col].card - 1
+    rows = row_of[np.asarray(changed, dtype=np.int64)]
+    new_codes = []
+    for pos in changed:
+        inst = instances[pos]
+        flags = 0
+        if inst.unreachable:
+            flags |= FLAG_UNREACHABLE
+        if inst.total_blocks is None:
+            flags |= FLAG_BLOCKS_UNKNOWN
+        elif inst.total_blocks > 1:
+            flags |= FLAG_SHARED
+        if (offers is None or offers[pos] is None) and inst.offer is None:
+            flags |= FLAG_NO_OFFER
+        st = inst.status
+        code = state_code(STATUS_CODES[st.value if hasattr(st, "value") else str(st)], flags)
+        fleet = unknown_fleet if inst.fleet_id is None else fleet_lookup.get(inst.fleet_id, -1)
+        if fleet < 0:
+            return None
+        new_codes.append((code, fleet))
+    for r, (code, fleet) in zip(rows, new_codes):
+        t.rows[r, state_col] = code
+        t.rows[r, fleet_col] = fleet
+    return rows
+
+
 class PoolIndex:
     """Pool rows resident on the GPU.  Build once per scheduler tick, query for many jobs."""
 
@@ -59,12 +94,41 @@ class PoolIndex:
         ticks, so that only rows whose stored JSON changed are parsed again."""
         self.matcher = matcher or default_matcher()
         self.instances = list(pool_instances)
+        self._offers, self._parse_cache = offers, parse_cache
         self.table: Optional[EncodedTable] = None
         self.device_table: Optional[DeviceTable] = None
+        self.rebuilds = 0
+        self._build()
+
+    def _build(self) -> None:
+        if self.device_table is not None:
+            self.device_table.close()
+            self.device_table = None
         if self.instances:
-            self.table = encode_table(columns_from_pool_instances(self.instances, offers=offers,
-                                                                  parse_cache=parse_cache))
+            self.table = encode_table(columns_from_pool_instances(self.instances, offers=self._offers,
+                                                                  parse_cache=self._parse_cache))
             self.device_table = self.matcher.upload(self.table)
+            self._row_of = np.empty(self.table.n_src, np.int64)  # source position -> physical row
+            live = self.table.perm >= 0
+            self._row_of[self.table.perm[live]] = np.flatnonzero(live)
+        self.rebuilds += 1
+
+    def refresh(self, changed: Sequence[int]) -> bool:
+        """The instances at positions ``changed`` (of the list this index was built from) have a new
+        status, reachability, block state or fleet -- what a scheduler pass changes
+        (``process_submitted_jobs.py:398-399``) and what ``filter_pool_instances`` reads fresh for
+        every job (``pools.py:458-488``).  Their rows are rewritten in place on the device.  Returns
+        True when that sufficed; when an instance moved to a fleet never seen in this pool the table
+        is rebuilt and False is returned.  Changes to an instance's offer, backend, region, name or
+        provisioning data, and added or removed instances, need a new index."""
+        if self.table is None or len(changed) == 0:
+            return True
+        rows = patch_pool_rows(self.table, self.instances, changed, self._row_of, self._offers)
+        if rows is None:
+            self._build()
+            return False
+        self.device_table.patch_rows(rows)
+        return True
 
     def close(self) -> None:
         if self.device_table is not None:

@@ -250,11 +250,63 @@ class OfferCatalog:
         self.device_table = self.matcher.upload(self.table)
         return self
 
-    def pair_at(self, i: int) -> Tuple[Any, Any]:
-        """``(backend, offer)`` of source position ``i``."""
+    @classmethod
+    def from_catalog_items(cls, items_by_backend: Sequence[Tuple[Any, Sequence[Any], Any]], *,
+                           matcher: Optional[Matcher] = None) -> "OfferCatalog":
+        """A catalog of ``gpuhunt.CatalogItem`` rows: ``[(backend, items, configurable_disk_size),
+        ...]`` in project-backend order, each list price-sorted -- what the backends'
+        ``get_catalog_offers`` reads BEFORE a job's requirements are applied.
+
+        This is the form to use for backends with configurable disks (AWS, GCP, Azure ...).  In the
+        reference an item without a disk size becomes an offer whose disk is sized to the job
+        (``catalog_item_to_offer`` / ``choose_disk_size_mib``, ``core/backends/base/offers.py:46-83,
+        161-175``), so whether it matches depends on the job's disk range overlapping the backend's
+        configurable range, not on a fixed size.  Here that overlap test is part of the device
+        predicate, and a result row is turned into an offer -- with the disk the job gets -- by
+        :meth:`pairs` / :meth:`offers_for`.  (A catalog built from ready-made offers,
+        ``OfferCatalog(offers_by_backend)``, takes every offer's disk as a fixed size.)"""
+        from .ingest import columns_from_backend_items
+
+        self = cls.__new__(cls)
+        self.matcher = matcher or default_matcher()
+        self.backends, self.offers, self._materialize = None, None, None
+        self._items = [(b, it, conf) for b, items, conf in items_by_backend for it in items]
+        self.table = encode_table(columns_from_backend_items([(b.TYPE, items, conf) for b, items, conf in items_by_backend]))
+        self.device_table = self.matcher.upload(self.table)
+        return self
+
+    def pair_at(self, i: int, disk_range: Optional[Any] = None) -> Tuple[Any, Any]:
+        """``(backend, offer)`` of source position ``i``; for a catalog of items the offer is made
+        here, its disk sized for a job whose disk range is ``disk_range`` (None: DEFAULT_DISK)."""
+        if getattr(self, "_items", None) is not None:
+            from .offers import choose_disk_size_mib
+
+            backend, item, conf = self._items[int(i)]
+            disk_mib = choose_disk_size_mib(item.disk_size, disk_range, conf)
+            if disk_mib is None:
+                raise RuntimeError("a matched catalog item has no feasible disk size: the device predicate "
+                                   "and choose_disk_size_mib disagree")
+            gpus = []
+            if item.gpu_count > 0:
+                gpus = [M.Gpu(vendor=item.gpu_vendor, name=item.gpu_name,
+                              memory_mib=round(item.gpu_memory * 1024))] * item.gpu_count
+            res = M.Resources(cpus=item.cpu, memory_mib=round(item.memory * 1024), gpus=gpus, spot=item.spot,
+                              disk=M.Disk(size_mib=disk_mib))
+            res.description = res.pretty_format()
+            return backend, M.InstanceOfferWithAvailability(
+                backend=backend.TYPE, region=item.location, price=item.price,
+                instance=M.InstanceType(name=item.instance_name, resources=res),
+                availability=M.InstanceAvailability.UNKNOWN)
         if self._materialize is not None:
             return self._materialize(int(i))
         return self.backends[i], self.offers[i]
+
+    @staticmethod
+    def _disk_range_of(f: JobFilter) -> Optional[Any]:
+        q = f.query
+        if q.min_disk_size is None and q.max_disk_size is None:
+            return None
+        return M.Range[M.Memory](min=q.min_disk_size, max=q.max_disk_size)
 
     def close(self) -> None:
         self.device_table.close()
@@ -270,15 +322,19 @@ class OfferCatalog:
         hits = self.matcher.match_all(self.device_table, self.jobs(filters), order="rank")
         out = []
         for f, rows in zip(filters, hits):
-            pairs = [self.pair_at(i) for i in rows]
+            disk = self._disk_range_of(f)
+            pairs = [self.pair_at(i, disk) for i in rows]
             if f.require_auto_divisible or f.blocks > 1:  # offers.py:116 writes the count back
                 for _, o in pairs:
                     o.total_blocks = _blocks_of_offer(o, "auto" if f.require_auto_divisible else f.blocks)[1]
             out.append(pairs)
         return out
 
-    def pairs(self, index_row: np.ndarray) -> List[Tuple[Any, Any]]:
-        return [self.pair_at(i) for i in index_row if i >= 0]
+    def pairs(self, index_row: np.ndarray, job: Optional[JobFilter] = None) -> List[Tuple[Any, Any]]:
+        """``(backend, offer)`` of a ``match_topk`` row; ``job``: the filter the row answers (a
+        catalog of items sizes the offers' disks for it)."""
+        disk = None if job is None else self._disk_range_of(job)
+        return [self.pair_at(i, disk) for i in index_row if i >= 0]
 
 
 class OfferCatalogCache:
@@ -289,7 +345,8 @@ class OfferCatalogCache:
     follows the same clock: ``get()`` returns the current catalog and rebuilds it from
     ``fetch()`` -- ``[(backend, price-sorted offers), ...]`` -- on the first use after ``ttl``
     seconds.  The previous table is freed once the new one is up.  Calls may come from several
-    threads (the reference fetches offers from a thread pool); a lock serialises rebuilds."""
+    threads (the reference fetches offers from a thread pool): one of them rebuilds, outside the
+    lock, the others keep matching against the previous table until the swap."""
 
     def __init__(self, fetch, *, ttl: float = 30.0, matcher: Optional[Matcher] = None,
                  clock=None, build=None):
@@ -302,20 +359,42 @@ class OfferCatalogCache:
         self._clock = clock or time.monotonic
         self._build = build or (lambda offers_by_backend: OfferCatalog(offers_by_backend, matcher=self._matcher))
         self._lock = threading.Lock()
+        self._ready = threading.Condition(self._lock)
+        self._building = False
         self._catalog: Optional[Any] = None
         self._born = 0.0
         self.rebuilds = 0
 
     def get(self) -> Any:
+        """The current catalog.  When it has expired, the caller that notices builds the replacement
+        -- fetch, encode, upload -- WITHOUT holding the lock, and swaps it in when it is up; matcher
+        threads that call meanwhile keep getting the previous catalog (only the very first build
+        makes them wait).  The replaced table is freed after the swap."""
         with self._lock:
             now = self._clock()
-            if self._catalog is None or now - self._born >= self.ttl:
-                fresh = self._build(self._fetch())
-                old, self._catalog, self._born = self._catalog, fresh, now
-                self.rebuilds += 1
-                if old is not None:
-                    old.close()
-            return self._catalog
+            fresh_enough = self._catalog is not None and now - self._born < self.ttl
+            if fresh_enough or (self._catalog is not None and self._building):
+                return self._catalog
+            if self._catalog is None and self._building:
+                while self._building:  # first build in progress on another thread
+                    self._ready.wait()
+                return self._catalog
+            self._building = True
+        try:
+            fresh = self._build(self._fetch())
+        except BaseException:
+            with self._lock:
+                self._building = False
+                self._ready.notify_all()
+            raise
+        with self._lock:
+            old, self._catalog, self._born = self._catalog, fresh, self._clock()
+            self._building = False
+            self.rebuilds += 1
+            self._ready.notify_all()
+        if old is not None:
+            old.close()
+        return fresh
 
     def invalidate(self) -> None:
         """Force a rebuild on the next ``get()`` (e.g. after a backend was added or removed)."""

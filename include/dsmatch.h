@@ -183,7 +183,11 @@ typedef struct dsm_raw_job {
 enum dsm_col_role {
   DSM_ROLE_NONE = 0, DSM_ROLE_CPU = 1, DSM_ROLE_MEMORY = 2, DSM_ROLE_CPU_MEMORY = 3, DSM_ROLE_DISK = 4,
   DSM_ROLE_GPU = 5, DSM_ROLE_BK = 6, DSM_ROLE_REGION = 7, DSM_ROLE_ITYPE = 8, DSM_ROLE_FLEET = 9,
-  DSM_ROLE_NAME = 10, DSM_ROLE_ZONE = 11
+  DSM_ROLE_NAME = 10, DSM_ROLE_ZONE = 11,
+  /* pool tables: entry = status * 16 + (unreachable | blocks unknown << 1 | shared << 2 | no offer << 3);
+   * accepted iff the status is in status_mask and the flags satisfy flag_req / flag_forbid (their low
+   * four bits; the remaining bits are tested on the DSM_ROLE_BK column) */
+  DSM_ROLE_STATE = 12
 };
 
 /* sorted distinct values of the table's range attributes, in this order */
@@ -214,6 +218,13 @@ int dsm_table_create(dsm_ctx* ctx, const dsm_table_desc* desc, const uint16_t* r
                      const double* price, const uint32_t* gpu_entries,
                      const uint32_t* bk_entries, const uint32_t* pair_entries, dsm_table** out);
 int dsm_table_destroy(dsm_table* t);
+
+/* Rewrite n rows of a resident table in place: rows[i] = physical row, codes = n * n_cols u16
+ * (host).  For attributes that change between scheduler passes without adding a dictionary
+ * value (an instance's status, reachability, busy blocks, fleet: server/services/pools.py:
+ * 458-488 reads them fresh for every job).  Row order and prices are not touched.  Serialised
+ * with the matches of `ctx` (same stream); matches on other contexts must not overlap it. */
+int dsm_table_patch_rows(dsm_ctx* ctx, dsm_table* t, const uint32_t* rows, uint32_t n, const uint16_t* codes);
 
 /* Copy a per-call code->class remap to the device (see dsm_layout.lut).  The returned device
  * pointer stays valid until the next dsm_lut_upload for the same (ctx, column). */
@@ -401,6 +412,13 @@ int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_row
                          double* d_out);
 
 /* ---- utilities ------------------------------------------------------------------------ */
+
+/* Size the context's scratch for batches of up to n_jobs jobs with this layout against this
+ * table (k = 0: bitmap calls, else top-k calls up to k), so that later calls of that shape find
+ * their buffers in place: the entry points otherwise grow scratch on first use with cudaFree +
+ * cudaMalloc, a device-wide synchronisation a scheduler does not want on its hot path.  The
+ * id array of raw-job calls is sized on use. */
+int dsm_reserve(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout, uint32_t n_jobs, uint32_t k);
 
 int dsm_sync(dsm_ctx* ctx);
 /* Pinned host memory for record / result buffers of the host-buffer entry points. */

@@ -98,7 +98,22 @@ def match_matrix(oc: OfferColumns, jc: JobColumns) -> np.ndarray:
     total = np.where((gcount > 0) & ~np.isnan(gmem), gcount.astype(np.float64) * np.nan_to_num(gmem), 0.0)
     ok &= _between(total, jc.gpu_total)                                                # 11
     disk = np.asarray(sh.disk_gib, dtype=np.float64)[sid]
-    ok &= np.isnan(disk)[None, :] | _between(np.nan_to_num(disk), jc.disk)             # 12
+    disk_ok = np.isnan(disk)[None, :] | _between(np.nan_to_num(disk), jc.disk)        # 12
+    if oc.disk_conf_ranges and sh.disk_conf is not None:
+        # an item without a disk size on a backend with configurable disks survives
+        # catalog_item_to_offer only if the job's disk range (DEFAULT_DISK = 100GB.. when it states
+        # none) overlaps the backend's range: core/backends/base/offers.py:63-66, 161-175
+        d = np.asarray(jc.disk, dtype=np.float64)
+        unset = np.isnan(d).all(axis=1)
+        lo = np.where(unset, 100.0, np.where(np.isnan(d[:, 0]), -np.inf, d[:, 0]))
+        hi = np.where(unset, np.inf, np.where(np.isnan(d[:, 1]), np.inf, d[:, 1]))
+        conf = np.asarray(sh.disk_conf, dtype=np.int64)[sid]
+        for ci, (cmin, cmax) in enumerate(oc.disk_conf_ranges):
+            start = np.maximum(lo, -np.inf if np.isnan(cmin) else cmin)
+            end = np.minimum(hi, np.inf if np.isnan(cmax) else cmax)
+            rows = np.isnan(disk) & (conf == ci)
+            disk_ok[:, rows] = ~(start > end)[:, None]
+    ok &= disk_ok
     # backend / region / instance type (server/services/offers.py:81-100)
     src = np.asarray(oc.src_backend, dtype=np.int64)
     off = np.asarray(oc.backend, dtype=np.int64)

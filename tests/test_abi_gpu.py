@@ -118,3 +118,22 @@ def test_any_k(matcher, k):
         dt.close()
     want = columnar.topk(cat.columns, sj.columns, k)
     assert np.array_equal(got.index, want.index) and np.array_equal(got.count, want.count)
+
+
+def test_reserve_sizes_the_scratch_ahead_of_the_first_call(matcher):
+    lib = native.lib()
+    cat, table, packed = _setup(matcher, n_offers=60_000, n_jobs=900, seed=91)
+    m = Matcher(0)  # a fresh context: nothing allocated yet
+    dt = m.upload(table)
+    try:
+        lay = m._layout(packed)
+        native.check(lib.dsm_reserve(m.handle, dt.handle, C.byref(lay), 900, 50))
+        native.check(lib.dsm_reserve(m.handle, dt.handle, C.byref(lay), 900, 0))
+        assert lib.dsm_reserve(m.handle, dt.handle, C.byref(lay), 0, 16) == DSM_E_ARG
+        got = m.topk_rows(dt, packed, 50)
+        want = matcher.topk_rows(matcher.upload(table), packed, 50)
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b)
+    finally:
+        dt.close()
+        m.close()

@@ -114,3 +114,36 @@ def test_index_lists_equal_the_oracle_matrix(matcher, by_source):
             rank = np.empty(len(order), np.int64)
             rank[order] = np.arange(len(order))
             assert np.array_equal(lists[j], hits[np.argsort(rank[hits], kind="stable")])
+
+
+def test_device_records_on_a_pool_table(matcher):
+    """32-byte rows with the state / fleet / zone columns: status masks and flag requirements go to
+    the state column, single fleet ids and zone lists to their bitsets."""
+    from dstack_b200 import pools as PP
+    from dstack_b200.ingest import columns_from_pool_instances, job_columns
+    from workloads import configs
+
+    rows = synth.make_pool(6_000, seed=96, n_fleets=40)
+    table = encode_table(columns_from_pool_instances(rows))
+    dt = matcher.upload(table)
+    try:
+        calls = [c for c in configs.config2_jobs(rows, 1500, seed=97) if c[0].instance_name is None]
+        filters = [PP._pool_filter(p, requirements=kw["requirements"], status=kw["status"], fleet_model=kw.get("fleet_model"),
+                                   multinode=kw.get("multinode", False),
+                                   master_job_provisioning_data=kw.get("master_job_provisioning_data"), volumes=None,
+                                   shared=(i % 5 == 0)) for i, (p, kw) in enumerate(calls)]
+        jc = job_columns(table, filters)
+        raw = raw_jobs(table, jc)
+        assert raw is not None and "state" in [c.name for c in table.columns][:raw[2]["n_used"]]
+        want = pack_jobs(table, jc, n_used=raw[2]["n_used"])
+        assert raw[2]["rec_off"] == want.layout["rec_off"] and raw[2]["kind"] == want.layout["kind"]
+        got, _ = _device_records(matcher, dt, raw)
+        assert np.array_equal(got, want.records)
+        # and the answers through the device-packed path equal the host-packed ones
+        a = matcher.topk_rows_raw(dt, raw, 16)
+        b = matcher.topk_rows(dt, pack_jobs(table, jc), 16)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+        assert a[1].sum() > 1000
+    finally:
+        dt.close()

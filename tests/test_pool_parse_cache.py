@@ -114,3 +114,98 @@ def test_offer_catalog_cache_follows_the_30_s_clock():
     assert c is not b and closed == [a, b]
     cache.close()
     assert closed == [a, b, c]
+
+
+def test_offer_catalog_cache_serves_the_old_table_while_the_new_one_is_built():
+    """Matcher threads must not stall for a rebuild (0.5 s per Mi rows): the thread that notices
+    the expiry builds outside the lock, the others keep the previous catalog until the swap."""
+    import threading
+
+    from dstack_b200.services import OfferCatalogCache
+
+    now = [0.0]
+    gate, started = threading.Event(), threading.Event()
+    built = []
+
+    class SlowCatalog:
+        def __init__(self, offers_by_backend):
+            if built:  # the first build is immediate, the rebuild waits for the test
+                started.set()
+                assert gate.wait(10)
+            built.append(self)
+
+        def close(self):
+            pass
+
+    cache = OfferCatalogCache(lambda: [], ttl=30.0, clock=lambda: now[0], build=SlowCatalog)
+    first = cache.get()
+    now[0] = 31.0
+    result = []
+    t = threading.Thread(target=lambda: result.append(cache.get()))
+    t.start()
+    assert started.wait(10)          # the rebuild is running ...
+    assert cache.get() is first      # ... and other callers are served at once, from the old table
+    gate.set()
+    t.join(10)
+    assert result and result[0] is not first and cache.get() is result[0] and cache.rebuilds == 2
+
+
+def _status_tick(rows, rng, share=0.01):
+    """What a scheduler pass changes on a pool: some idle instances turn busy (and back), one
+    becomes unreachable, one moves to another fleet that the pool already knows."""
+    n = max(4, int(len(rows) * share))
+    changed = sorted(int(i) for i in rng.choice(len(rows), size=n, replace=False))
+    fleets = [r.fleet_id for r in rows if r.fleet_id is not None]
+    for c, i in enumerate(changed):
+        r = rows[i]
+        if c % 4 == 0:
+            r.unreachable = not r.unreachable
+        elif c % 4 == 1:
+            r.fleet_id = fleets[int(rng.integers(0, len(fleets)))]
+        elif r.status == M.InstanceStatus.IDLE:
+            r.status, r.busy_blocks = M.InstanceStatus.BUSY, (r.total_blocks or 1)
+        elif r.status == M.InstanceStatus.BUSY:
+            r.status, r.busy_blocks = M.InstanceStatus.IDLE, 0
+        else:
+            r.status = M.InstanceStatus.IDLE
+    return changed
+
+
+def test_rows_patched_in_place_answer_like_a_rebuilt_table():
+    """status / reachability / fleet changes rewrite the affected rows of the
+    resident table instead of rebuilding it; every job must get the rows a rebuilt table gives."""
+    import device_emulator as emu
+    from dstack_b200 import pools as PP
+    from dstack_b200.encode import encode_table, pack_jobs
+    from dstack_b200.ingest import job_columns
+    from workloads import configs
+
+    rng = np.random.default_rng(7)
+    rows = synth.make_pool(3000, seed=71, n_fleets=10)
+    table = encode_table(columns_from_pool_instances(rows))
+    row_of = np.empty(table.n_src, np.int64)
+    live = table.perm >= 0
+    row_of[table.perm[live]] = np.flatnonzero(live)
+    calls = configs.config2_jobs(rows, 60, seed=72)
+    filters = [PP._pool_filter(p, requirements=kw["requirements"], status=kw["status"], fleet_model=kw.get("fleet_model"),
+                               multinode=kw.get("multinode", False),
+                               master_job_provisioning_data=kw.get("master_job_provisioning_data"), volumes=None,
+                               shared=False) for p, kw in calls]
+    patched_ticks = 0
+    for tick in range(4):
+        changed = _status_tick(rows, rng)
+        got_rows = PP.patch_pool_rows(table, rows, changed, row_of)
+        fresh = encode_table(columns_from_pool_instances(rows))
+        if got_rows is None:  # a combination the dictionaries do not hold: the caller rebuilds
+            table = fresh
+            continue
+        patched_ticks += 1
+        assert len(got_rows) == len(changed)
+        a = emu.match_matrix(table, pack_jobs(table, job_columns(table, filters)))
+        b = emu.match_matrix(fresh, pack_jobs(fresh, job_columns(fresh, filters)))
+        # same source rows for every job (the two tables may number their dictionaries differently)
+        src_a = [np.sort(table.perm[np.flatnonzero(m)]) for m in a]
+        src_b = [np.sort(fresh.perm[np.flatnonzero(m)]) for m in b]
+        assert all(np.array_equal(x, y) for x, y in zip(src_a, src_b))
+        assert sum(len(x) for x in src_a) > 100
+    assert patched_ticks >= 2

@@ -290,3 +290,40 @@ def test_gpu_offer_catalog_equals_oracle(matcher):
         assert sum(bool(w) for w in wants) >= 9
     finally:
         catalog.close()
+
+
+@pytest.mark.gpu
+def test_pool_index_refresh_patches_rows_in_place(matcher):
+    """A scheduler pass changes statuses, reachability and fleets; PoolIndex.refresh rewrites those
+    rows on the device and every job gets what the reference's filter gives on the changed pool."""
+    import test_pool_parse_cache as T
+    from workloads import configs
+
+    rng = np.random.default_rng(11)
+    rows = synth.make_pool(4000, seed=12, n_fleets=8)
+    calls = configs.config2_jobs(rows, 40, seed=13)
+    index = PP.PoolIndex(rows, matcher=matcher)
+    try:
+        for tick in range(3):
+            changed = T._status_tick(rows, rng, share=0.02)
+            assert index.refresh(changed) is True and index.rebuilds == 1
+            filters = [PP._pool_filter(p, requirements=kw["requirements"], status=kw["status"],
+                                       fleet_model=kw.get("fleet_model"), multinode=kw.get("multinode", False),
+                                       master_job_provisioning_data=kw.get("master_job_provisioning_data"),
+                                       volumes=None, shared=False) for p, kw in calls]
+            got = index.match(filters)
+            for j in (0, 1, 2, 3, 4, 5 + tick):
+                want = ref.filter_pool_instances(rows, calls[j][0], **calls[j][1])
+                assert len(want) == len(got[j]) and all(rows[i] is w for i, w in zip(got[j], want)), (tick, j)
+        # an instance moving to a fleet the pool has never seen cannot be patched: rebuilt instead
+        rows[7].fleet_id = uuid.UUID(int=987654321)
+        assert index.refresh([7]) is False and index.rebuilds == 2
+        want = ref.filter_pool_instances(rows, calls[0][0], **calls[0][1])
+        got = index.match([PP._pool_filter(calls[0][0], requirements=calls[0][1]["requirements"],
+                                           status=calls[0][1]["status"], fleet_model=calls[0][1].get("fleet_model"),
+                                           multinode=calls[0][1].get("multinode", False),
+                                           master_job_provisioning_data=calls[0][1].get("master_job_provisioning_data"),
+                                           volumes=None, shared=False)])[0]
+        assert len(want) == len(got) and all(rows[i] is w for i, w in zip(got, want))
+    finally:
+        index.close()
