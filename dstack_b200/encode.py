@@ -452,6 +452,15 @@ def _range_words(vals: np.ndarray, bounds: np.ndarray) -> np.ndarray:
     return lo | (hi << np.uint32(16))
 
 
+def _pack_bool_rows(ok: np.ndarray) -> np.ndarray:
+    """bool [J, card] -> uint32 [J, ceil(card / 32)], bit e of row j = ok[j, e]."""
+    j, card = ok.shape
+    nw = (card + 31) // 32
+    padded = np.zeros((j, nw * 32), dtype=bool)
+    padded[:, :card] = ok
+    return np.packbits(padded, axis=1, bitorder="little").view("<u4").reshape(j, nw)
+
+
 def _bitset_from_csr(any_mask: np.ndarray, ptr: np.ndarray, ids: np.ndarray, n_words: int,
                      pass_bits: Sequence[int] = ()) -> np.ndarray:
     """[J, n_words] uint32 with one bit per accepted code; ``any`` rows are all ones."""
@@ -555,9 +564,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns, n_used: Optional[int] = None) -> 
         ok = (e >= (cpu_w & 0xFFFF)[:, None]) & (e <= (cpu_w >> 16)[:, None])
         vals = cpu_vals.astype(np.int64)[None, :]
         ok &= np.where(blocks[:, None] > 1, vals % np.maximum(blocks, 1)[:, None] == 0, blocks[:, None] == 0)
-        cpu_bits = np.zeros((j, (len(cpu_vals) + 31) // 32), dtype=np.uint32)
-        jj, ee = np.nonzero(ok)
-        np.bitwise_or.at(cpu_bits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
+        cpu_bits = _pack_bool_rows(ok)
     cpu_triv = _range_trivial(cpu_w, len(cpu_vals)) & (blocks == 0)
     mem_triv = _range_trivial(mem_w, len(mem_vals))
     if t.pair_entries is not None:
@@ -587,10 +594,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns, n_used: Optional[int] = None) -> 
             end = hi if np.isnan(cmax) else np.minimum(hi, cmax)
             ok[:, nv + ci] = ~(start > end)
         ok[:, dcol.card - 1] = True
-        bits = np.zeros((j, (dcol.card + 31) // 32), dtype=np.uint32)
-        jj, ee = np.nonzero(ok)
-        np.bitwise_or.at(bits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
-        put("disk", bits, KIND_BITSET, dcol.card, ok.all(axis=1))
+        put("disk", _pack_bool_rows(ok), KIND_BITSET, dcol.card, ok.all(axis=1))
 
     # accelerator sub-predicate
     gd = t.gpu_dict
@@ -633,10 +637,7 @@ def pack_jobs(t: EncodedTable, jc: JobColumns, n_used: Optional[int] = None) -> 
         e = np.arange((NO_STATUS_CODE + 1) * 16, dtype=np.uint32)[None, :]
         dyn_req, dyn_forbid = (req & DYNAMIC_FLAGS)[:, None], (forbid & DYNAMIC_FLAGS)[:, None]
         ok = (((st_mask[:, None] >> (e >> 4)) & 1) != 0) & (((e & 15) & dyn_req) == dyn_req) & (((e & 15) & dyn_forbid) == 0)
-        sbits = np.zeros((j, ok.shape[1] // 32 + (ok.shape[1] % 32 != 0)), dtype=np.uint32)
-        jj, ee = np.nonzero(ok)
-        np.bitwise_or.at(sbits, (jj, ee >> 5), np.uint32(1) << (ee & 31).astype(np.uint32))
-        put("state", sbits, KIND_BITSET, ok.shape[1], ok.all(axis=1))
+        put("state", _pack_bool_rows(ok), KIND_BITSET, ok.shape[1], ok.all(axis=1))
         st_mask = np.full(j, 0xFF, dtype=np.uint32)
         req, forbid = req & ~np.uint32(DYNAMIC_FLAGS), forbid & ~np.uint32(DYNAMIC_FLAGS)
     bwords = np.stack([src_m, off_m, spot_mask | (st_mask << np.uint32(8)), req | (forbid << np.uint32(16))], axis=1)

@@ -134,9 +134,9 @@ class Matcher:
             total = int(ptr[j])
             if total:
                 buf = (C.c_uint32 * total).from_address(out.value)
-                ids = np.frombuffer(buf, dtype=np.uint32).astype(np.int64)  # copy: the buffer is the context's
+                ids = np.frombuffer(buf, dtype=np.int32).copy()  # copy: the buffer is the context's
             else:
-                ids = np.zeros(0, np.int64)
+                ids = np.zeros(0, np.int32)
         return np.split(ids, ptr[1:-1].astype(np.int64))
 
     def bitmap_rows(self, dt: "DeviceTable", packed: PackedJobs) -> np.ndarray:

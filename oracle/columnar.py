@@ -22,7 +22,7 @@ from typing import Dict, Optional
 
 import numpy as np
 
-from dstack_b200._gpuhunt import compute_capability_of
+from .gpuhunt_restated import compute_capability_of  # the oracle's own table
 from dstack_b200.encode import BACKEND_CODES, FLAG_AUTO_DIVISIBLE, JobColumns, OfferColumns
 
 

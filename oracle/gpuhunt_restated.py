@@ -16,7 +16,58 @@ from __future__ import annotations
 import heapq
 from typing import Dict, Iterable, List, Optional, Sequence
 
-from dstack_b200._gpuhunt import CatalogItem, QueryFilter, compute_capability_of
+from dstack_b200._gpuhunt import CatalogItem, QueryFilter  # plain dataclasses: field names only
+
+# Compute capability by GPU name -- the oracle's OWN table, typed from NVIDIA's public list
+# ("CUDA GPUs - Compute Capability", developer.nvidia.com/cuda-gpus; architecture in the comment),
+# so that a wrong entry in the product's table (dstack_b200/_gpuhunt.py) shows up as a parity
+# failure instead of being shared by both sides.  tests/test_oracle_known_answers.py compares the two.
+COMPUTE_CAPABILITY = {
+    # Kepler / Maxwell
+    "K80": (3, 7),         # Tesla K80, GK210
+    "M60": (5, 2),         # Tesla M60, GM204
+    # Pascal
+    "P100": (6, 0),        # Tesla P100, GP100
+    "P4": (6, 1),          # Tesla P4, GP104
+    "P40": (6, 1),         # Tesla P40, GP102
+    # Volta
+    "V100": (7, 0),        # Tesla V100, GV100
+    # Turing
+    "T4": (7, 5),          # Tesla T4, TU104
+    "RTX6000": (7, 5),     # Quadro RTX 6000, TU102
+    "RTX8000": (7, 5),     # Quadro RTX 8000, TU102
+    # Ampere
+    "A100": (8, 0),        # GA100
+    "A30": (8, 0),         # GA100
+    "A2": (8, 6),          # GA107
+    "A10": (8, 6),         # GA102
+    "A10G": (8, 6),        # GA102 (AWS G5)
+    "A16": (8, 6),         # GA107 x4
+    "A40": (8, 6),         # GA102
+    "A4000": (8, 6),       # RTX A4000, GA104
+    "A4500": (8, 6),       # RTX A4500, GA102
+    "A5000": (8, 6),       # RTX A5000, GA102
+    "A6000": (8, 6),       # RTX A6000, GA102
+    "RTX3060": (8, 6), "RTX3070": (8, 6), "RTX3080": (8, 6), "RTX3090": (8, 6),  # GeForce RTX 30, GA10x
+    # Ada Lovelace
+    "L4": (8, 9),          # AD104
+    "L40": (8, 9),         # AD102
+    "L40S": (8, 9),        # AD102
+    "RTX2000Ada": (8, 9), "RTX4000Ada": (8, 9), "RTX5000Ada": (8, 9), "RTX6000Ada": (8, 9),  # RTX Ada generation
+    "RTX4070": (8, 9), "RTX4080": (8, 9), "RTX4090": (8, 9),                                  # GeForce RTX 40, AD10x
+    # Hopper
+    "H100": (9, 0),        # GH100
+    "H100NVL": (9, 0),     # GH100
+    "H200": (9, 0),        # GH100 + HBM3e
+    # Blackwell
+    "B200": (10, 0),       # GB100
+}
+_CC_LOWER = {name.lower(): cc for name, cc in COMPUTE_CAPABILITY.items()}
+
+
+def compute_capability_of(gpu_name: Optional[str]):
+    """Case-insensitive; ``None`` for a name the table does not hold."""
+    return None if gpu_name is None else _CC_LOWER.get(gpu_name.lower())
 
 
 def _within(value, low, high) -> bool:
@@ -57,13 +108,19 @@ def matches(item: CatalogItem, q: QueryFilter) -> bool:
             return False
         if item.gpu_name.lower() not in {n.lower() for n in q.gpu_name}:
             return False
-    # 9. per-GPU memory: any bound needs at least one GPU
+    # 9. per-GPU memory: any bound -- a maximum alone too -- needs at least one GPU.  Reading
+    # assumed (unpinned): upstream returns False for gpu_count == 0 before comparing; the other
+    # reading (compare gpu_memory = 0 / None with the bounds) would let a CPU-only item pass
+    # "memory ..16GB, count 0..".  Call-site evidence: offers.py:128-136 only sets these bounds
+    # inside `if res.gpu:`, i.e. for jobs that speak about GPUs at all.
     if q.min_gpu_memory is not None or q.max_gpu_memory is not None:
         if item.gpu_count <= 0 or item.gpu_memory is None:
             return False
         if not _within(item.gpu_memory, q.min_gpu_memory, q.max_gpu_memory):
             return False
-    # 10. compute capability: unknown capability fails a bound
+    # 10. compute capability: an unknown capability -- which includes an item without any GPU
+    # (gpu_name None) -- fails a bound.  Reading assumed (unpinned): the test is not skipped for
+    # gpu_count == 0; dstack only sets the bound together with a GPU spec (offers.py:143-144).
     if q.min_compute_capability is not None or q.max_compute_capability is not None:
         cc = compute_capability_of(item.gpu_name)
         if cc is None:

@@ -87,6 +87,24 @@ CASES = [
     ("cc minor compare", req(gpu={"compute_capability": "8.6"}), offer(gpus=1, gpu="L4", gpu_gib=24), True),
     ("cc unknown gpu fails", req(gpu={"compute_capability": "7.0"}), offer(gpus=1, gpu="GH200", gpu_gib=96), False),
     ("cc vs cpu offer", req(gpu={"compute_capability": "7.0", "count": "0.."}), offer(gpus=0), False),
+    # ---- gpu_count == 0 against jobs whose count range includes 0 (`gpu: 0..2` style).  gpuhunt is
+    # absent here, so each row states the READING of upstream `matches` it assumes (all unpinned,
+    # SURVEY App. A.1 / B) and the call-site evidence for it (core/backends/base/offers.py:128-144:
+    # every one of these bounds is only ever set inside `if res.gpu:`).
+    # reading: any per-GPU memory bound, a maximum alone too, requires gpu_count > 0
+    ("max gpu mem only, no gpu", req(gpu={"memory": "..16GB", "count": "0.."}), offer(gpus=0), False),
+    ("max gpu mem only, small gpu", req(gpu={"memory": "..16GB", "count": "0.."}), offer(gpus=1, gpu="T4", gpu_gib=16), True),
+    # reading: total memory of an item without GPUs is 0, compared like any other value
+    ("max total only, no gpu", req(gpu={"total_memory": "..100GB", "count": "0.."}), offer(gpus=0), True),
+    ("min total only, no gpu", req(gpu={"total_memory": "1GB..", "count": "0.."}), offer(gpus=0), False),
+    # reading: a vendor filter needs the item to name that vendor; an item without GPUs names none
+    ("vendor set, no gpu", req(gpu={"vendor": "amd", "count": "0.."}), offer(gpus=0), False),
+    # reading: a name filter needs the item to name a GPU
+    ("name set, no gpu", req(gpu={"name": ["A100"], "count": "0.."}), offer(gpus=0), False),
+    # reading: the compute-capability test is NOT skipped for items without GPUs (unknown capability fails)
+    ("min cc, no gpu, count 0..0", req(gpu={"compute_capability": "3.5", "count": "0..0"}), offer(gpus=0), False),
+    # and the count range itself still admits the CPU-only item when nothing else is asked
+    ("count 0.. alone, no gpu", req(gpu={"count": "0.."}), offer(gpus=0), True),
 ]
 
 
@@ -106,3 +124,17 @@ def test_gpu_known_answers(matcher):
         assert (any(x is o for x in kept)) is expected, name
     assert P.match_requirements([], CASES[0][1], matcher=matcher) == []
     assert P.match_requirements(offers, None, matcher=matcher) == offers
+
+
+def test_oracle_and_product_compute_capability_tables_agree():
+    """The oracle carries its own table (typed from NVIDIA's public list); an entry that is wrong
+    on one side only would otherwise be invisible to every parity test."""
+    from dstack_b200 import _gpuhunt
+    from oracle import gpuhunt_restated as G
+
+    names = {g.name for g in _gpuhunt.KNOWN_NVIDIA_GPUS} | set(G.COMPUTE_CAPABILITY)
+    assert len(names) >= 35
+    for name in sorted(names):
+        assert G.compute_capability_of(name) == _gpuhunt.compute_capability_of(name), name
+        assert G.compute_capability_of(name.lower()) == G.compute_capability_of(name.upper())
+    assert G.compute_capability_of("GH200") is None and G.compute_capability_of(None) is None
