@@ -355,20 +355,22 @@ int dsm_match_bitmap_dev(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* lay
  *     allocator, a fixed MIG slice), where a fresh allocation can be refused.
  * Same arguments and same result as dsm_match_bitmap_dev: d_jobs (records) and d_bits (output,
  * n_jobs * n_rows/32 words) are the caller's device buffers.  The scratch the other entry
- * points allocate -- the acceptance tables and the work counter -- lives in a fixed array of
- * DSM_STATIC_SCRATCH_BYTES inside the library's device image, so every GPU that loads the
- * library holds that much until the process exits.  No cudaMalloc, cudaFree or other
- * allocating call is made.
- *   Limit: 256 + ceil(n_jobs/128) * (sum of layout.card) * 16 bytes must fit in the array
- *   (e.g. 465 dictionary entries -> up to ~36,000 jobs per call); larger requests fail with
+ * points allocate -- the acceptance tables, one word per job group (the columns the group
+ * needs) and the work counter -- lives in a fixed array of DSM_STATIC_SCRATCH_BYTES inside the
+ * library's device image, so every GPU that loads the library holds that much until the
+ * process exits.  No cudaMalloc, cudaFree or other allocating call is made.  layout.job_order,
+ * if used, is a device array like d_jobs.
+ *   Limit: with g = ceil(n_jobs/128) job groups, 256 + (4 g rounded up to 256) +
+ *   g * (sum of layout.card) * 16 bytes must fit in the array (e.g. 562 dictionary entries ->
+ *   up to ~29,000 jobs per call); larger requests fail with
  *   DSM_E_TOO_LARGE and a message saying how much was needed.  A layout that uses lut[] needs
  *   its dsm_lut_upload done beforehand (that call does allocate).
  *   First call on a GPU: the array's device address is looked up once per device
  *   (cudaGetSymbolAddress, with that device current); make that first call before starting any
  *   stream capture.
  *   Sharing: all calls on a GPU use the one array and it keeps the previous call's contents.
- *   Everything that has to start from zero (the work counter) is reset by the call itself and
- *   the tables are rewritten for every job group used, but two calls whose kernels overlap on
+ *   Everything that has to start from zero (the work counter) is reset by the call itself, the
+ *   tables and the per-group words are rewritten for every job group used, but two calls whose kernels overlap on
  *   the same GPU -- different contexts, streams or threads -- race on it: serialise them. */
 #define DSM_STATIC_SCRATCH_BYTES (2u << 20)
 int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* layout,
