@@ -29,6 +29,7 @@ def get(metric, scale_to_bytes=False):
     return v
 
 
+n_sm = int(get("device__attribute_multiprocessor_count")) if "device__attribute_multiprocessor_count" in head else 148
 path = os.path.join(ROOT, "profiles", "k_match_traffic.json")
 doc = json.load(open(path)) if os.path.exists(path) else {}
 sha = hashlib.sha256(open(os.path.join(ROOT, "dstack_b200", "csrc", "kernels.cuh"), "rb").read()).hexdigest()[:16]
@@ -41,7 +42,9 @@ doc[name] = {
     "dram_read_bytes": int(get("dram__bytes_read.sum", True)),
     "dram_write_bytes": int(get("dram__bytes_write.sum", True)),
     "warp_instructions": int(get("smsp__inst_executed.sum")),
-    "lsu_wavefronts": int(get("l1tex__data_pipe_lsu_wavefronts.sum")),
+    # LSU data-pipe wavefronts of all kinds (shared + global + local): ncu's triage section has the
+    # per-SM average
+    "lsu_wavefronts": int(get("SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts.avg") * n_sm),
     "shared_wavefronts": int(get("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum")),
     "duration_us_under_ncu": get("gpu__time_duration.sum"),
     "lsu_pipe_pct": get("l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed"),
