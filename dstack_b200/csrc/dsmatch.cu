@@ -275,26 +275,33 @@ static dim3 build_grid(const Plan& pl) {
   return dim3(pl.n_groups * TPG, pl.lay.n_used, (longest + BUILD_CHUNK - 1) / BUILD_CHUNK);
 }
 
-template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT>
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST>
 static cudaError_t launch_match_v(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(k_match<NCMAX, ROW32, MODE, HAS_LUT>,
+  cudaError_t e = cudaFuncSetAttribute(k_match<NCMAX, ROW32, MODE, HAS_LUT, EVFAST>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  k_match<NCMAX, ROW32, MODE, HAS_LUT><<<grid, MATCH_THREADS, smem, st>>>(mp);
+  k_match<NCMAX, ROW32, MODE, HAS_LUT, EVFAST><<<grid, MATCH_THREADS, smem, st>>>(mp);
   return cudaGetLastError();
 }
 
+// evfast: see k_match; only 16-byte rows in count mode have the unrolled windows it concerns
 template <int MODE>
-static cudaError_t launch_match(bool row32, const MatchParams& mp, bool has_lut, uint32_t grid, uint32_t smem,
-                                cudaStream_t st) {
+static cudaError_t launch_match(bool row32, const MatchParams& mp, bool has_lut, bool evfast, uint32_t grid,
+                                uint32_t smem, cudaStream_t st) {
+  if (MODE != MODE_COUNT || row32) evfast = false;
 #ifdef DSM_FAST_BUILD  // experiments: only the shape the benchmark uses
   if (row32 || has_lut) return cudaErrorInvalidValue;
-  return launch_match_v<8, false, MODE, false>(mp, grid, smem, st);
+  return evfast ? launch_match_v<8, false, MODE, false, true>(mp, grid, smem, st)
+                : launch_match_v<8, false, MODE, false, false>(mp, grid, smem, st);
 #else
-  if (!row32) return has_lut ? launch_match_v<8, false, MODE, true>(mp, grid, smem, st)
-                             : launch_match_v<8, false, MODE, false>(mp, grid, smem, st);
-  return has_lut ? launch_match_v<16, true, MODE, true>(mp, grid, smem, st)
-                 : launch_match_v<16, true, MODE, false>(mp, grid, smem, st);
+  if (!row32) {
+    if (evfast) return has_lut ? launch_match_v<8, false, MODE, true, true>(mp, grid, smem, st)
+                               : launch_match_v<8, false, MODE, false, true>(mp, grid, smem, st);
+    return has_lut ? launch_match_v<8, false, MODE, true, false>(mp, grid, smem, st)
+                   : launch_match_v<8, false, MODE, false, false>(mp, grid, smem, st);
+  }
+  return has_lut ? launch_match_v<16, true, MODE, true, false>(mp, grid, smem, st)
+                 : launch_match_v<16, true, MODE, false, false>(mp, grid, smem, st);
 #endif
 }
 
@@ -398,8 +405,12 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
   ctx->launches++;
   if (tev) CK(cudaEventRecord(tev->e[1], ctx->stream));
 
-  cudaError_t e = bitmap ? launch_match<MODE_BITMAP>(row32, mp, has_lut, pl.grid, pl.smem, ctx->stream)
-                         : launch_match<MODE_COUNT>(row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  // windows with a cut-off inside: up to 2 x 128 cut-offs per job group over the table's windows
+  const unsigned long long n_win_all = (unsigned long long)Pieces::windows(pl.split_block) +
+                                       Pieces::windows(pl.n_blocks - pl.split_block);
+  const bool evfast = 2ull * JPG * 20ull > n_win_all;  // more than ~5 % of the windows
+  cudaError_t e = bitmap ? launch_match<MODE_BITMAP>(row32, mp, has_lut, false, pl.grid, pl.smem, ctx->stream)
+                         : launch_match<MODE_COUNT>(row32, mp, has_lut, evfast, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   if (tev) CK(cudaEventRecord(tev->e[2], ctx->stream));
   ctx->launches++;
@@ -1282,7 +1293,7 @@ int dsm_match_bitmap_static(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* 
   k_build_tables<<<build_grid(pl), 256, 0, ctx->stream>>>(bp);
   CK(cudaGetLastError());
   ctx->launches++;
-  cudaError_t e = launch_match<MODE_BITMAP>(row32, mp, has_lut, pl.grid, pl.smem, ctx->stream);
+  cudaError_t e = launch_match<MODE_BITMAP>(row32, mp, has_lut, false, pl.grid, pl.smem, ctx->stream);
   if (e != cudaSuccess) return fail(DSM_E_CUDA, "k_match launch: %s", cudaGetErrorString(e));
   ctx->launches++;
   return 0;

@@ -369,9 +369,49 @@ struct IntC {
 
 __device__ __forceinline__ uint32_t maj3(uint32_t a, uint32_t b, uint32_t c) { return (a & b) | (c & (a | b)); }
 
+// Cut-off classification of one block for the 128 jobs of a group (lane j of tile t holds job
+// 32t+j's cut-off row in cut_lane[32 t]): full = jobs whose cut-off lies behind the block (they
+// pass on all its rows, and on the following blocks up to `next_evt`), pw = per row lane, the jobs
+// whose cut-off falls inside the block and lies behind this lane's row.  Out of line on purpose:
+// it runs once per cut-off, but is reachable from every block of the unrolled windows.
+struct BlockClass {
+  uint32_t full[TPG];
+  uint32_t pw[TPG];
+  uint32_t next_evt;
+  uint32_t any_part;
+};
+__device__ __noinline__ BlockClass classify_block(const uint32_t* cut_lane, uint32_t blk, uint32_t lane) {
+  constexpr uint32_t FULL = 0xFFFFFFFFu;
+  BlockClass r;
+  const uint32_t row = blk * 32u + lane;
+  const uint32_t row_end = (blk + 1u) * 32u;
+  uint32_t nxt = 0xFFFFFFFFu;
+  r.any_part = 0;
+#pragma unroll
+  for (int t = 0; t < TPG; ++t) {
+    const uint32_t cutv = cut_lane[t * 32];
+    r.full[t] = __ballot_sync(FULL, cutv >= row_end);
+    uint32_t part = __ballot_sync(FULL, cutv > blk * 32u && cutv < row_end);
+    r.any_part |= part;
+    r.pw[t] = 0;
+    while (part) {
+      const uint32_t j = __ffs(part) - 1;
+      part &= part - 1;
+      r.pw[t] |= (row < __shfl_sync(FULL, cutv, j)) ? (1u << j) : 0u;
+    }
+    if (cutv >= row_end) nxt = min(nxt, cutv >> 5);  // block where this job leaves `full`
+  }
+  r.next_evt = __reduce_min_sync(FULL, nxt);
+  return r;
+}
+
 // NCMAX = 8 (16-byte rows) or 16 (32-byte rows); the number of columns a call uses and the number
 // a job group needs are run-time values (p.n_used, n_act).
-template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT>
+// EVFAST (count mode): the unrolled windows also take windows with a cut-off inside (a per-block
+// test and an out-of-line call) instead of leaving them to the generic path.  Pays when such
+// windows are frequent (few rows per job group: config 3, 0.141 against 0.145 ms) and costs when
+// they are rare (8 M rows x 128 groups: 3.88 against 3.66 ms); the host picks per call.
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
   static_assert(MODE == MODE_BITMAP || MODE == MODE_COUNT, "unknown k_match mode");
   constexpr bool COUNT = MODE == MODE_COUNT;
@@ -516,26 +556,11 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     // classify block `blk`: full[] for it and the blocks after it, the rows of jobs whose cut-off
     // lies inside it (pw), and the next block at which a job leaves full[]
     auto classify = [&](const uint32_t blk, uint32_t (&pw)[TPG]) -> bool {
-      const uint32_t row = blk * 32u + lane;
-      const uint32_t row_end = (blk + 1u) * 32u;
-      uint32_t nxt = 0xFFFFFFFFu;
-      uint32_t any_part = 0;
+      const BlockClass bc = classify_block(cut_lane, blk, lane);
 #pragma unroll
-      for (int t = 0; t < TPG; ++t) {
-        const uint32_t cutv = cut_lane[t * 32];  // lane j: cut-off row of job 32t+j
-        full[t] = __ballot_sync(FULL, cutv >= row_end);
-        uint32_t part = __ballot_sync(FULL, cutv > blk * 32u && cutv < row_end);
-        any_part |= part;
-        pw[t] = 0;
-        while (part) {
-          const uint32_t j = __ffs(part) - 1;
-          part &= part - 1;
-          pw[t] |= (row < __shfl_sync(FULL, cutv, j)) ? (1u << j) : 0u;
-        }
-        if (cutv >= row_end) nxt = min(nxt, cutv >> 5);  // block where this job leaves `full`
-      }
-      next_evt = __reduce_min_sync(FULL, nxt);
-      return any_part != 0;
+      for (int t = 0; t < TPG; ++t) { full[t] = bc.full[t]; pw[t] = bc.pw[t]; }
+      next_evt = bc.next_evt;
+      return bc.any_part != 0;
     };
     auto block_mask = [&](const uint32_t blk) -> uint4 {
       if (blk == next_evt) {  // warp-uniform, once per cut-off inside this warp's rows
@@ -591,7 +616,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
     if constexpr (COUNT) {
       uint32_t cnt[TPG] = {0, 0, 0, 0};  // per job (lane j, tile t): matches in this slot
       uint32_t blk = b0, widx = 0;
-      if (b0 < b1) {
+      if (!EVFAST && b0 < b1) {
         uint32_t pw[TPG];
         if (classify(b0, pw)) next_evt = b0;  // a cut-off inside the first block: take the generic path
       }
@@ -613,10 +638,10 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
         uint32_t P[TPG][WIN_PLANES];  // bit b of the number of matches per (row lane, job) in this window
         bool fast_done = false;
         if constexpr (!ROW32) {
-          if (nb == WIN_BLOCKS && next_evt >= blk + WIN_BLOCKS) {
-            // ---- the usual window: no cut-off inside, so full[] is constant; the 15 blocks are
-            // unrolled and their match words summed with a carry-save adder tree (11 full adders
-            // per tile and window instead of a ripple-carry add per block)
+          if (nb == WIN_BLOCKS && (EVFAST || next_evt >= blk + WIN_BLOCKS)) {
+            // ---- a whole window: the 15 blocks are unrolled and their match words summed with a
+            // carry-save adder tree (11 full adders per tile and window instead of a ripple-carry
+            // add per block).  full[] only changes at a block a cut-off falls into (next_evt)
             auto window = [&](auto na_tag) {
               constexpr int NA = decltype(na_tag)::value;
               uint32_t s1[TPG], p1[TPG], s2[TPG], p2[TPG], d1[TPG], d2[TPG];
@@ -625,7 +650,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
                 const RowCodes<NCMAX>& cur = (i % 3 == 0) ? ra : (i % 3 == 1) ? rb : rc;
                 RowCodes<NCMAX>& nxt = (i % 3 == 0) ? rc : (i % 3 == 1) ? ra : rb;  // block i + 2
                 if (blk + i + 2 < b1) load_row<NCMAX, ROW32>(rp + (size_t)(i + 2) * 32u * ROW_U4, nxt);
-                uint4 m = make_uint4(full[0], full[1], full[2], full[3]);
+                uint4 m = EVFAST ? block_mask(blk + i) : make_uint4(full[0], full[1], full[2], full[3]);
 #pragma unroll
                 for (int c = 0; c < NA; ++c) {
                   uint32_t code = (c & 1) ? (cur.w[c >> 1] >> 16) : (cur.w[c >> 1] & 0xFFFFu);
@@ -680,8 +705,8 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
           }
         }
         if (!fast_done) {
-          // ---- a window with a cut-off inside, the short last window of a segment, or 32-byte
-          // rows: block by block, ripple-carry add into the counter planes
+          // ---- the short last window of a segment, or 32-byte rows: block by block, ripple-carry
+          // add into the counter planes
 #pragma unroll
           for (int t = 0; t < TPG; ++t)
 #pragma unroll
