@@ -595,9 +595,10 @@ def topk_line(args, r, world):
     if r["api_s"]:
         out["e2e_api"] = {"value": evals / statistics.mean(r["api_s"]), "unit": UNIT,
                           "p50_batch_latency_ms": 1e3 * statistics.median(r["api_s"]),
-                          "host_pack_ms": r["pack_ms"],
-                          "path": "Matcher.match_topk(JobColumns) -> TopK: record packing (numpy, host), "
-                                  "dsm_match_topk, rows -> source positions"}
+                          "path": "Matcher.match_topk(JobColumns) -> TopK through dsm_match_topk_cols: job columns in, "
+                                  "records + evaluation order built on the device, source positions / counts / "
+                                  "max prices out",
+                          "host_numpy_pack_ms_for_comparison": r["pack_ms"]}
     return out
 
 

@@ -150,7 +150,9 @@ static int ensure(DevBuf& b, size_t bytes) {
 struct Plan {
   LayoutDev lay;
   Pieces pc;
-  uint32_t n_groups, n_blocks, split_block, slots, smem, rep_shift, direct_fill, grid, wps, dead_entry;
+  uint32_t n_groups, n_blocks, split_block, slots, smem, grid, wps, dead_entry;
+  uint32_t col_off[DSM_MAX_COLS], col_shift[DSM_MAX_COLS], tab_bytes, stage;  // see MatchParams
+  uint32_t rep_shift, big_col, big_shift;
 };
 
 // Words of a record a column's predicate occupies.
@@ -202,28 +204,50 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     base += L->card[c];
   }
   d.n_entries = base;
-  // Replicate the table in shared memory when it fits: 8 copies make the gathers bank-conflict
-  // free (2 and 4 copies measured slower than one).  Prefer keeping MATCH_CTAS_PER_SM CTAs resident.
+  // Shared-memory layout of a group's tables.  Eight copies of an entry make its gathers bank-
+  // conflict free; every column gets eight while MATCH_CTAS_PER_SM CTAs' tables fit in an SM,
+  // otherwise the copies of the column with the largest area are halved until they do (a table
+  // of 312 regions gathered from 4 copies costs about 7 wavefronts instead of 4 when it is
+  // gathered at all, which buys the room to pair cpu with memory: one gather less on every row).
   const uint32_t cuts = 2u * JPG * 4u;
   if (base * 16u + cuts > MAX_SMEM_BYTES)
     return fail(DSM_E_DICT_TOO_LARGE, "acceptance tables need more shared memory than one CTA has");
-  pl.rep_shift = 0;
-  if (base * 16u * 9u + cuts <= MAX_SMEM_BYTES / MATCH_CTAS_PER_SM) pl.rep_shift = 3;
-  if (ctx->force_rep >= 0) pl.rep_shift = ctx->force_rep >= 3 ? 3u : 0u;
-  pl.smem = base * 16u * (pl.rep_shift ? 9u : 1u) + cuts;
-  if (pl.smem > MAX_SMEM_BYTES) { pl.rep_shift = 0; pl.smem = base * 16u + cuts; }
-  // Eight copies fit beside MATCH_CTAS_PER_SM CTAs but a ninth (the TMA staging copy) does not:
-  // keep the eight and let the threads fill them from global memory.
-  pl.direct_fill = 0;
-  if (pl.rep_shift == 0 && ctx->force_rep < 0 && !ctx->no_direct &&
-      MATCH_CTAS_PER_SM * (base * 128u + cuts + 1024u) <= 220u * 1024u) {
-    pl.rep_shift = 3;
-    pl.direct_fill = 1;
-    pl.smem = base * 128u + cuts;
-  } else if (pl.rep_shift == 3 && ctx->force_direct) {
-    pl.direct_fill = 1;
-    pl.smem = base * 128u + cuts;
+  const uint32_t budget = 220u * 1024u / MATCH_CTAS_PER_SM - 1024u - cuts;  // table area of one of 3 CTAs
+  // every column 8 copies; if that does not fit, the largest column 4, 2 or 1; if not even that,
+  // one copy of everything
+  uint32_t big = 0;
+  for (uint32_t c = 1; c < L->n_used; ++c) if (L->card[c] > L->card[big]) big = c;
+  auto area_with = [&](uint32_t rep, uint32_t bshift) {
+    uint32_t a = 0;
+    for (uint32_t c = 0; c < L->n_used; ++c) {
+      const uint32_t bytes = (L->card[c] * 16u) << (c == big ? bshift : rep);
+      a += (bytes + 127u) / 128u * 128u;  // column areas start on a 128-byte boundary
+    }
+    return a;
+  };
+  pl.rep_shift = 3;
+  pl.big_shift = 3;
+  if (ctx->force_rep >= 0) {
+    pl.rep_shift = pl.big_shift = ctx->force_rep >= 3 ? 3u : 0u;
+  } else {
+    while (pl.big_shift > 0 && area_with(3, pl.big_shift) > budget) --pl.big_shift;
+    if (area_with(3, pl.big_shift) > budget) pl.rep_shift = pl.big_shift = 0;
   }
+  pl.big_col = pl.big_shift < pl.rep_shift ? big : 0xFFFFFFFFu;
+  bool single = pl.rep_shift == 0;
+  uint32_t off = 0;
+  for (uint32_t c = 0; c < L->n_used; ++c) {
+    pl.col_off[c] = off;
+    pl.col_shift[c] = c == pl.big_col ? pl.big_shift : pl.rep_shift;
+    const uint32_t bytes = (L->card[c] * 16u) << pl.col_shift[c];
+    off += single ? bytes : (bytes + 127u) / 128u * 128u;
+  }
+  pl.tab_bytes = off;
+  // TMA into a staging copy when there is room for one beside the table area (or straight in
+  // place when the area is one copy of everything), else the threads read from global memory
+  pl.stage = single ? 1u : ((pl.tab_bytes + base * 16u <= budget && !ctx->force_direct) || ctx->no_direct ? 1u : 0u);
+  pl.smem = pl.tab_bytes + ((pl.stage && !single) ? base * 16u : 0u) + cuts;
+  if (pl.smem > MAX_SMEM_BYTES) return fail(DSM_E_DICT_TOO_LARGE, "acceptance tables need more shared memory than one CTA has");
   pl.n_groups = (n_jobs + JPG - 1) / JPG;
   pl.n_blocks = t->desc.n_rows / 32u;
   pl.split_block = t->desc.split_row / 32u;
@@ -275,13 +299,19 @@ static dim3 build_grid(const Plan& pl) {
   return dim3(pl.n_groups * TPG, pl.lay.n_used, (longest + BUILD_CHUNK - 1) / BUILD_CHUNK);
 }
 
-template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST>
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST, bool MIXED>
 static cudaError_t launch_match_v(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
-  cudaError_t e = cudaFuncSetAttribute(k_match<NCMAX, ROW32, MODE, HAS_LUT, EVFAST>,
+  cudaError_t e = cudaFuncSetAttribute(k_match<NCMAX, ROW32, MODE, HAS_LUT, EVFAST, MIXED>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  k_match<NCMAX, ROW32, MODE, HAS_LUT, EVFAST><<<grid, MATCH_THREADS, smem, st>>>(mp);
+  k_match<NCMAX, ROW32, MODE, HAS_LUT, EVFAST, MIXED><<<grid, MATCH_THREADS, smem, st>>>(mp);
   return cudaGetLastError();
+}
+
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST>
+static cudaError_t launch_match_m(const MatchParams& mp, uint32_t grid, uint32_t smem, cudaStream_t st) {
+  return mp.big_col != 0xFFFFFFFFu ? launch_match_v<NCMAX, ROW32, MODE, HAS_LUT, EVFAST, true>(mp, grid, smem, st)
+                                   : launch_match_v<NCMAX, ROW32, MODE, HAS_LUT, EVFAST, false>(mp, grid, smem, st);
 }
 
 // evfast: see k_match; only 16-byte rows in count mode have the unrolled windows it concerns
@@ -291,17 +321,17 @@ static cudaError_t launch_match(bool row32, const MatchParams& mp, bool has_lut,
   if (MODE != MODE_COUNT || row32) evfast = false;
 #ifdef DSM_FAST_BUILD  // experiments: only the shape the benchmark uses
   if (row32 || has_lut) return cudaErrorInvalidValue;
-  return evfast ? launch_match_v<8, false, MODE, false, true>(mp, grid, smem, st)
-                : launch_match_v<8, false, MODE, false, false>(mp, grid, smem, st);
+  return evfast ? launch_match_m<8, false, MODE, false, true>(mp, grid, smem, st)
+                : launch_match_m<8, false, MODE, false, false>(mp, grid, smem, st);
 #else
   if (!row32) {
-    if (evfast) return has_lut ? launch_match_v<8, false, MODE, true, true>(mp, grid, smem, st)
-                               : launch_match_v<8, false, MODE, false, true>(mp, grid, smem, st);
-    return has_lut ? launch_match_v<8, false, MODE, true, false>(mp, grid, smem, st)
-                   : launch_match_v<8, false, MODE, false, false>(mp, grid, smem, st);
+    if (evfast) return has_lut ? launch_match_m<8, false, MODE, true, true>(mp, grid, smem, st)
+                               : launch_match_m<8, false, MODE, false, true>(mp, grid, smem, st);
+    return has_lut ? launch_match_m<8, false, MODE, true, false>(mp, grid, smem, st)
+                   : launch_match_m<8, false, MODE, false, false>(mp, grid, smem, st);
   }
-  return has_lut ? launch_match_v<16, true, MODE, true, false>(mp, grid, smem, st)
-                 : launch_match_v<16, true, MODE, false, false>(mp, grid, smem, st);
+  return has_lut ? launch_match_m<16, true, MODE, true, false>(mp, grid, smem, st)
+                 : launch_match_m<16, true, MODE, false, false>(mp, grid, smem, st);
 #endif
 }
 
@@ -337,8 +367,16 @@ static void fill_params(const dsm_table* t, const dsm_layout* L, const Plan& pl,
   mp.dead_entry = pl.dead_entry;
   mp.live_a = t->desc.n_live_a;
   mp.live_b = t->desc.split_row + t->desc.n_live_b;
+  for (uint32_t c = 0; c < L->n_used; ++c) {
+    mp.col_off[c] = pl.col_off[c];
+    mp.col_shift[c] = pl.col_shift[c];
+    mp.gbase[c] = pl.col_off[c] / (16u << pl.rep_shift);
+  }
   mp.rep_shift = pl.rep_shift;
-  mp.direct_fill = pl.direct_fill;
+  mp.big_col = pl.big_col;
+  mp.big_shift = pl.big_shift;
+  mp.tab_bytes = pl.tab_bytes;
+  mp.stage = pl.stage;
   mp.n_jobs = n_jobs;
   mp.slots = pl.slots;
   mp.work_counter = counter;
@@ -448,13 +486,17 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     const bool wide = pl.slots >= 1024u;
     const dim3 grid(wide ? n_jobs : (n_jobs + 7) / 8);
     const uint32_t sm_bytes = wide ? chunk_bytes : 8u * chunk_bytes;
-#define EXTRACT(W, R, L) k_extract<W, R, L><<<grid, 256, sm_bytes, ctx->stream>>>(gp)
+#define EXTRACT(W, R, L, S) k_extract<W, R, L, S><<<grid, 256, sm_bytes, ctx->stream>>>(gp)
+    const bool shortw = !wide && pl.slots <= 512u && pl.wps <= 8u;  // counts in registers, records in one batch
     if (wide) {
-      if (row32) { if (has_lut) EXTRACT(8, true, true); else EXTRACT(8, true, false); }
-      else       { if (has_lut) EXTRACT(8, false, true); else EXTRACT(8, false, false); }
+      if (row32) { if (has_lut) EXTRACT(8, true, true, false); else EXTRACT(8, true, false, false); }
+      else       { if (has_lut) EXTRACT(8, false, true, false); else EXTRACT(8, false, false, false); }
+    } else if (shortw) {
+      if (row32) { if (has_lut) EXTRACT(1, true, true, true); else EXTRACT(1, true, false, true); }
+      else       { if (has_lut) EXTRACT(1, false, true, true); else EXTRACT(1, false, false, true); }
     } else {
-      if (row32) { if (has_lut) EXTRACT(1, true, true); else EXTRACT(1, true, false); }
-      else       { if (has_lut) EXTRACT(1, false, true); else EXTRACT(1, false, false); }
+      if (row32) { if (has_lut) EXTRACT(1, true, true, false); else EXTRACT(1, true, false, false); }
+      else       { if (has_lut) EXTRACT(1, false, true, false); else EXTRACT(1, false, false, false); }
     }
 #undef EXTRACT
     CK(cudaGetLastError());

@@ -202,9 +202,17 @@ struct MatchParams {
   uint32_t n_entries;
   uint32_t dead_entry;   // table entry every job rejects by construction (padding rows), or ~0
   uint32_t live_a, live_b;  // rows >= live_a in the first segment / >= live_b in the second are padding
-  uint32_t rep_shift;    // log2 of the table replication factor in shared memory (0 or 3)
-  uint32_t direct_fill;  // 1: the 8 copies fit but no staging copy beside them; the threads fill the
-                         // copies straight from global memory instead of fanning out a TMA-staged table
+  // shared-memory layout of a group's acceptance tables: column c's entries are stored
+  // 2^col_shift[c] times each (copy r of entry e at col_off[c] + ((e << shift) + r) * 16), see k_match
+  uint32_t col_off[DSM_MAX_COLS];    // bytes from the start of the table area
+  uint32_t col_shift[DSM_MAX_COLS];  // log2 copies: rep_shift for every column but big_col (big_shift)
+  uint32_t gbase[DSM_MAX_COLS];      // col_off / (16 << rep_shift): entry offset of a column in gather units
+  uint32_t rep_shift;    // log2 copies of the columns: 3 = conflict-free gathers, 0 = one copy
+  uint32_t big_col;      // column stored with fewer copies (big_shift < rep_shift) to make room, or ~0
+  uint32_t big_shift;
+  uint32_t tab_bytes;    // size of the table area
+  uint32_t stage;        // 1: the tables arrive by TMA in a staging copy in front of the table area (or,
+                         // with every col_shift 0, straight in place); 0: the threads read them from global memory
   uint32_t n_jobs;
   uint32_t slots;        // slots per job = pieces per group * 8
   uint32_t* work_counter;
@@ -411,25 +419,32 @@ __device__ __noinline__ BlockClass classify_block(const uint32_t* cut_lane, uint
 // test and an out-of-line call) instead of leaving them to the generic path.  Pays when such
 // windows are frequent (few rows per job group: config 3, 0.141 against 0.145 ms) and costs when
 // they are rare (8 M rows x 128 groups: 3.88 against 3.66 ms); the host picks per call.
-template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST>
+// MIXED: one column (p.big_col) is stored with fewer copies than the others, so the gather
+// address takes its stride and lane offset per column (one more instruction per gather than the
+// uniform formula: 6 % on a batch that does not need it, hence a variant of its own).
+template <int NCMAX, bool ROW32, int MODE, bool HAS_LUT, bool EVFAST, bool MIXED>
 __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(const MatchParams p) {
   static_assert(MODE == MODE_BITMAP || MODE == MODE_COUNT, "unknown k_match mode");
   constexpr bool COUNT = MODE == MODE_COUNT;
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   constexpr uint32_t ROW_U4 = ROW32 ? 2u : 1u;  // uint4 per row
-  // shared memory: [staging: E entries][table: E entries x R copies][cut-offs: 2 x 128]
-  // Each table entry is stored R = 2^rep_shift times, copy r at uint4 index e*R + r.  With
-  // R = 8 copy r lies in bank group r (4 banks), lane l reads copy l%8, and the 8 lanes of every
-  // quarter-warp phase of a 128-bit gather hit 8 different bank groups: no bank conflicts
-  // whatever the codes are.  R = 1 (large dictionaries) gathers from a single copy.  When the
-  // eight copies fit but not a ninth for staging (p.direct_fill) there is no staging area: the
-  // threads fill the copies straight from global memory.
+  // shared memory: [staging copy: E entries, if p.stage][table area][cut-offs: 2 x 128]
+  // In the table area every entry of column c is stored R_c = 2^col_shift[c] times, copy r of the
+  // column's entry e at uint4 index (e << shift) + r.  With R = 8 copy r lies in bank group r
+  // (4 banks), lane l reads copy l%8, and the 8 lanes of every quarter-warp phase of a 128-bit
+  // gather hit 8 different bank groups: no bank conflicts whatever the codes are.  The host gives 8
+  // copies to every column while three CTAs' tables fit in an SM's shared memory and halves the
+  // copies of the largest column(s) otherwise (those gathers then conflict now and then).  The
+  // tables arrive by TMA into the staging copy when there is room for one, else the threads read
+  // them from global memory; with one copy of everything the TMA lands them in place.
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const uint32_t rep_shift = p.rep_shift;
-  const bool direct_fill = rep_shift != 0u && p.direct_fill != 0u;
+  bool in_place = p.stage != 0u;  // p.stage and a single copy of every column: layout == the global one
+#pragma unroll
+  for (int c = 0; c < NCMAX; ++c) in_place = in_place && (c >= (int)p.n_used || p.col_shift[c] == 0u);
+  const bool staged = p.stage != 0u && !in_place;
   uint4* s_stage = reinterpret_cast<uint4*>(smem_raw);
-  uint4* s_tab = (rep_shift && !direct_fill) ? s_stage + p.n_entries : s_stage;
-  uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + ((size_t)p.n_entries << rep_shift));  // [2][128]
+  unsigned char* s_tab = smem_raw + (staged ? (size_t)p.n_entries * 16u : 0u);
+  uint32_t* s_cut = reinterpret_cast<uint32_t*>(s_tab + p.tab_bytes);  // [2][128]
   __shared__ __align__(8) uint64_t s_bar;
   __shared__ uint32_t s_unit, s_nact;
 
@@ -439,10 +454,21 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
   XposeCtl xc;
   transpose_setup(xc, lane);
 
-  // Gather address of column c for a row: lane_base (table start + this lane's copy)
-  //                                      + (code + base[c]) * stride
-  const uint32_t stride = 16u << rep_shift;
-  const uint32_t lane_base = smem_u32(s_tab) + ((lane & ((1u << rep_shift) - 1u)) << 4);
+  // Gather address of column c for a row: lane_base (table area + this lane's copy)
+  //                                      + (code + gbase[c]) * stride;
+  // for the one column with fewer copies its own stride and lane offset
+  const uint32_t stride = 16u << p.rep_shift;
+  const uint32_t lane_base = smem_u32(s_tab) + ((lane & ((1u << p.rep_shift) - 1u)) << 4);
+  const uint32_t tab_u32 = smem_u32(s_tab);
+  const uint32_t lane16 = lane << 4;
+  auto gather_addr = [&](const int c, const uint32_t code) -> uint32_t {
+    if constexpr (MIXED) {  // per-column stride and lane offset, branch-free (measured faster than a
+                            // predicated special case for the one column: 3.44 against 3.60 ms)
+      const uint32_t st = 16u << p.col_shift[c];
+      return tab_u32 + p.col_off[c] + code * st + (lane16 & (st - 16u));
+    }
+    return lane_base + (code + p.gbase[c]) * stride;
+  };
 
   if (tid == 0) {
     mbar_init(&s_bar, 1);
@@ -475,7 +501,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 
     if (group != cur_group) {
       // ---- stage this group's acceptance table (TMA bulk copy) and cut-off rows
-      if (tid == 0 && !direct_fill) {
+      if (tid == 0 && p.stage) {
         const uint32_t bytes = p.n_entries * 16u;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         mbar_expect_tx(&s_bar, bytes);
@@ -500,30 +526,31 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 #pragma unroll
       for (int t = 0; t < TPG; ++t)
         live[t] = nj >= 32u * (t + 1) ? FULL : (nj > 32u * t ? (1u << (nj - 32u * t)) - 1u : 0u);
-      if (!direct_fill) {
+      if (p.stage) {
         mbar_wait(&s_bar, parity);
         parity ^= 1u;
       }
       // one thread per entry: read it once (from global memory, or from the TMA-staged copy) and
-      // write its R copies, lane l starting at copy l so that the eight lanes of a store phase hit
-      // eight different bank groups
+      // write its copies, lane l starting at copy l so that the lanes of a store phase hit
+      // different bank groups
       {
-        const uint4* src = direct_fill ? p.tabs + (size_t)group * p.n_entries : s_stage;
+        const uint4* src = p.stage ? s_stage : p.tabs + (size_t)group * p.n_entries;
         uint32_t need = 0;
         for (uint32_t e = tid; e < p.n_entries; e += MATCH_THREADS) {
-          const uint4 v = direct_fill ? __ldg(src + e) : src[e];
-          if (rep_shift) {
+          const uint4 v = p.stage ? src[e] : __ldg(src + e);
+          uint32_t c = 0;  // the entry's column
 #pragma unroll
-            for (uint32_t r = 0; r < 8u; ++r) s_tab[(size_t)e * 8u + ((r + lane) & 7u)] = v;
+          for (int i = 1; i < NCMAX; ++i) c += (i < (int)p.n_used && e >= p.base[i]) ? 1u : 0u;
+          if (!in_place) {
+            const uint32_t sh = p.col_shift[c], R = 1u << sh;
+            uint4* dst = reinterpret_cast<uint4*>(s_tab + p.col_off[c]) + ((size_t)(e - p.base[c]) << sh);
+#pragma unroll
+            for (uint32_t r = 0; r < 8u; ++r)
+              if (r < R) dst[(r + lane) & (R - 1u)] = v;
           }
           const bool all = ((v.x & live[0]) == live[0]) && ((v.y & live[1]) == live[1]) &&
                            ((v.z & live[2]) == live[2]) && ((v.w & live[3]) == live[3]);
-          if (!all && e != p.dead_entry) {
-            uint32_t c = 0;
-#pragma unroll
-            for (int i = 1; i < NCMAX; ++i) c += (i < (int)p.n_used && e >= p.base[i]) ? 1u : 0u;
-            need = max(need, c + 1u);
-          }
+          if (!all && e != p.dead_entry) need = max(need, c + 1u);
         }
         if (need > 1u) atomicMax(&s_nact, need);
       }
@@ -580,7 +607,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
           if constexpr (HAS_LUT) {
             if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
           }
-          const uint4 a = lds128(lane_base + (code + p.base[c]) * stride);
+          const uint4 a = lds128(gather_addr(c, code));
           m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
         }
       }
@@ -657,7 +684,7 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
                   if constexpr (HAS_LUT) {
                     if (p.lut[c] != nullptr) code = __ldg(p.lut[c] + code);
                   }
-                  const uint4 a = lds128(lane_base + (code + p.base[c]) * stride);
+                  const uint4 a = lds128(gather_addr(c, code));
                   m.x &= a.x; m.y &= a.y; m.z &= a.z; m.w &= a.w;
                 }
                 const uint32_t mm[TPG] = {m.x, m.y, m.z, m.w};
@@ -812,8 +839,13 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 // all 8 warps; the rest is done by the first of them).
 // ------------------------------------------------------------------------------------------
 
-template <int WPJ, bool ROW32, bool HAS_LUT>
+// SHORT (one warp per job, at most 512 slots of at most 8 windows): the slot counts stay in
+// registers after pass 1, so the slots that hold the first k matches are known exactly -- those
+// whose prefix count is below k -- before any further load; their window records are then fetched
+// in ONE batch (lane i = i-th such slot) instead of chunk by chunk with a dependent round trip each.
+template <int WPJ, bool ROW32, bool HAS_LUT, bool SHORT>
 __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
+  static_assert(!SHORT || WPJ == 1, "the batched walk is for one warp per job");
   constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
   constexpr uint32_t FULL = 0xFFFFFFFFu;
   extern __shared__ uint32_t chunk_sums[];  // [JPC][n_chunks]
@@ -836,7 +868,27 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
 #endif
   uint32_t* csum = chunk_sums + jl * n_chunks;
 
-  {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
+  uint32_t creg[SHORT ? 16 : 1] = {0};  // SHORT: this lane's slot of every chunk
+  if constexpr (SHORT) {
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      const uint32_t s = u * 32u + lane;
+      creg[u] = (live && s < n_slots) ? cnt[s] : 0u;
+    }
+    uint32_t tot = 0;
+    int ls_a = -1, ls_b = -1;
+#pragma unroll
+    for (int u = 0; u < 16; ++u) {
+      if (u * 32u >= n_slots) break;  // warp-uniform
+      const uint32_t s = u * 32u + lane;
+      tot += __reduce_add_sync(FULL, creg[u]);
+      const uint32_t hit_a = __ballot_sync(FULL, creg[u] != 0 && s < p.slots_a);
+      const uint32_t hit_b = __ballot_sync(FULL, creg[u] != 0 && s >= p.slots_a);
+      if (hit_a) ls_a = (int)(u * 32u + 31u - __clz(hit_a));
+      if (hit_b) ls_b = (int)(u * 32u + 31u - __clz(hit_b));
+    }
+    if (lane == 0) { red_total[warp] = tot; red_last_a[warp] = ls_a; red_last_b[warp] = ls_b; }
+  } else {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
     uint32_t tot = 0;
     int ls_a = -1, ls_b = -1;
     for (uint32_t ch0 = wj; ch0 < n_chunks; ch0 += 8u * WPJ) {
@@ -933,8 +985,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   __shared__ uint32_t s_wlist[8][256][2];  // long slots: (window, row-lane set) of non-empty windows
   uint32_t (*wlist)[2] = s_wlist[warp];
   uint32_t n_pend = 0, q_total = 0;
-  uint32_t have = 0;             // forward mode: matches written so far
-  uint32_t last = DSM_NO_ROW;    // backward mode: highest matching row seen
+  uint32_t have = 0;             // matches written so far
   auto push = [&](const uint32_t bs, const uint32_t nb, const uint32_t R, const uint32_t cut) {
     if (lane == 0) {
       pend[n_pend][0] = bs;
@@ -945,38 +996,36 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
     q_total += nb * (uint32_t)__popc(R);
     ++n_pend;
   };
-  // forward: append the matching candidates to out[] until k are there;
-  // backward: walk the candidates from the end and stop at the first match
-  auto flush = [&](const bool backward) {  // warp-uniform
+  // append the matching candidates of the queued windows to out[] until k are there
+  auto flush = [&]() {  // warp-uniform
     __syncwarp();
     for (uint32_t q0 = 0; q0 < q_total; q0 += 32u * EXTRACT_LANE_ROWS) {
-      if (backward ? last != DSM_NO_ROW : have >= k) break;
+      if (have >= k) break;
       uint32_t row[EXTRACT_LANE_ROWS], ok[EXTRACT_LANE_ROWS];
 #pragma unroll
       for (int u = 0; u < EXTRACT_LANE_ROWS; ++u) {
-        const uint32_t qi = q0 + u * 32 + lane;
+        const uint32_t q = q0 + u * 32 + lane;
         row[u] = 0;
         ok[u] = 0;
-        if (qi < q_total) {
-          const uint32_t q = backward ? q_total - 1u - qi : qi;
+        if (q < q_total) {
           uint32_t e = 0;  // the queued window that holds candidate q: starts ascend, at most 16 entries
 #pragma unroll
           for (uint32_t s = EXTRACT_PENDING / 2; s >= 1u; s >>= 1)
             if (e + s < n_pend && q >= pend[e + s][3]) e += s;
           row[u] = candidate(q - pend[e][3], pend[e][0], pend[e][1]);
+#ifdef DSM_X_NOEVAL
+          ok[u] = 1;
+#else
           ok[u] = eval_row(row[u], pend[e][2]);
+#endif
         }
       }
 #pragma unroll
       for (int u = 0; u < EXTRACT_LANE_ROWS; ++u) {
         const uint32_t hits = __ballot_sync(FULL, ok[u]);
-        if (backward) {
-          if (hits && last == DSM_NO_ROW) last = __shfl_sync(FULL, row[u], __ffs(hits) - 1);
-        } else {
-          const uint32_t rank = have + __popc(hits & lt_mask);
-          if (ok[u] && rank < k) out[rank] = row[u];
-          have = min(k, have + (uint32_t)__popc(hits));
-        }
+        const uint32_t rank = have + __popc(hits & lt_mask);
+        if (ok[u] && rank < k) out[rank] = row[u];
+        have = min(k, have + (uint32_t)__popc(hits));
       }
     }
     n_pend = 0;
@@ -984,8 +1033,84 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
     __syncwarp();
   };
 
-  // ---- first k matches: walk slots and windows in row order, skipping empty ones
-  for (uint32_t c0 = 0; c0 < n_chunks && have < k; c0 += 32) {
+  // ---- the last match of each segment (the max-price row) lies in the last non-empty window of
+  // the segment's last non-empty slot.  Lanes 0-15 look after the first segment, lanes 16-31 after
+  // the second; the slot bounds and window records are requested here, before the walk for the
+  // first k matches, so that their latency is hidden behind it.
+  const uint32_t half = lane >> 4, hl = lane & 15u;
+  const int t_slot = half ? ls_b : ls_a;
+  uint32_t t_b0 = 0, t_b1 = 0;
+  if (t_slot >= 0) { t_b0 = p.slot_start[t_slot]; t_b1 = p.slot_start[t_slot + 1]; }
+  const uint32_t t_nwin = (t_b1 - t_b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+  // the last (up to) 16 windows of the slot, window t_w = t_nwin - 1 - hl for this lane
+  uint32_t t_rec = 0;
+  if (t_slot >= 0 && hl < t_nwin)
+    t_rec = wr_job[((size_t)t_slot * p.wps + (t_nwin - 1u - hl)) * JPG];
+
+  // ---- first k matches, SHORT: the needed slots from the counts in registers, their records in
+  // one batch of loads, then the same queue of windows as below
+  if constexpr (SHORT) {
+    __shared__ uint32_t s_need[8][32];
+    uint32_t* need = s_need[warp];
+    uint32_t round_lo = 0;  // needed slots (in row order) handled by earlier rounds
+    bool more = true;
+    while (more && have < k) {
+      uint32_t base = 0, n_need = 0;
+#pragma unroll
+      for (int u = 0; u < 16; ++u) {
+        if (u * 32u >= n_slots) break;  // warp-uniform
+        const uint32_t v = creg[u];
+        uint32_t incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const uint32_t y = __shfl_up_sync(FULL, incl, d);
+          if (lane >= (uint32_t)d) incl += y;
+        }
+        const bool nd = v != 0u && base + incl - v < k;  // matches before this slot: fewer than k
+        const uint32_t nm = __ballot_sync(FULL, nd);
+        const uint32_t pos = n_need + __popc(nm & lt_mask);
+        if (nd && pos >= round_lo && pos < round_lo + 32u) need[pos - round_lo] = u * 32u + lane;
+        n_need += __popc(nm);
+        base += __shfl_sync(FULL, incl, 31);
+      }
+      __syncwarp();
+      const uint32_t n_here = min(32u, n_need - min(n_need, round_lo));
+      more = n_need > round_lo + 32u;
+      // lane i: bounds and window records of the i-th needed slot of this round
+      uint32_t my_s = 0, my_b0 = 0, my_b1 = 0;
+      uint32_t mk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+      if (lane < n_here) {
+        my_s = need[lane];
+        my_b0 = p.slot_start[my_s];
+        my_b1 = p.slot_start[my_s + 1];
+        const uint32_t* wr = wr_job + (size_t)my_s * p.wps * JPG;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < p.wps ? wr[(size_t)w * JPG] : 0u;
+        const uint32_t my_nwin = (my_b1 - my_b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < my_nwin ? mk[w] : 0u;  // records past the slot's end are stale
+      }
+      __syncwarp();
+      for (uint32_t i = 0; i < n_here && have < k; ++i) {
+        const uint32_t sl = __shfl_sync(FULL, my_s, i);
+        const uint32_t b0 = __shfl_sync(FULL, my_b0, i), b1 = __shfl_sync(FULL, my_b1, i);
+        const uint32_t cut = sl >= p.slots_a ? cut_b : cut_a;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) {
+          const uint32_t R = __shfl_sync(FULL, mk[w], i);
+          if (R != 0) {
+            const uint32_t bs = b0 + (uint32_t)w * WIN_BLOCKS;
+            push(bs, min(bs + WIN_BLOCKS, b1) - bs, R, cut);
+          }
+        }
+        if (n_pend > EXTRACT_PENDING - 8u || q_total >= 32u * EXTRACT_LANE_ROWS) flush();
+      }
+      flush();
+      round_lo += 32u;
+    }
+  }
+  // ---- first k matches, general: walk slots and windows in row order, skipping empty ones
+  for (uint32_t c0 = 0; !SHORT && c0 < n_chunks && have < k; c0 += 32) {
     const uint32_t cs = c0 + lane < n_chunks ? csum[c0 + lane] : 0u;
     uint32_t open_ch = __ballot_sync(FULL, cs != 0);
     while (open_ch && have < k) {  // all loops below are warp-uniform
@@ -1023,7 +1148,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
             }
           }
           // one flush site per slot (the queue holds two slots' worth of windows)
-          if (n_pend > EXTRACT_PENDING - 8u || q_total >= 32u * EXTRACT_LANE_ROWS) flush(false);
+          if (n_pend > EXTRACT_PENDING - 8u || q_total >= 32u * EXTRACT_LANE_ROWS) flush();
           continue;
         }
         const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
@@ -1052,39 +1177,61 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
           for (uint32_t i = 0; i < n_list && have < k; ++i) {
             const uint32_t bs = b0 + wlist[i][0] * WIN_BLOCKS;
             push(bs, min(bs + WIN_BLOCKS, b1) - bs, wlist[i][1], cut);
-            if (n_pend == EXTRACT_PENDING || q_total >= 32u * EXTRACT_LANE_ROWS) flush(false);
+            if (n_pend == EXTRACT_PENDING || q_total >= 32u * EXTRACT_LANE_ROWS) flush();
           }
           __syncwarp();
         }
       }
     }
   }
-  flush(false);
+  flush();
   for (uint32_t i = have + lane; i < k; i += 32) out[i] = DSM_NO_ROW;
 
-  // ---- last match of each segment: last non-empty slot -> its last non-empty window ->
-  // candidates from the end
-  auto last_row_of = [&](const int sl) -> uint32_t {
-    if (sl < 0) return DSM_NO_ROW;
-    const uint32_t b0 = p.slot_start[sl], b1 = p.slot_start[sl + 1];
-    const uint32_t cut = (uint32_t)sl >= p.slots_a ? cut_b : cut_a;
-    const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
-    const uint32_t* wr = wr_job + (size_t)sl * p.wps * JPG;
-    last = DSM_NO_ROW;
-    for (int w0 = (int)((n_win - 1) / 32u * 32u); w0 >= 0; w0 -= 32) {
-      const uint32_t wv = (uint32_t)w0 + lane < n_win ? wr[(size_t)(w0 + lane) * JPG] : 0u;
-      const uint32_t nz = __ballot_sync(FULL, wv != 0);
-      if (!nz) continue;
-      const uint32_t wl = 31u - __clz(nz);
-      const uint32_t bs = b0 + ((uint32_t)w0 + wl) * WIN_BLOCKS;
-      push(bs, min(bs + WIN_BLOCKS, b1) - bs, __shfl_sync(FULL, wv, wl), cut);
-      flush(true);
-      break;
+  // ---- last match of each segment.  Per half-warp: the last non-empty window among the 16
+  // requested above (a slot's last match is almost always there; otherwise the earlier windows are
+  // read 16 at a time), then its candidate rows from the end, 16 per round, both segments at once.
+  uint32_t last_ab[2] = {DSM_NO_ROW, DSM_NO_ROW};
+  {
+    uint32_t w_off = 0;  // windows before the 16 in t_rec (counted from the slot's end)
+    uint32_t nz = (__ballot_sync(FULL, t_rec != 0) >> (16u * half)) & 0xFFFFu;
+    // warp-uniform loop; a half that has found its window (or has none) idles
+    while (__any_sync(FULL, t_slot >= 0 && nz == 0u && w_off + 16u < t_nwin)) {
+      const bool more = t_slot >= 0 && nz == 0u && w_off + 16u < t_nwin;
+      if (more) w_off += 16u;
+      uint32_t rec = 0;
+      if (more && w_off + hl < t_nwin) rec = wr_job[((size_t)t_slot * p.wps + (t_nwin - 1u - w_off - hl)) * JPG];
+      const uint32_t z = (__ballot_sync(FULL, rec != 0) >> (16u * half)) & 0xFFFFu;
+      if (more) { t_rec = rec; nz = z; }
     }
-    return last;
-  };
-  const uint32_t last_a = last_row_of(ls_a);
-  const uint32_t last_b = last_row_of(ls_b);
+    // lane with the latest non-empty window of its half = lowest set bit of nz
+    const uint32_t src = (nz ? (uint32_t)__ffs(nz) - 1u : 0u) + 16u * half;
+    const uint32_t R = __shfl_sync(FULL, t_rec, src);
+    const bool has = t_slot >= 0 && nz != 0u;
+    const uint32_t w = t_nwin - 1u - w_off - (src & 15u);
+    const uint32_t bs = t_b0 + w * WIN_BLOCKS;
+    const uint32_t nb = has ? min(bs + WIN_BLOCKS, t_b1) - bs : 0u;
+    const uint32_t n_cand = nb * (uint32_t)__popc(R);
+    const uint32_t cut = half ? cut_b : cut_a;
+    uint32_t found = DSM_NO_ROW;
+#ifdef DSM_X_NOTAIL
+    if (false)
+#endif
+    for (uint32_t r0 = 0; __any_sync(FULL, has && found == DSM_NO_ROW && r0 < n_cand); r0 += 16u) {
+      const uint32_t q = r0 + hl;
+      uint32_t row = 0, ok = 0;
+      if (has && found == DSM_NO_ROW && q < n_cand) {
+        row = candidate(n_cand - 1u - q, bs, R);
+        ok = eval_row(row, cut);
+      }
+      const uint32_t hits = (__ballot_sync(FULL, ok) >> (16u * half)) & 0xFFFFu;
+      const uint32_t first = (hits ? (uint32_t)__ffs(hits) - 1u : 0u) + 16u * half;
+      const uint32_t r = __shfl_sync(FULL, row, first);
+      if (hits && found == DSM_NO_ROW) found = r;
+    }
+    last_ab[0] = __shfl_sync(FULL, found, 0);
+    last_ab[1] = __shfl_sync(FULL, found, 16);
+  }
+  const uint32_t last_a = last_ab[0], last_b = last_ab[1];
   if (lane == 0) {
     p.out_cnt[job] = total;
     uint32_t best = last_a;

@@ -56,10 +56,26 @@ GPUF_MEM_BOUNDED, GPUF_CC_BOUNDED, GPUF_NAME_ANY = 1, 2, 8
 NO_ROW = 0xFFFFFFFF
 MAX_CODES = 65535
 LUT_THRESHOLD = 1024  # set columns with more dictionary entries go through a per-call remap
-# Eight conflict-free copies of a job group's acceptance tables fit beside three resident CTAs per
-# SM up to this many table entries (dsmatch.cu:make_plan); cpu and memory are merged into one
-# pair-coded column only while the tables stay within it.
-PAIR_ENTRY_BUDGET = 570
+# Shared memory one of three resident CTAs per SM has for a job group's acceptance tables
+# (dsmatch.cu:make_plan).  Every entry is stored 8 times for conflict-free gathers; when that does
+# not fit the library halves the copies of the largest column.  cpu and memory are merged into one
+# pair-coded column only if the tables then still fit with at least 4 copies of every column.
+TABLE_AREA_BUDGET = 220 * 1024 // 3 - 1024 - 1024
+
+
+def table_copies(cards: Sequence[int]) -> List[int]:
+    """log2 of the copies per column the library will keep in shared memory for these dictionary
+    sizes (mirror of dsmatch.cu:make_plan): 8 of everything, else the largest column 4 / 2 / 1,
+    else one copy of everything."""
+    big = max(range(len(cards)), key=lambda i: (cards[i], -i))
+    pad = lambda n: (n + 127) // 128 * 128
+    area = lambda bshift: sum(pad((c * 16) << (bshift if i == big else 3)) for i, c in enumerate(cards))
+    bshift = 3
+    while bshift > 0 and area(bshift) > TABLE_AREA_BUDGET:
+        bshift -= 1
+    if area(bshift) > TABLE_AREA_BUDGET:
+        return [0] * len(cards)
+    return [bshift if i == big else 3 for i in range(len(cards))]
 
 
 def backend_code(b: Any) -> int:
@@ -210,7 +226,7 @@ def _check_card(name: str, n: int) -> None:
 def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
                  pair_columns: Optional[bool] = None) -> EncodedTable:
     """``pair_columns``: merge cpu and memory into one pair-coded column (one table gather per row
-    instead of two).  ``None`` = when the acceptance tables stay within ``PAIR_ENTRY_BUDGET``."""
+    instead of two).  ``None`` = when the tables then still fit with at least 4 copies of every column (``table_copies``)."""
     n = len(oc)
     sh = oc.shapes
     price = np.asarray(oc.price, dtype=np.float64)
@@ -345,9 +361,9 @@ def encode_table(oc: OfferColumns, *, check_sorted_backends: bool = True,
     # cpu + memory: one pair-coded column when the tables stay small enough for eight copies
     pkey = cpu_ord.astype(np.int64) | (mem_ord.astype(np.int64) << 16)
     puniq, pinv = np.unique(pkey, return_inverse=True)
-    resident_entries = sum(c.card for c in tail_cols if c.card <= LUT_THRESHOLD)
+    resident = [c.card for c in tail_cols if c.card <= LUT_THRESHOLD]
     if pair_columns is None:
-        pair_columns = len(puniq) + resident_entries <= PAIR_ENTRY_BUDGET and len(puniq) <= MAX_CODES
+        pair_columns = min(table_copies([len(puniq)] + resident)) >= 2 and len(puniq) <= MAX_CODES
     pair_entries = None
     if pair_columns:
         _check_card("cpu_memory", len(puniq))

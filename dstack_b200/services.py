@@ -298,7 +298,15 @@ class OfferCatalog:
                 instance=M.InstanceType(name=item.instance_name, resources=res),
                 availability=M.InstanceAvailability.UNKNOWN)
         if self._materialize is not None:
-            return self._materialize(int(i))
+            # building an offer object costs ~50 us (pydantic); a pass asks for the same cheap rows
+            # for many jobs, so the objects made so far are kept (bounded)
+            cache = self.__dict__.setdefault("_made", {})
+            pair = cache.get(int(i))
+            if pair is None:
+                if len(cache) >= 200_000:
+                    cache.clear()
+                pair = cache[int(i)] = self._materialize(int(i))
+            return pair
         return self.backends[i], self.offers[i]
 
     @staticmethod

@@ -231,16 +231,53 @@ def test_topk_on_a_pool_table_agrees_with_its_bitmap(matcher):
 
 
 def test_tables_that_fit_eight_times_only_without_a_staging_copy(matcher):
-    """Dictionaries of 467..570 entries: eight shared-memory copies fit beside three CTAs, a ninth
-    (the TMA staging copy) does not, so the kernel fills the copies straight from global memory.
-    The plan must say so (shared memory = entries * 128 + cut-offs) and results stay exact."""
+    """Dictionaries of 467..570 entries: eight shared-memory copies fit beside three CTAs; whether
+    a ninth (the TMA staging copy) does too decides between the TMA path and the threads filling
+    the copies straight from global memory.  The plan must say which, and results stay exact."""
     cat = synth.make_catalog(200_000, seed=4, n_shapes=4096)
-    table = encode_table(cat.columns)
+    table = encode_table(cat.columns, pair_columns=False)
     sj = synth.make_jobs(cat, table, 300, seed=4)
     dt = matcher.upload(table)
     try:
-        plan = matcher.plan(dt, pack_jobs(table, sj.columns), 16)
+        packed = pack_jobs(table, sj.columns)
+        plan = matcher.plan(dt, packed, 16)
+        got = matcher.topk_rows(dt, packed, 16)
     finally:
         dt.close()
-    assert 466 < plan["entries"] <= 570 and plan["smem"] == plan["entries"] * 128 + 1024
+    from dstack_b200.encode import TABLE_AREA_BUDGET
+
+    e = plan["entries"]
+    assert 466 < e <= 570
+    staged = e * 144 <= TABLE_AREA_BUDGET  # room for the TMA staging copy beside the eight copies?
+    assert plan["smem"] == e * (144 if staged else 128) + 1024
+    want = columnar.topk(cat.columns, sj.columns, 16)
+    assert np.array_equal(got[1].astype(np.int64), want.count)
+    src = np.where(got[0] == NO_ROW, -1, table.perm[np.minimum(got[0], table.n_rows - 1)])
+    assert np.array_equal(src, want.index)
+
+
+def test_largest_column_with_fewer_copies(matcher):
+    """cpu and memory paired into one column push the tables past what fits eight times beside
+    three CTAs; the library then keeps the largest column (regions) four times and the rest
+    eight times.  The plan must show that layout, and results stay exact."""
+    from dstack_b200.encode import table_copies
+
+    cat = synth.make_catalog(200_000, seed=4, n_shapes=4096)
+    table = encode_table(cat.columns)
+    assert table.pair_entries is not None
+    sj = synth.make_jobs(cat, table, 300, seed=4)
+    packed = pack_jobs(table, sj.columns)
+    cards = packed.layout["card"]
+    copies = table_copies(cards)
+    assert min(copies) == 2 and copies.count(2) == 1 and cards[copies.index(2)] == max(cards)
+    dt = matcher.upload(table)
+    try:
+        plan = matcher.plan(dt, packed, 16)
+    finally:
+        dt.close()
+    pad = lambda n: (n + 127) // 128 * 128
+    assert plan["entries"] > 570
+    assert plan["smem"] == sum(pad((c * 16) << s) for c, s in zip(cards, copies)) + 1024
     _check(matcher, cat, sj, 16)
+
+
