@@ -258,7 +258,9 @@ struct ExtractParams {
 // warps stride over the column's dictionary entries; one ballot = one table word.
 // ------------------------------------------------------------------------------------------
 
+#ifndef BUILD_CHUNK
 #define BUILD_CHUNK 64u
+#endif
 
 __device__ __forceinline__ bool range_accepts(uint32_t word, uint32_t e) {
   return e >= (word & 0xFFFFu) && e <= (word >> 16);
@@ -1013,11 +1015,7 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
           for (uint32_t s = EXTRACT_PENDING / 2; s >= 1u; s >>= 1)
             if (e + s < n_pend && q >= pend[e + s][3]) e += s;
           row[u] = candidate(q - pend[e][3], pend[e][0], pend[e][1]);
-#ifdef DSM_X_NOEVAL
-          ok[u] = 1;
-#else
           ok[u] = eval_row(row[u], pend[e][2]);
-#endif
         }
       }
 #pragma unroll
@@ -1213,9 +1211,6 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
     const uint32_t n_cand = nb * (uint32_t)__popc(R);
     const uint32_t cut = half ? cut_b : cut_a;
     uint32_t found = DSM_NO_ROW;
-#ifdef DSM_X_NOTAIL
-    if (false)
-#endif
     for (uint32_t r0 = 0; __any_sync(FULL, has && found == DSM_NO_ROW && r0 < n_cand); r0 += 16u) {
       const uint32_t q = r0 + hl;
       uint32_t row = 0, ok = 0;
