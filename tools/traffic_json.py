@@ -46,7 +46,8 @@ doc[name] = {
     # per-SM average
     "lsu_wavefronts": int(get("SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts.avg") * n_sm),
     "shared_wavefronts": int(get("l1tex__data_pipe_lsu_wavefronts_mem_shared.sum")),
-    "duration_us_under_ncu": get("gpu__time_duration.sum"),
+    "duration_us_under_ncu": get("gpu__time_duration.sum") * {"ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}[
+        units[head.index("gpu__time_duration.sum")]],
     "lsu_pipe_pct": get("l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed"),
     "issue_active_pct": get("smsp__issue_active.avg.pct_of_peak_sustained_active"),
 }
