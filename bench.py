@@ -344,7 +344,7 @@ def run_topk_workload(args, wl, rank, world, local_rank, dist, *, steps):
     cat = synth.make_catalog(N, seed=wl["seed"], n_shapes=wl["shapes"])
     full = cat.columns
     order = rank_order(full)
-    sm = ShardedMatcher(full, rank=rank, world=world, device=local_rank, order=order)
+    sm = ShardedMatcher(full, rank=rank, world=world, device=local_rank, order=order, exchange=args.exchange)
     table = sm.table
     sj = synth.make_jobs(cat, table, J, seed=wl["seed"])  # dictionaries are shared by every shard
     t_pack = time.perf_counter()
@@ -474,6 +474,9 @@ def run_topk_workload(args, wl, rank, world, local_rank, dist, *, steps):
             bd_max = dict(bd)
             per_rank_match_ms = [match_ms]
 
+        missing = sm.exchange_status()
+        assert missing == 0, f"peer exchange: a wait timed out (rank {missing - 1} never arrived)"
+
         # ---- parity at full size (outside the timed regions)
         sm.step()
         rng = np.random.default_rng(1000 + rank)
@@ -499,7 +502,8 @@ def run_topk_workload(args, wl, rank, world, local_rank, dist, *, steps):
         e2e_p50=e2e_p50, api_s=api_s, pack_ms=pack_ms, breakdown=bd_max, match_ms=match_ms,
         per_rank_match_ms=per_rank_match_ms, launches=int(launches), clock_info=clock_info, verified=int(verified),
         shard_verified=int(shard_verified), setup_s=setup_s, rec_words=rec_words, table=table, packed=packed,
-        warm=warm, steps=steps, sms=torch.cuda.get_device_properties(dev).multi_processor_count)
+        warm=warm, steps=steps, sms=torch.cuda.get_device_properties(dev).multi_processor_count,
+        exchange=sm.exchange_used, exchange_note=sm.exchange_note)
     sm.close()
     del flush
     torch.cuda.empty_cache()
@@ -558,6 +562,14 @@ def roofline_block(r, world):
     return out
 
 
+EXCHANGES = {
+    "p2p": "dsm_xchg_all_gather_dev: own kernels, every rank stores its record into its peers' IPC-mapped buffers "
+           "over NVLink and raises a flag",
+    "nccl": "NCCL all_gather_into_tensor",
+    "none": "no exchange",
+}
+
+
 def topk_line(args, r, world):
     wl, J, N, k = r["wl"], r["J"], r["N"], r["k"]
     table = r["table"]
@@ -573,13 +585,14 @@ def topk_line(args, r, world):
                    "job_order": "grouped by the last column a job filters on" if r["packed"].order is not None else "as given",
                    "l2": "flushed between timed steps (256 MiB memset outside the event pairs)",
                    "parallelism": f"catalog sharded x{world} (result order dealt out in 1024-row chunks), "
-                                  "one NCCL all_gather of per-shard top-k + k-way merge kernel"
+                                  f"one all-gather of per-shard top-k ({EXCHANGES[r['exchange']]}) + k-way merge kernel"
                    if world > 1 else "1 GPU"},
         "e2e": {"value": evals / r["e2e_mean"], "unit": UNIT, "h2d_bytes_per_step": int(J * r["rec_words"] * 4),
                 "d2h_bytes_per_step": int(J * (k + 2) * 4 if world == 1 else J * (k * 8 + 16)),
                 "p50_batch_latency_ms": 1e3 * r["e2e_p50"],
                 "path": "dsm_match_topk (C ABI, pinned host buffers)" if world == 1 else
-                        "pinned H2D + dsm_match_topk_dev + NCCL all_gather + dsm_merge_shards_interleaved_dev + D2H"},
+                        f"pinned H2D + dsm_match_topk_dev + {EXCHANGES[r['exchange']]} + "
+                        "dsm_merge_shards_interleaved_dev + D2H"},
         "gpu_launches": r["launches"],
         "clocks": r["clock_info"],
         "step_breakdown_ms": {**r["breakdown"],
@@ -591,6 +604,8 @@ def topk_line(args, r, world):
         "setup_seconds": r["setup_s"],
     }
     if world > 1:
+        out["exchange"] = {"kind": r["exchange"], "what": EXCHANGES[r["exchange"]],
+                           **({"fell_back_because": r["exchange_note"]} if r["exchange_note"] else {})}
         out["anchor_workload"] = "cfg4 (the N=1 line carries the same workload on one GPU as strong_scaling_anchor)"
     if r["api_s"]:
         out["e2e_api"] = {"value": evals / statistics.mean(r["api_s"]), "unit": UNIT,
@@ -815,6 +830,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="")
+    ap.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                    help="N>1: the step's all-gather (own peer-store kernels, or NCCL)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="N=1: skip the config-4 anchor and configs 1, 2, 5")
     args = ap.parse_args()

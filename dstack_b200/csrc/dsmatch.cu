@@ -29,6 +29,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <mutex>
 #include <new>
 #include <string>
@@ -36,6 +37,7 @@
 #include <vector>
 
 #include "kernels.cuh"
+#include "exchange.cuh"
 
 #define MAX_SMEM_BYTES (200 * 1024)
 
@@ -1373,6 +1375,167 @@ int dsm_plan_query(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* lay
   out[5] = pl.smem;
   out[6] = pl.lay.n_entries;
   out[7] = pl.n_groups;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// peer exchange (exchange.cuh): the sharded step's all-gather over IPC-mapped peer memory
+// ------------------------------------------------------------------------------------------
+
+}  // extern "C"
+
+struct dsm_xchg {
+  dsm_ctx* ctx;
+  uint32_t world, rank;
+  uint64_t slot_bytes;          // multiple of 256
+  char* local = nullptr;        // [2][world][slot_bytes] | flags [2][world] | ticket | err
+  size_t flags_off, ticket_off, err_off, total;
+  XchgPeers peers;
+  bool opened[DSM_XCHG_MAX_WORLD];  // mapped with cudaIpcOpenMemHandle (to be closed)
+  bool connected = false;
+  uint32_t epoch = 0;
+};
+
+static void xchg_wire(dsm_xchg* x, uint32_t r, char* base) {
+  x->peers.data[r] = base;
+  x->peers.flags[r] = reinterpret_cast<uint32_t*>(base + x->flags_off);
+}
+
+extern "C" {
+
+int dsm_xchg_create(dsm_ctx* ctx, uint32_t world, uint32_t rank, uint64_t bytes_per_rank, dsm_xchg** out,
+                    void* ipc_handle_out) {
+  if (!ctx || !out) return fail(DSM_E_ARG, "NULL argument");
+  if (world == 0 || world > DSM_XCHG_MAX_WORLD || rank >= world) return fail(DSM_E_ARG, "exchange takes 1..32 ranks");
+  if (bytes_per_rank == 0 || bytes_per_rank % 16) return fail(DSM_E_ARG, "bytes_per_rank must be a non-zero multiple of 16");
+  static_assert(sizeof(cudaIpcMemHandle_t) == DSM_IPC_HANDLE_BYTES, "IPC handle size");
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  dsm_xchg* x = new (std::nothrow) dsm_xchg();
+  if (!x) return fail(DSM_E_ARG, "out of host memory");
+  x->ctx = ctx;
+  x->world = world;
+  x->rank = rank;
+  x->slot_bytes = (bytes_per_rank + 255) / 256 * 256;
+  x->flags_off = 2 * (size_t)world * x->slot_bytes;
+  x->ticket_off = x->flags_off + 256;  // 2 * 32 flag words fit in 256 bytes
+  x->err_off = x->ticket_off + 256;
+  x->total = x->err_off + 256;
+  memset(&x->peers, 0, sizeof x->peers);
+  memset(x->opened, 0, sizeof x->opened);
+  // a plain cudaMalloc of its own: IPC handles cover whole allocations
+  cudaError_t e = cudaMalloc(reinterpret_cast<void**>(&x->local), x->total);
+  if (e != cudaSuccess) {
+    delete x;
+    return fail(DSM_E_CUDA, "cudaMalloc (exchange): %s", cudaGetErrorString(e));
+  }
+  e = cudaMemset(x->local + x->flags_off, 0, x->total - x->flags_off);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e == cudaSuccess && ipc_handle_out)
+    e = cudaIpcGetMemHandle(reinterpret_cast<cudaIpcMemHandle_t*>(ipc_handle_out), x->local);
+  if (e != cudaSuccess) {
+    cudaFree(x->local);
+    delete x;
+    return fail(DSM_E_CUDA, "exchange setup: %s", cudaGetErrorString(e));
+  }
+  xchg_wire(x, rank, x->local);
+  *out = x;
+  return 0;
+}
+
+int dsm_xchg_local_base(dsm_xchg* x, void** base) {
+  if (!x || !base) return fail(DSM_E_ARG, "NULL argument");
+  *base = x->local;
+  return 0;
+}
+
+int dsm_xchg_connect_ipc(dsm_xchg* x, const void* handles) {
+  if (!x || !handles) return fail(DSM_E_ARG, "NULL argument");
+  if (x->connected) return fail(DSM_E_ARG, "exchange already connected");
+  std::lock_guard<std::mutex> g(x->ctx->mu);
+  USE_DEVICE(x->ctx->device);
+  const cudaIpcMemHandle_t* h = static_cast<const cudaIpcMemHandle_t*>(handles);
+  for (uint32_t r = 0; r < x->world; ++r) {
+    if (r == x->rank) continue;
+    void* p = nullptr;
+    cudaError_t e = cudaIpcOpenMemHandle(&p, h[r], cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      for (uint32_t q = 0; q < r; ++q)
+        if (x->opened[q]) { cudaIpcCloseMemHandle(x->peers.data[q]); x->opened[q] = false; }
+      (void)cudaGetLastError();
+      return fail(DSM_E_CUDA, "cudaIpcOpenMemHandle: %s", cudaGetErrorString(e));
+    }
+    x->opened[r] = true;
+    xchg_wire(x, r, static_cast<char*>(p));
+  }
+  x->connected = true;
+  return 0;
+}
+
+int dsm_xchg_connect_ptrs(dsm_xchg* x, void* const* bases) {
+  if (!x || !bases) return fail(DSM_E_ARG, "NULL argument");
+  if (x->connected) return fail(DSM_E_ARG, "exchange already connected");
+  for (uint32_t r = 0; r < x->world; ++r) {
+    if (r == x->rank) continue;
+    if (!bases[r]) return fail(DSM_E_ARG, "NULL peer base");
+    xchg_wire(x, r, static_cast<char*>(bases[r]));
+  }
+  x->connected = true;
+  return 0;
+}
+
+int dsm_xchg_all_gather_dev(dsm_xchg* x, const void* d_src, uint64_t bytes, const void** d_gathered,
+                            uint64_t* slot_stride_bytes) {
+  if (!x || !d_src || !d_gathered) return fail(DSM_E_ARG, "NULL argument");
+  if (!x->connected && x->world > 1) return fail(DSM_E_ARG, "exchange not connected");
+  if (bytes == 0 || bytes % 16 || bytes > x->slot_bytes) return fail(DSM_E_ARG, "bytes must be a multiple of 16 within the slot");
+  if (reinterpret_cast<uintptr_t>(d_src) % 16) return fail(DSM_E_ARG, "source must be 16-byte aligned");
+  dsm_ctx* ctx = x->ctx;
+  std::lock_guard<std::mutex> g(ctx->mu);
+  USE_DEVICE(ctx->device);
+  const uint32_t epoch = ++x->epoch, parity = epoch & 1;
+  XchgPushParams p;
+  p.peers = x->peers;
+  p.src = static_cast<const uint4*>(d_src);
+  p.n_vec = (uint32_t)(bytes / 16);
+  p.world = x->world;
+  p.rank = x->rank;
+  p.parity = parity;
+  p.epoch = epoch;
+  p.slot_bytes = x->slot_bytes;
+  p.ticket = reinterpret_cast<uint32_t*>(x->local + x->ticket_off);
+  uint32_t chunks = (p.n_vec + 1023) / 1024;
+  const uint32_t most = std::max(1u, 2u * (uint32_t)ctx->sm_count / x->world);
+  if (chunks > most) chunks = most;
+  k_xchg_push<<<dim3(chunks, x->world), 256, 0, ctx->stream>>>(p);
+  CK(cudaGetLastError());
+  k_xchg_wait<<<1, 32, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(x->local + x->flags_off), x->world, parity,
+                                          epoch, 5ull * 1000 * 1000 * 1000,
+                                          reinterpret_cast<uint32_t*>(x->local + x->err_off));
+  CK(cudaGetLastError());
+  ctx->launches += 2;
+  *d_gathered = x->local + (size_t)parity * x->world * x->slot_bytes;
+  if (slot_stride_bytes) *slot_stride_bytes = x->slot_bytes;
+  return 0;
+}
+
+int dsm_xchg_status(dsm_xchg* x, uint32_t* waited_for_rank_plus_1) {
+  if (!x || !waited_for_rank_plus_1) return fail(DSM_E_ARG, "NULL argument");
+  std::lock_guard<std::mutex> g(x->ctx->mu);
+  USE_DEVICE(x->ctx->device);
+  CK(cudaMemcpyAsync(waited_for_rank_plus_1, x->local + x->err_off, 4, cudaMemcpyDeviceToHost, x->ctx->stream));
+  CK(cudaStreamSynchronize(x->ctx->stream));
+  return 0;
+}
+
+int dsm_xchg_destroy(dsm_xchg* x) {
+  if (!x) return 0;
+  DeviceGuard guard_(x->ctx->device);
+  cudaStreamSynchronize(x->ctx->stream);
+  for (uint32_t r = 0; r < x->world; ++r)
+    if (x->opened[r]) cudaIpcCloseMemHandle(x->peers.data[r]);
+  cudaFree(x->local);
+  delete x;
   return 0;
 }
 

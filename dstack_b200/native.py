@@ -29,7 +29,10 @@ EXPORTS = [
     "dsm_table_set_source_map", "dsm_match_topk_raw", "dsm_jobs_pack_dev", "dsm_match_indices",
     "dsm_match_topk_raw_src", "dsm_match_topk_cols", "dsm_reserve",
     "dsm_table_patch_rows",
+    "dsm_xchg_create", "dsm_xchg_local_base", "dsm_xchg_connect_ipc", "dsm_xchg_connect_ptrs",
+    "dsm_xchg_all_gather_dev", "dsm_xchg_status", "dsm_xchg_destroy",
 ]
+IPC_HANDLE_BYTES = 64  # DSM_IPC_HANDLE_BYTES
 N_PACK_DICTS = 7  # cpu, memory, disk, gpu count, gpu memory, gpu total, compute capability
 
 # dsm_raw_job (include/dsmatch.h): little-endian, 168 bytes
@@ -134,6 +137,13 @@ def lib() -> C.CDLL:
     L.dsm_merge_shards_interleaved_dev.argtypes = [vp, u32, u32, u32, vp, vp, vp, vp, C.c_size_t, vp, u32,
                                                    vp, vp, vp, vp]
     L.dsm_gather_price_dev.argtypes = [vp, vp, vp, u32, vp]
+    L.dsm_xchg_create.argtypes = [vp, u32, u32, u64, C.POINTER(vp), vp]
+    L.dsm_xchg_local_base.argtypes = [vp, C.POINTER(vp)]
+    L.dsm_xchg_connect_ipc.argtypes = [vp, vp]
+    L.dsm_xchg_connect_ptrs.argtypes = [vp, C.POINTER(vp)]
+    L.dsm_xchg_all_gather_dev.argtypes = [vp, vp, u64, C.POINTER(vp), C.POINTER(u64)]
+    L.dsm_xchg_status.argtypes = [vp, C.POINTER(u32)]
+    L.dsm_xchg_destroy.argtypes = [vp]
     L.dsm_sync.argtypes = [vp]
     L.dsm_host_alloc.argtypes = [C.c_size_t, C.POINTER(vp)]
     L.dsm_host_free.argtypes = [vp]

@@ -1,10 +1,14 @@
-"""Catalog sharded over the GPUs of one node: one process per GPU, NCCL for the one exchange.
+"""Catalog sharded over the GPUs of one node: one process per GPU, one exchange per step.
 
 Rank r holds a contiguous range of the global result order (stable sort of the source list by
 ``(not available, price)``, the order ``server/services/backends/__init__.py:449-451``
 produces) as its own device table with its own dictionaries; job records are replicated.  A
-step is: local ``dsm_match_topk_dev`` -> ``dsm_gather_price_dev`` -> ONE ``all_gather`` of a per-shard
-record (first-k rows, counts, max rows and their prices) -> a merge kernel.  By default the result
+step is: local ``dsm_match_topk_dev`` -> ``dsm_gather_price_dev`` -> ONE all-gather of a per-shard
+record (first-k rows, counts, max rows and their prices) -> a merge kernel.  The all-gather is the
+library's own peer exchange (``dsm_xchg_*``: every rank stores its record straight into its peers'
+IPC-mapped buffers over NVLink and raises a flag; ``exchange="p2p"``) with NCCL's
+``all_gather_into_tensor`` as the fallback when the ranks cannot map each other (``"nccl"``);
+``torch.distributed`` carries the set-up (handles, sizes) either way.  By default the result
 order is dealt out to the ranks in chunks of 1024 positions (``dsm_merge_shards_interleaved_dev`` keeps
 the k smallest global positions), which balances the ranks; with ``chunk_rows=0`` every rank holds
 one contiguous range, the merge is a concatenation (``dsm_merge_shards_strided_dev``) and the total
@@ -89,9 +93,11 @@ class ShardedMatcher:
     """Device path.  ``torch`` supplies device memory, the stream and the process group only."""
 
     def __init__(self, full: OfferColumns, *, rank: int, world: int, device: int, order: Optional[np.ndarray] = None,
-                 chunk_rows: int = 1024):
+                 chunk_rows: int = 1024, exchange: str = "p2p"):
         """``chunk_rows > 0`` deals the result order out in chunks (balanced shards, the default);
-        ``0`` gives every rank one contiguous range."""
+        ``0`` gives every rank one contiguous range.  ``exchange``: ``"p2p"`` (peer stores over
+        NVLink, NCCL if the ranks cannot map each other's memory) or ``"nccl"``; what a batch
+        shape ended up with is ``self.exchange_used`` after :meth:`prepare`."""
         import torch
         import torch.distributed as dist
 
@@ -104,6 +110,12 @@ class ShardedMatcher:
         self.order = rank_order(full) if order is None else order
         self.full = full
         self.chunk_rows = chunk_rows
+        if exchange not in ("p2p", "nccl"):
+            raise ValueError(f"exchange must be 'p2p' or 'nccl', not {exchange!r}")
+        self.exchange = exchange
+        self.exchange_used = "none" if world == 1 else "nccl"
+        self.exchange_note = ""
+        self._xchg = None
         self.positions = shard_positions(self.order, rank, world, chunk_rows) if world > 1 else None
         cols = subset_columns(full, self.positions) if world > 1 else full
         self.table: EncodedTable = encode_table(cols)
@@ -141,21 +153,72 @@ class ShardedMatcher:
         w_head = (w_idx + 2 * w_cnt + 1) // 2 * 2          # keep the f64 part 8-byte aligned
         words = w_head + 2 * j
         b["words"] = words
-        rec_out = torch.empty((words,), dtype=torch.int32, device=dev)
+        rec_out = torch.empty(((words + 3) // 4 * 4,), dtype=torch.int32, device=dev)  # whole 16-byte units
         b["out"] = rec_out
         b["idx"] = rec_out[:w_idx].view(j, k)
         b["cnt"] = rec_out[w_idx:w_idx + w_cnt]
         b["max"] = rec_out[w_idx + w_cnt:w_idx + 2 * w_cnt]
-        b["mp"] = rec_out[w_head:].view(torch.float64)
+        b["mp"] = rec_out[w_head:w_head + 2 * j].view(torch.float64)
         if self.world > 1:
             w = self.world
-            b["g_out"] = torch.empty((w, words), dtype=torch.int32, device=dev)
+            b["g_out"] = torch.empty((w, rec_out.numel()), dtype=torch.int32, device=dev)
             b["o_idx"] = torch.empty((j, k), dtype=torch.int64, device=dev)
             b["o_cnt"] = torch.empty((j,), dtype=torch.int64, device=dev)
             b["o_max"] = torch.empty((j,), dtype=torch.int64, device=dev)
             b["o_mp"] = torch.empty((j,), dtype=torch.float64, device=dev)
+            self._close_exchange()
+            if self.exchange == "p2p":
+                self._open_exchange(4 * rec_out.numel())
         self._bufs = b
         return b
+
+    def _open_exchange(self, nbytes: int) -> None:
+        """Collective: every rank creates its exchange buffer, the IPC handles travel through
+        ``torch.distributed``, every rank maps its peers; all or none use it."""
+        torch, dist, native = self.torch, self.dist, self.native
+        lib = native.lib()
+        handle = (C.c_ubyte * native.IPC_HANDLE_BYTES)()
+        x = C.c_void_p()
+        rc = lib.dsm_xchg_create(self.matcher.handle, self.world, self.rank, nbytes, C.byref(x), handle)
+        note = "" if rc == 0 else lib.dsm_last_error().decode(errors="replace")
+        mine = torch.tensor(list(bytes(handle)), dtype=torch.uint8, device=self.dev)
+        every = torch.empty((self.world, native.IPC_HANDLE_BYTES), dtype=torch.uint8, device=self.dev)
+        dist.all_gather_into_tensor(every, mine)
+        if rc == 0:
+            blob = every.cpu().numpy().tobytes()
+            rc = lib.dsm_xchg_connect_ipc(x, blob)
+            if rc != 0:
+                note = lib.dsm_last_error().decode(errors="replace")
+        ok = torch.tensor([1 if rc == 0 else 0], dtype=torch.int32, device=self.dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if int(ok.item()) == 1:
+            self._xchg = x
+            self.exchange_used = "p2p"
+            return
+        # some rank could not map its peers: nobody uses the exchange (nobody has pushed yet)
+        if x.value:
+            dist.barrier()
+            lib.dsm_xchg_destroy(x)
+        else:
+            dist.barrier()
+        self.exchange_used = "nccl"
+        self.exchange_note = note or "a peer could not map this rank's buffer"
+
+    def _close_exchange(self) -> None:
+        if self._xchg is not None:
+            self.stream.synchronize()
+            self.dist.barrier()  # peers may still be storing into this rank's buffer
+            self.native.lib().dsm_xchg_destroy(self._xchg)
+            self._xchg = None
+            self.exchange_used = "nccl"
+
+    def exchange_status(self) -> int:
+        """0 = every wait of the peer exchange saw all ranks; else 1 + a rank that was missing."""
+        if self._xchg is None:
+            return 0
+        bad = C.c_uint32()
+        self.native.check(self.native.lib().dsm_xchg_status(self._xchg, C.byref(bad)))
+        return int(bad.value)
 
     def step(self, marks=None) -> None:
         """One batch on the resident buffers; asynchronous on ``self.stream`` (call under it).
@@ -171,13 +234,19 @@ class ShardedMatcher:
             dist = self.dist
             check(lib.dsm_gather_price_dev(h, self.device_table.handle, b["max"].data_ptr(), b["j"], b["mp"].data_ptr()))
             mark(1)
-            dist.all_gather_into_tensor(b["g_out"], b["out"])  # the one exchange of the step
+            # the one exchange of the step
+            if self._xchg is not None:
+                gathered, stride = C.c_void_p(), C.c_uint64()
+                check(lib.dsm_xchg_all_gather_dev(self._xchg, b["out"].data_ptr(), 4 * b["out"].numel(),
+                                                  C.byref(gathered), C.byref(stride)))
+                base_ptr, stride_bytes = gathered.value, stride.value
+            else:
+                dist.all_gather_into_tensor(b["g_out"], b["out"])
+                base_ptr, stride_bytes = b["g_out"].data_ptr(), 4 * b["out"].numel()
             mark(2)
-            g = b["g_out"]
             w_idx, w_cnt = b["j"] * b["k"], b["j"]
-            base_ptr = g.data_ptr()
             fields = (base_ptr, base_ptr + 4 * w_idx, base_ptr + 4 * (w_idx + w_cnt),
-                      base_ptr + 4 * (b["words"] - 2 * b["j"]), 4 * b["words"])
+                      base_ptr + 4 * (b["words"] - 2 * b["j"]), stride_bytes)
             outs = (b["o_idx"].data_ptr(), b["o_cnt"].data_ptr(), b["o_max"].data_ptr(), b["o_mp"].data_ptr())
             if self.chunk_rows > 0:
                 check(lib.dsm_merge_shards_interleaved_dev(h, self.world, b["j"], b["k"], *fields,
@@ -209,5 +278,6 @@ class ShardedMatcher:
         return src, b["o_cnt"].cpu().numpy(), b["o_mp"].cpu().numpy()
 
     def close(self) -> None:
+        self._close_exchange()
         self.device_table.close()
         self.matcher.close()

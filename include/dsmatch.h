@@ -413,6 +413,38 @@ int dsm_merge_shards_interleaved_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n
 int dsm_gather_price_dev(dsm_ctx* ctx, const dsm_table* t, const uint32_t* d_rows, uint32_t n,
                          double* d_out);
 
+/* ---- peer exchange: the sharded step's all-gather over NVLink peer memory ---------------------
+ *
+ * One dsm_xchg per rank (one rank per GPU; the ranks may be processes or threads).  Every rank
+ * owns a device buffer [2][world][slot] that its peers map: across processes with the CUDA IPC
+ * handle dsm_xchg_create returns (exchange the world handles with whatever the host has --
+ * torch.distributed, MPI, a pipe -- and pass all of them to dsm_xchg_connect_ipc), inside one
+ * process with the peers' base pointers (dsm_xchg_local_base -> dsm_xchg_connect_ptrs).
+ *
+ * dsm_xchg_all_gather_dev enqueues, on the context's stream, (1) a kernel that stores the
+ * `bytes` at d_src into slot[rank] of every rank's buffer and then raises this rank's flag on
+ * every peer, (2) a kernel that waits until the flags of all ranks show this call's epoch.  Work
+ * enqueued after it may read *d_gathered = [world][*slot_stride_bytes]: the records of all ranks
+ * in rank order, in local memory.  Every rank must make the same sequence of calls; buffers
+ * alternate between two parities, so a rank may run at most one call ahead of its peers, which
+ * the wait itself guarantees.  The wait gives up after 5 s (a dead peer must not leave this GPU
+ * spinning): dsm_xchg_status synchronises the stream and returns 0 if no wait ever timed out,
+ * else 1 + the highest rank that was missing -- the gathered data of that call is then undefined.
+ * Destroy only after every rank has finished its last call (host barrier).
+ * Replaces the NCCL all_gather of the step in dstack_b200/sharded.py; no counterpart in the
+ * reference, which runs one scheduler process against one catalog. */
+typedef struct dsm_xchg dsm_xchg;
+#define DSM_IPC_HANDLE_BYTES 64
+int dsm_xchg_create(dsm_ctx* ctx, uint32_t world, uint32_t rank, uint64_t bytes_per_rank, dsm_xchg** out,
+                    void* ipc_handle_out /* DSM_IPC_HANDLE_BYTES, may be NULL */);
+int dsm_xchg_local_base(dsm_xchg* x, void** base);
+int dsm_xchg_connect_ipc(dsm_xchg* x, const void* handles /* [world][DSM_IPC_HANDLE_BYTES] */);
+int dsm_xchg_connect_ptrs(dsm_xchg* x, void* const* bases /* [world], own entry ignored */);
+int dsm_xchg_all_gather_dev(dsm_xchg* x, const void* d_src, uint64_t bytes, const void** d_gathered,
+                            uint64_t* slot_stride_bytes);
+int dsm_xchg_status(dsm_xchg* x, uint32_t* waited_for_rank_plus_1);
+int dsm_xchg_destroy(dsm_xchg* x);
+
 /* ---- utilities ------------------------------------------------------------------------ */
 
 /* Size the context's scratch for batches of up to n_jobs jobs with this layout against this
