@@ -489,16 +489,19 @@ static int run_match(dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L, cons
     const dim3 grid(wide ? n_jobs : (n_jobs + 7) / 8);
     const uint32_t sm_bytes = wide ? chunk_bytes : 8u * chunk_bytes;
 #define EXTRACT(W, R, L, S) k_extract<W, R, L, S><<<grid, 256, sm_bytes, ctx->stream>>>(gp)
-    const bool shortw = !wide && pl.slots <= 512u && pl.wps <= 8u;  // counts in registers, records in one batch
+    const bool shortw = !wide && pl.slots <= 512u;  // counts in registers, needed slots known before any further load
     if (wide) {
-      if (row32) { if (has_lut) EXTRACT(8, true, true, false); else EXTRACT(8, true, false, false); }
-      else       { if (has_lut) EXTRACT(8, false, true, false); else EXTRACT(8, false, false, false); }
+      if (row32) { if (has_lut) EXTRACT(8, true, true, 0); else EXTRACT(8, true, false, 0); }
+      else       { if (has_lut) EXTRACT(8, false, true, 0); else EXTRACT(8, false, false, 0); }
+    } else if (shortw && pl.wps <= 8u) {  // ... and their records in one batch
+      if (row32) { if (has_lut) EXTRACT(1, true, true, 1); else EXTRACT(1, true, false, 1); }
+      else       { if (has_lut) EXTRACT(1, false, true, 1); else EXTRACT(1, false, false, 1); }
     } else if (shortw) {
-      if (row32) { if (has_lut) EXTRACT(1, true, true, true); else EXTRACT(1, true, false, true); }
-      else       { if (has_lut) EXTRACT(1, false, true, true); else EXTRACT(1, false, false, true); }
+      if (row32) { if (has_lut) EXTRACT(1, true, true, 2); else EXTRACT(1, true, false, 2); }
+      else       { if (has_lut) EXTRACT(1, false, true, 2); else EXTRACT(1, false, false, 2); }
     } else {
-      if (row32) { if (has_lut) EXTRACT(1, true, true, false); else EXTRACT(1, true, false, false); }
-      else       { if (has_lut) EXTRACT(1, false, true, false); else EXTRACT(1, false, false, false); }
+      if (row32) { if (has_lut) EXTRACT(1, true, true, 0); else EXTRACT(1, true, false, 0); }
+      else       { if (has_lut) EXTRACT(1, false, true, 0); else EXTRACT(1, false, false, 0); }
     }
 #undef EXTRACT
     CK(cudaGetLastError());

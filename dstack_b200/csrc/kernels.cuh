@@ -841,12 +841,18 @@ __global__ void __launch_bounds__(MATCH_THREADS, MATCH_CTAS_PER_SM) k_match(cons
 // all 8 warps; the rest is done by the first of them).
 // ------------------------------------------------------------------------------------------
 
-// SHORT (one warp per job, at most 512 slots of at most 8 windows): the slot counts stay in
-// registers after pass 1, so the slots that hold the first k matches are known exactly -- those
-// whose prefix count is below k -- before any further load; their window records are then fetched
-// in ONE batch (lane i = i-th such slot) instead of chunk by chunk with a dependent round trip each.
-template <int WPJ, bool ROW32, bool HAS_LUT, bool SHORT>
-__global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
+// SHORT != 0 (one warp per job, at most 512 slots; 1: of at most 8 windows, 2: longer): lane l
+// keeps the counts of slots 16l .. 16l+15 in registers (four 128-bit loads), so one sequential
+// pass per lane and two warp scans give the total, the last non-empty slot of each segment and
+// -- exactly -- the slots that hold the first k matches: the non-empty ones whose prefix count is
+// below k.  Their bounds and, when a slot has at most 8 windows, their window records are then
+// fetched in ONE batch (lane i = i-th such slot) instead of chunk by chunk with a dependent round
+// trip each.
+#ifndef EXTRACT_CTAS_PER_SM
+#define EXTRACT_CTAS_PER_SM 4
+#endif
+template <int WPJ, bool ROW32, bool HAS_LUT, int SHORT>
+__global__ void __launch_bounds__(256, EXTRACT_CTAS_PER_SM) k_extract(const ExtractParams p) {
   static_assert(!SHORT || WPJ == 1, "the batched walk is for one warp per job");
   constexpr uint32_t JPC = 8u / WPJ;  // jobs per CTA
   constexpr uint32_t FULL = 0xFFFFFFFFu;
@@ -870,25 +876,51 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
 #endif
   uint32_t* csum = chunk_sums + jl * n_chunks;
 
-  uint32_t creg[SHORT ? 16 : 1] = {0};  // SHORT: this lane's slot of every chunk
+  uint32_t creg[SHORT ? 16 : 1] = {0};  // SHORT: the counts of slots 16 * lane .. 16 * lane + 15
+  uint32_t need_mask = 0, need_off = 0, n_need = 0;  // SHORT: this lane's needed slots, their rank, all of them
   if constexpr (SHORT) {
+    // n_slots is a multiple of 8 (8 warps per piece), so a job's counts are 16-byte aligned and
+    // every uint4 lies wholly inside or outside them
+    const uint4* c4 = reinterpret_cast<const uint4*>(cnt) + lane * 4u;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint4 v = make_uint4(0u, 0u, 0u, 0u);
+      if (live && lane * 16u + q * 4u < n_slots) v = c4[q];
+      creg[q * 4 + 0] = v.x; creg[q * 4 + 1] = v.y; creg[q * 4 + 2] = v.z; creg[q * 4 + 3] = v.w;
+    }
+    uint32_t lane_tot = 0;
+    int la = -1, lb = -1;  // slots ascend with u: the last assignment is the lane's last non-empty slot
 #pragma unroll
     for (int u = 0; u < 16; ++u) {
-      const uint32_t s = u * 32u + lane;
-      creg[u] = (live && s < n_slots) ? cnt[s] : 0u;
+      const uint32_t sl = lane * 16u + u;
+      lane_tot += creg[u];
+      if (creg[u] != 0u) {
+        if (sl < p.slots_a) la = (int)sl;
+        else lb = (int)sl;
+      }
     }
-    uint32_t tot = 0;
-    int ls_a = -1, ls_b = -1;
+    uint32_t incl = lane_tot;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t y = __shfl_up_sync(FULL, incl, d);
+      if (lane >= (uint32_t)d) incl += y;
+    }
+    const uint32_t tot = __shfl_sync(FULL, incl, 31);
+    const int ls_a = __reduce_max_sync(FULL, la), ls_b = __reduce_max_sync(FULL, lb);
+    uint32_t run = incl - lane_tot;  // matches in the slots before this lane's
 #pragma unroll
     for (int u = 0; u < 16; ++u) {
-      if (u * 32u >= n_slots) break;  // warp-uniform
-      const uint32_t s = u * 32u + lane;
-      tot += __reduce_add_sync(FULL, creg[u]);
-      const uint32_t hit_a = __ballot_sync(FULL, creg[u] != 0 && s < p.slots_a);
-      const uint32_t hit_b = __ballot_sync(FULL, creg[u] != 0 && s >= p.slots_a);
-      if (hit_a) ls_a = (int)(u * 32u + 31u - __clz(hit_a));
-      if (hit_b) ls_b = (int)(u * 32u + 31u - __clz(hit_b));
+      if (creg[u] != 0u && run < p.k) need_mask |= 1u << u;
+      run += creg[u];
     }
+    uint32_t nincl = (uint32_t)__popc(need_mask);
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t y = __shfl_up_sync(FULL, nincl, d);
+      if (lane >= (uint32_t)d) nincl += y;
+    }
+    need_off = nincl - (uint32_t)__popc(need_mask);
+    n_need = __shfl_sync(FULL, nincl, 31);
     if (lane == 0) { red_total[warp] = tot; red_last_a[warp] = ls_a; red_last_b[warp] = ls_b; }
   } else {  // pass 1: totals of 32 slots at a time, last slot with a match per segment
     uint32_t tot = 0;
@@ -1045,70 +1077,99 @@ __global__ void __launch_bounds__(256, 4) k_extract(const ExtractParams p) {
   if (t_slot >= 0 && hl < t_nwin)
     t_rec = wr_job[((size_t)t_slot * p.wps + (t_nwin - 1u - hl)) * JPG];
 
-  // ---- first k matches, SHORT: the needed slots from the counts in registers, their records in
-  // one batch of loads, then the same queue of windows as below
+  // ---- first k matches, SHORT: the needed slots are known from the counts in registers; lane i
+  // fetches the bounds (and, for slots of at most 8 windows, the window records) of the i-th of
+  // them, 32 slots a round; a longer slot's records are fetched 256 windows at a time and the
+  // non-empty ones compacted into a list.  Either way the windows reach the queue 8 at a time, so
+  // that there is one flush site in the loop.
   if constexpr (SHORT) {
     __shared__ uint32_t s_need[8][32];
     uint32_t* need = s_need[warp];
-    uint32_t round_lo = 0;  // needed slots (in row order) handled by earlier rounds
-    bool more = true;
-    while (more && have < k) {
-      uint32_t base = 0, n_need = 0;
-#pragma unroll
-      for (int u = 0; u < 16; ++u) {
-        if (u * 32u >= n_slots) break;  // warp-uniform
-        const uint32_t v = creg[u];
-        uint32_t incl = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-          const uint32_t y = __shfl_up_sync(FULL, incl, d);
-          if (lane >= (uint32_t)d) incl += y;
+    constexpr bool short_slots = SHORT == 1;  // SHORT == 2: slots of more than 8 windows
+    for (uint32_t round_lo = 0; round_lo < n_need && have < k; round_lo += 32u) {
+      {
+        uint32_t m = need_mask, pos = need_off - round_lo;  // wraps for slots of earlier rounds: >= 32
+        while (m != 0u) {
+          const uint32_t u = (uint32_t)__ffs(m) - 1u;
+          m &= m - 1u;
+          if (pos < 32u) need[pos] = lane * 16u + u;
+          ++pos;
         }
-        const bool nd = v != 0u && base + incl - v < k;  // matches before this slot: fewer than k
-        const uint32_t nm = __ballot_sync(FULL, nd);
-        const uint32_t pos = n_need + __popc(nm & lt_mask);
-        if (nd && pos >= round_lo && pos < round_lo + 32u) need[pos - round_lo] = u * 32u + lane;
-        n_need += __popc(nm);
-        base += __shfl_sync(FULL, incl, 31);
       }
       __syncwarp();
-      const uint32_t n_here = min(32u, n_need - min(n_need, round_lo));
-      more = n_need > round_lo + 32u;
-      // lane i: bounds and window records of the i-th needed slot of this round
+      const uint32_t n_here = min(32u, n_need - round_lo);
       uint32_t my_s = 0, my_b0 = 0, my_b1 = 0;
       uint32_t mk[8] = {0, 0, 0, 0, 0, 0, 0, 0};
       if (lane < n_here) {
         my_s = need[lane];
         my_b0 = p.slot_start[my_s];
         my_b1 = p.slot_start[my_s + 1];
-        const uint32_t* wr = wr_job + (size_t)my_s * p.wps * JPG;
+        if constexpr (short_slots) {
+          const uint32_t* wr = wr_job + (size_t)my_s * p.wps * JPG;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < p.wps ? wr[(size_t)w * JPG] : 0u;
-        const uint32_t my_nwin = (my_b1 - my_b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+          for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < p.wps ? wr[(size_t)w * JPG] : 0u;
+          const uint32_t my_nwin = (my_b1 - my_b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < my_nwin ? mk[w] : 0u;  // records past the slot's end are stale
+          for (int w = 0; w < 8; ++w) mk[w] = (uint32_t)w < my_nwin ? mk[w] : 0u;  // records past the slot's end are stale
+        }
       }
       __syncwarp();
       for (uint32_t i = 0; i < n_here && have < k; ++i) {
         const uint32_t sl = __shfl_sync(FULL, my_s, i);
         const uint32_t b0 = __shfl_sync(FULL, my_b0, i), b1 = __shfl_sync(FULL, my_b1, i);
         const uint32_t cut = sl >= p.slots_a ? cut_b : cut_a;
+        const uint32_t n_win = (b1 - b0 + WIN_BLOCKS - 1) / WIN_BLOCKS;
+        const uint32_t* wr = wr_job + (size_t)sl * p.wps * JPG;
+        // w0: first window of the batch of records at hand (8 in mk, or up to 256 in wlist)
+        for (uint32_t w0 = 0; w0 < (short_slots ? 1u : n_win) && have < k; w0 += 256u) {
+          uint32_t n_list = 8u;
+          if constexpr (!short_slots) {
+            uint32_t wv[8];
 #pragma unroll
-        for (int w = 0; w < 8; ++w) {
-          const uint32_t R = __shfl_sync(FULL, mk[w], i);
-          if (R != 0) {
-            const uint32_t bs = b0 + (uint32_t)w * WIN_BLOCKS;
-            push(bs, min(bs + WIN_BLOCKS, b1) - bs, R, cut);
+            for (int u = 0; u < 8; ++u) {
+              const uint32_t w = w0 + u * 32 + lane;
+              wv[u] = w < n_win ? wr[(size_t)w * JPG] : 0u;
+            }
+            n_list = 0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+              const uint32_t nz = __ballot_sync(FULL, wv[u] != 0);
+              if (wv[u] != 0) {
+                const uint32_t at = n_list + __popc(nz & lt_mask);
+                wlist[at][0] = w0 + u * 32 + lane;
+                wlist[at][1] = wv[u];
+              }
+              n_list += __popc(nz);
+            }
+            __syncwarp();
           }
+          for (uint32_t l0 = 0; l0 < n_list && have < k; l0 += 8u) {
+#pragma unroll
+            for (int w = 0; w < 8; ++w) {
+              uint32_t win = (uint32_t)w, R = 0;
+              if constexpr (short_slots) {
+                R = __shfl_sync(FULL, mk[w], i);
+              } else {
+                const bool in = l0 + w < n_list;
+                win = in ? wlist[l0 + w][0] : 0u;
+                R = in ? wlist[l0 + w][1] : 0u;
+              }
+              if (R != 0) {
+                const uint32_t bs = b0 + win * WIN_BLOCKS;
+                push(bs, min(bs + WIN_BLOCKS, b1) - bs, R, cut);
+              }
+            }
+            if (n_pend > EXTRACT_PENDING - 8u || q_total >= 32u * EXTRACT_LANE_ROWS) flush();
+          }
+          __syncwarp();  // before wlist is filled again
         }
-        if (n_pend > EXTRACT_PENDING - 8u || q_total >= 32u * EXTRACT_LANE_ROWS) flush();
       }
       flush();
-      round_lo += 32u;
+      __syncwarp();  // before need[] is filled again
     }
   }
   // ---- first k matches, general: walk slots and windows in row order, skipping empty ones
-  for (uint32_t c0 = 0; !SHORT && c0 < n_chunks && have < k; c0 += 32) {
+  for (uint32_t c0 = 0; SHORT == 0 && c0 < n_chunks && have < k; c0 += 32) {
     const uint32_t cs = c0 + lane < n_chunks ? csum[c0 + lane] : 0u;
     uint32_t open_ch = __ballot_sync(FULL, cs != 0);
     while (open_ch && have < k) {  // all loops below are warp-uniform
