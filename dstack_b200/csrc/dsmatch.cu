@@ -1156,9 +1156,14 @@ int dsm_merge_shards_interleaved_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n
   if (shard_stride_bytes == 0 || shard_stride_bytes % 8) return fail(DSM_E_ARG, "shard stride must be a non-zero multiple of 8");
   std::lock_guard<std::mutex> g(ctx->mu);
   USE_DEVICE(ctx->device);
-  k_merge_shards_interleaved<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
-      n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
-      reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
+  if (n_shards * k <= MERGE_WARP_CANDIDATES)  // a warp per job, all candidates ranked at once
+    k_merge_shards_interleaved_warp<<<(n_jobs + 7) / 8, 256, 8u * n_shards * k * sizeof(uint64_t), ctx->stream>>>(
+        n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
+        reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
+  else
+    k_merge_shards_interleaved<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
+        n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
+        reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
   CK(cudaGetLastError());
   ctx->launches++;
   return 0;
