@@ -100,6 +100,7 @@ struct dsm_ctx {
   bool no_direct = false;    // DSM_NO_DIRECT_FILL
   bool force_direct = false; // DSM_FORCE_DIRECT_FILL
   uint32_t units_per_cta = 0;// DSM_UNITS_PER_CTA
+  uint32_t force_wpw = 0;    // DSM_WPW: windows per warp and unit
   std::mutex mu;
   uint64_t launches;
   // optional timing of the match kernel alone (bench.py's roofline): event pairs recorded
@@ -281,6 +282,7 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     const unsigned long long fill = wpw_for(resident);  // the share that gives every CTA one unit
     wpw = fill < MIN_WPW ? fill : MIN_WPW;
   }
+  if (ctx->force_wpw) wpw = ctx->force_wpw;
   pl.pc.n_groups = pl.n_groups;
   pl.pc.n_blocks = pl.n_blocks;
   pl.pc.split_block = pl.split_block;
@@ -563,6 +565,7 @@ int dsm_ctx_create(int device, void* stream, dsm_ctx** out) {
   c->no_direct = getenv("DSM_NO_DIRECT_FILL") != nullptr;
   c->force_direct = getenv("DSM_FORCE_DIRECT_FILL") != nullptr;
   if (const char* v = getenv("DSM_UNITS_PER_CTA")) c->units_per_cta = (uint32_t)atoi(v);
+  if (const char* v = getenv("DSM_WPW")) c->force_wpw = (uint32_t)atoi(v);
   *out = c;
   return 0;
 }
@@ -1156,14 +1159,9 @@ int dsm_merge_shards_interleaved_dev(dsm_ctx* ctx, uint32_t n_shards, uint32_t n
   if (shard_stride_bytes == 0 || shard_stride_bytes % 8) return fail(DSM_E_ARG, "shard stride must be a non-zero multiple of 8");
   std::lock_guard<std::mutex> g(ctx->mu);
   USE_DEVICE(ctx->device);
-  if (n_shards * k <= MERGE_WARP_CANDIDATES)  // a warp per job, all candidates ranked at once
-    k_merge_shards_interleaved_warp<<<(n_jobs + 7) / 8, 256, 8u * n_shards * k * sizeof(uint64_t), ctx->stream>>>(
-        n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
-        reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
-  else
-    k_merge_shards_interleaved<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
-        n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
-        reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
+  k_merge_shards_interleaved<<<(n_jobs + 127) / 128, 128, 0, ctx->stream>>>(
+      n_shards, n_jobs, k, d_idx0, d_cnt0, d_max0, d_maxprice0, shard_stride_bytes,
+      reinterpret_cast<const uint2*>(d_shard_geom), chunk_rows, d_idx_out, d_cnt_out, d_max_out, d_maxprice_out);
   CK(cudaGetLastError());
   ctx->launches++;
   return 0;

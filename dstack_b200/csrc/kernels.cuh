@@ -1387,8 +1387,8 @@ __global__ void k_merge_shards_interleaved(uint32_t n_shards, uint32_t n_jobs, u
   };
   auto position = [&](uint32_t s, uint32_t row) -> uint64_t {
     const uint2 g = geom[s];
-    const uint64_t q = row < g.x ? row : (uint64_t)g.y + (row - g.x);
-    return ((q / chunk_rows) * n_shards + s) * chunk_rows + q % chunk_rows;
+    const uint32_t q = row < g.x ? row : g.y + (row - g.x);  // < the shard's row count: 32-bit division
+    return ((uint64_t)(q / chunk_rows) * n_shards + s) * chunk_rows + q % chunk_rows;
   };
   uint64_t head[32];  // global position of each shard's next unread entry, ~0 = exhausted
   uint8_t used[32];
@@ -1420,97 +1420,6 @@ __global__ void k_merge_shards_interleaved(uint32_t n_shards, uint32_t n_jobs, u
   cnt_out[job] = total;
   max_out[job] = best;
   maxprice_out[job] = (best == ~0ull) ? __longlong_as_double(0x7FF8000000000000LL) : best_price;
-}
-
-// The same merge with one warp per job, for n_shards * k <= MERGE_WARP_CANDIDATES: all candidate
-// positions go to shared memory at once, and because every shard's list ascends, the place of
-// candidate i of shard s in the merged order is i + (for every other shard) the number of its
-// entries below it -- a binary search each, no serial k-step selection.  Positions are unique, so
-// the places are too.  The max-price row: highest price, the lower shard on a tie, as above.
-#define MERGE_WARP_CANDIDATES 512
-__global__ void __launch_bounds__(256) k_merge_shards_interleaved_warp(
-    uint32_t n_shards, uint32_t n_jobs, uint32_t k, const uint32_t* idx_all, const uint32_t* cnt_all,
-    const uint32_t* max_all, const double* maxprice_all, size_t shard_stride_bytes, const uint2* geom,
-    uint32_t chunk_rows, uint64_t* idx_out, uint64_t* cnt_out, uint64_t* max_out, double* maxprice_out) {
-  constexpr uint32_t FULL = 0xFFFFFFFFu;
-  extern __shared__ uint64_t merge_pos[];  // [8 warps][n_shards * k]
-  const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-  const uint32_t job = blockIdx.x * 8u + warp;
-  if (job >= n_jobs) return;  // whole warps leave; no CTA-wide barrier below
-  const uint32_t n_cand = n_shards * k;
-  uint64_t* pos = merge_pos + (size_t)warp * n_cand;
-  auto field = [&](const void* base, uint32_t s) {
-    return reinterpret_cast<const char*>(base) + (size_t)s * shard_stride_bytes;
-  };
-  auto position = [&](uint32_t s, uint32_t row) -> uint64_t {
-    const uint2 g = geom[s];
-    const uint64_t q = row < g.x ? row : (uint64_t)g.y + (row - g.x);
-    return ((q / chunk_rows) * n_shards + s) * chunk_rows + q % chunk_rows;
-  };
-  // per shard (lane = shard): count, max row and its price
-  uint64_t total = 0, best = ~0ull;
-  double best_price = 0.0;
-  uint32_t my_cnt = 0;
-  if (lane < n_shards) {
-    my_cnt = reinterpret_cast<const uint32_t*>(field(cnt_all, lane))[job];
-    total = my_cnt;
-    const uint32_t m = reinterpret_cast<const uint32_t*>(field(max_all, lane))[job];
-    if (m != DSM_NO_ROW) {
-      best = position(lane, m);
-      best_price = reinterpret_cast<const double*>(field(maxprice_all, lane))[job];
-    }
-  }
-  uint32_t best_s = lane;
-#pragma unroll
-  for (int d = 16; d >= 1; d >>= 1) {
-    total += __shfl_xor_sync(FULL, total, d);
-    const uint64_t ob = __shfl_xor_sync(FULL, best, d);
-    const double op = __shfl_xor_sync(FULL, best_price, d);
-    const uint32_t os = __shfl_xor_sync(FULL, best_s, d);
-    const bool take = ob != ~0ull && (best == ~0ull || op > best_price || (op == best_price && os < best_s));
-    if (take) { best = ob; best_price = op; best_s = os; }
-  }
-  // candidates: entry i of shard s is valid while the shard has matches and the entry is a row
-  uint32_t n_valid = 0;
-  for (uint32_t c0 = 0; c0 < n_cand; c0 += 32u) {
-    const uint32_t c = c0 + lane;
-    uint64_t v = ~0ull;
-    const uint32_t s = min(c, n_cand - 1u) / k, i = c - s * k;
-    const uint32_t sc = __shfl_sync(FULL, my_cnt, s);  // every lane takes part; s < n_shards <= 32
-    if (c < n_cand) {
-      const uint32_t r = reinterpret_cast<const uint32_t*>(field(idx_all, s))[(size_t)job * k + i];
-      if (sc != 0u && r != DSM_NO_ROW) v = position(s, r);
-      pos[c] = v;
-    }
-    n_valid += __popc(__ballot_sync(FULL, v != ~0ull));
-  }
-  __syncwarp();
-  for (uint32_t c0 = 0; c0 < n_cand; c0 += 32u) {
-    const uint32_t c = c0 + lane;
-    if (c >= n_cand) break;
-    const uint64_t v = pos[c];
-    if (v == ~0ull) continue;
-    const uint32_t s = c / k;
-    uint32_t place = c - s * k;
-    for (uint32_t o = 0; o < n_shards; ++o) {
-      if (o == s) continue;
-      const uint64_t* l = pos + o * k;
-      uint32_t lo = 0, hi = k;  // first entry of shard o that is not below v (the ~0 tail never is)
-      while (lo < hi) {
-        const uint32_t mid = (lo + hi) >> 1;
-        if (l[mid] < v) lo = mid + 1;
-        else hi = mid;
-      }
-      place += lo;
-    }
-    if (place < k) idx_out[(size_t)job * k + place] = v;
-  }
-  for (uint32_t i = min(n_valid, k) + lane; i < k; i += 32u) idx_out[(size_t)job * k + i] = ~0ull;
-  if (lane == 0) {
-    cnt_out[job] = total;
-    max_out[job] = best;
-    maxprice_out[job] = (best == ~0ull) ? __longlong_as_double(0x7FF8000000000000LL) : best_price;
-  }
 }
 
 // ------------------------------------------------------------------------------------------

@@ -89,10 +89,8 @@ def test_interleaved_merge_with_not_available_segment_and_k50(matcher):
     _run(matcher, 5_000, 40, 50, 4, 128, seed=67)
 
 
-@pytest.mark.parametrize("world,k", [(8, 64), (8, 65), (3, 200), (32, 16), (32, 17)])
-def test_interleaved_merge_either_side_of_the_warp_kernel_limit(matcher, world, k):
-    """Up to 512 candidates per job (shards x k) a warp ranks them all at once; beyond that one
-    thread per job selects them one by one.  Same answer either way."""
+@pytest.mark.parametrize("world,k", [(8, 64), (3, 200), (32, 17)])
+def test_interleaved_merge_many_shards_or_long_lists(matcher, world, k):
     _run(matcher, 6_000, 70, k, world, 16, seed=71)
 
 
