@@ -273,7 +273,8 @@ def columns_from_pool_instances(instances: Sequence[Any], *, blocks_of: Optional
 @dataclass
 class JobFilter:
     """Everything one job asks of a row, after the reference's derivations
-    (``server/services/offers.py:46-82`` / ``pools.py:425-456``) have been applied."""
+    (``server/services/offers.py:46-82`` / ``pools.py:425-456``) have been applied.  Immutable
+    once it has been matched: ``job_columns`` keeps the table-independent numbers on the object."""
 
     query: QueryFilter = field(default_factory=QueryFilter)
     backend_types: Optional[Sequence[Any]] = None   # None = unconstrained
@@ -297,117 +298,107 @@ def _pair(lo, hi) -> Tuple[float, float]:
     return (math.nan if lo is None else float(lo), math.nan if hi is None else float(hi))
 
 
+_POOL_FORBID = FLAG_UNREACHABLE | FLAG_BLOCKS_UNKNOWN
+
+
+def _filter_scalars(f: JobFilter) -> Tuple[Tuple[float, ...], Optional[List[str]]]:
+    """The part of a filter's columns that does not depend on any table: 23 numbers (all exactly
+    representable as float64, ``nan`` = no bound) and the lower-cased GPU names.  Kept on the filter
+    object after the first use -- a pending job is matched again every scheduler pass -- so a
+    filter and its query are to be treated as immutable once matched (``dataclasses.replace``
+    gives a fresh filter)."""
+    q = f.query
+    if q.min_price is not None:
+        raise ValueError("min_price is not part of the dstack path (offers.py:117 sets max_price only)")
+    if q.max_compute_capability is not None:
+        raise ValueError("max_compute_capability is never set by dstack (offers.py:143-144)")
+    nan = math.nan
+    cc = q.min_compute_capability
+    if f.backend_types is not None:
+        off = 0
+        for b in f.backend_types:
+            off |= 1 << backend_code(b)
+        src = off | ((1 << BACKEND_CODES["dstack"]) if f.keep_dstack_backend else 0)
+    else:
+        off = src = 0xFFFFFFFF
+    req = FLAG_AUTO_DIVISIBLE if f.require_auto_divisible else 0
+    forbid, st_mask = 0, 0xFF
+    if f.shared is not None:  # pool filter (pools.py:460,484-488)
+        forbid |= _POOL_FORBID
+        if f.shared:
+            req |= FLAG_SHARED
+        else:
+            forbid |= FLAG_SHARED
+        if f.require_offer:
+            forbid |= FLAG_NO_OFFER
+        if f.status is not None:
+            st = f.status
+            st_mask = 1 << STATUS_CODES[st.value if hasattr(st, "value") else str(st)]
+    bounds = (q.min_cpu, q.max_cpu, q.min_memory, q.max_memory, q.min_disk_size, q.max_disk_size,
+              q.min_gpu_count, q.max_gpu_count, q.min_gpu_memory, q.max_gpu_memory,
+              q.min_total_gpu_memory, q.max_total_gpu_memory)
+    scalars = (nan if q.max_price is None else float(q.max_price), -1 if q.spot is None else (1 if q.spot else 0),
+               *[nan if v is None else float(v) for v in bounds],
+               vendor_code(q.gpu_vendor), -1 if cc is None else int(cc[0]) * 1000 + int(cc[1]),
+               off, src, 1 if f.exclude_not_available else 0, req, forbid, f.blocks, st_mask)
+    return scalars, (None if q.gpu_name is None else [n.lower() for n in q.gpu_name])
+
+
 def job_columns(table: EncodedTable, filters: Sequence[JobFilter]) -> JobColumns:
-    """Job filters -> columns.  One pass over the filter objects collecting plain Python values
-    (assigning numpy scalars one by one costs several times as much), arrays are built at the end."""
+    """Job filters -> columns.  One pass over the filter objects: the table-independent numbers
+    come from the filter (computed once per filter, see ``_filter_scalars``) and go into one
+    float64 array at the end; names, regions, instance types, zones, fleets and instance names are
+    looked up in this table's dictionaries."""
     j = len(filters)
     cols = {c.name: c for c in table.columns}
-    names = table.gpu_dict["names"]
-    nan = math.nan
-    bounds: List[List[float]] = [[] for _ in range(12)]  # cpu lo/hi, memory, disk, gpu count, gpu memory, gpu total
-    max_price, spot, vendor, cc_min, name_any = [], [], [], [], []
-    src_mask, off_mask, excl, flag_req, flag_forbid, blocks, status_mask = [], [], [], [], [], [], []
-    fleet_any, fleet_ids, inst_any, inst_ids = [], [], [], []
-    dstack_bit = 1 << BACKEND_CODES["dstack"]
-    pool_forbid = FLAG_UNREACHABLE | FLAG_BLOCKS_UNKNOWN
 
-    class Csr:
-        def __init__(self, lookup: Dict[Any, int]):
-            self.lookup, self.any, self.ptr, self.ids = lookup, [], [0], []
+    def cached(f: JobFilter):
+        c = f.__dict__.get("_scalars")
+        if c is None:
+            c = f.__dict__["_scalars"] = _filter_scalars(f)
+        return c
 
-        def put(self, values: Optional[Sequence[Any]]) -> None:
-            self.any.append(values is None)
-            if values is not None:
-                get = self.lookup.get
-                self.ids.extend(get(v, -1) for v in values)
-            self.ptr.append(len(self.ids))
+    per_filter = [cached(f) for f in filters]
+    rows = [c[0] for c in per_filter]
 
-        def arrays(self):
-            return np.array(self.any, bool), np.array(self.ptr, np.int64), np.array(self.ids, np.int64)
+    def csr(values: List[Optional[Sequence[Any]]], lookup: Dict[Any, int]):
+        """Per job a set of dictionary ids (-1: a value this table does not hold), or "any"."""
+        any_ = np.array([v is None for v in values], bool)
+        if any_.all():
+            return any_, np.zeros(j + 1, np.int64), np.zeros(0, np.int64)
+        ptr, ids, get = [0], [], lookup.get
+        for v in values:
+            if v is not None:
+                ids.extend([get(x, -1) for x in v])
+            ptr.append(len(ids))
+        return any_, np.array(ptr, np.int64), np.array(ids, np.int64)
 
-    gname = Csr(names)
-    region = Csr(cols["region"].lookup)
-    itype = Csr(cols["itype"].lookup)
-    zone = Csr(cols["zone"].lookup) if table.is_pool else None
-    fleet_lookup = cols["fleet"].lookup if table.is_pool else {}
-    name_lookup = cols["name"].lookup if table.is_pool else {}
+    gn_any, gn_ptr, gn_ids = csr([c[1] for c in per_filter], table.gpu_dict["names"])
+    r_any, r_ptr, r_ids = csr([f.regions for f in filters], cols["region"].lookup)
+    t_any, t_ptr, t_ids = csr([f.instance_types for f in filters], cols["itype"].lookup)
+    if table.is_pool:
+        pool = [f.shared is not None for f in filters]
+        z_any, z_ptr, z_ids = csr([f.zones if p else None for f, p in zip(filters, pool)], cols["zone"].lookup)
+        fleet_get, name_get = cols["fleet"].lookup.get, cols["name"].lookup.get
+        fleet_any = [not p or f.any_fleet for f, p in zip(filters, pool)]
+        fleet_ids = [-1 if a else fleet_get(f.fleet_id, -1) for f, a in zip(filters, fleet_any)]
+        inst_any = [not p or f.instance_name is None for f, p in zip(filters, pool)]
+        inst_ids = [-1 if a else name_get(f.instance_name, -1) for f, a in zip(filters, inst_any)]
 
-    for f in filters:
-        q = f.query
-        if q.min_price is not None:
-            raise ValueError("min_price is not part of the dstack path (offers.py:117 sets max_price only)")
-        if q.max_compute_capability is not None:
-            raise ValueError("max_compute_capability is never set by dstack (offers.py:143-144)")
-        max_price.append(nan if q.max_price is None else q.max_price)
-        spot.append(-1 if q.spot is None else (1 if q.spot else 0))
-        for k, v in enumerate((q.min_cpu, q.max_cpu, q.min_memory, q.max_memory, q.min_disk_size, q.max_disk_size,
-                               q.min_gpu_count, q.max_gpu_count, q.min_gpu_memory, q.max_gpu_memory,
-                               q.min_total_gpu_memory, q.max_total_gpu_memory)):
-            bounds[k].append(nan if v is None else float(v))
-        vendor.append(vendor_code(q.gpu_vendor))
-        cc = q.min_compute_capability
-        cc_min.append(-1 if cc is None else int(cc[0]) * 1000 + int(cc[1]))
-        name_any.append(q.gpu_name is None)
-        gname.put(None if q.gpu_name is None else [n.lower() for n in q.gpu_name])
-        if f.backend_types is not None:
-            m = 0
-            for b in f.backend_types:
-                m |= 1 << backend_code(b)
-            off_mask.append(m)
-            src_mask.append(m | (dstack_bit if f.keep_dstack_backend else 0))
-        else:
-            off_mask.append(0xFFFFFFFF)
-            src_mask.append(0xFFFFFFFF)
-        excl.append(f.exclude_not_available)
-        region.put(f.regions)
-        itype.put(f.instance_types)
-        req = FLAG_AUTO_DIVISIBLE if f.require_auto_divisible else 0
-        forbid = 0
-        blocks.append(f.blocks)
-        st_mask, fl_any, fl_id, in_any, in_id = 0xFF, True, -1, True, -1
-        if f.shared is not None:  # pool filter (pools.py:460,484-488)
-            forbid |= pool_forbid
-            if f.shared:
-                req |= FLAG_SHARED
-            else:
-                forbid |= FLAG_SHARED
-            if f.require_offer:
-                forbid |= FLAG_NO_OFFER
-            if f.status is not None:
-                st = f.status
-                st_mask = 1 << STATUS_CODES[st.value if hasattr(st, "value") else str(st)]
-            if not f.any_fleet:
-                fl_any, fl_id = False, fleet_lookup.get(f.fleet_id, -1)
-            if f.instance_name is not None:
-                in_any, in_id = False, name_lookup.get(f.instance_name, -1)
-            zone.put(f.zones)
-        elif zone is not None:
-            zone.put(None)
-        flag_req.append(req)
-        flag_forbid.append(forbid)
-        status_mask.append(st_mask)
-        fleet_any.append(fl_any)
-        fleet_ids.append(fl_id)
-        inst_any.append(in_any)
-        inst_ids.append(in_id)
-
-    pair = lambda k: np.array([bounds[2 * k], bounds[2 * k + 1]], dtype=np.float64).T.copy() if j else np.zeros((0, 2))
-    gn_any, gn_ptr, gn_ids = gname.arrays()
-    r_any, r_ptr, r_ids = region.arrays()
-    t_any, t_ptr, t_ids = itype.arrays()
-    blocks_a = np.array(blocks, np.int64)
+    a = np.array(rows, dtype=np.float64).reshape(j, 23)
+    pair = lambda k: np.ascontiguousarray(a[:, 2 + 2 * k:4 + 2 * k])
+    blocks_a = a[:, 21].astype(np.int64)
     jc = JobColumns(
-        n=j, max_price=np.array(max_price, np.float64), spot=np.array(spot, np.int8), cpu=pair(0), memory=pair(1),
-        disk=pair(2), gpu_count=pair(3), gpu_memory=pair(4), gpu_total=pair(5), gpu_vendor=np.array(vendor, np.int8),
-        cc_min=np.array(cc_min, np.int64), gpu_name_any=np.array(name_any, bool), gpu_name_ptr=gn_ptr,
-        gpu_name_ids=gn_ids, src_backend_mask=np.array(src_mask, np.uint32), off_backend_mask=np.array(off_mask, np.uint32),
-        exclude_not_available=np.array(excl, bool), region_any=r_any, region_ptr=r_ptr, region_ids=r_ids,
-        itype_any=t_any, itype_ptr=t_ptr, itype_ids=t_ids, flag_req=np.array(flag_req, np.uint16),
-        flag_forbid=np.array(flag_forbid, np.uint16), status_mask=np.array(status_mask, np.uint8),
+        n=j, max_price=np.ascontiguousarray(a[:, 0]), spot=a[:, 1].astype(np.int8), cpu=pair(0), memory=pair(1),
+        disk=pair(2), gpu_count=pair(3), gpu_memory=pair(4), gpu_total=pair(5), gpu_vendor=a[:, 14].astype(np.int8),
+        cc_min=a[:, 15].astype(np.int64), gpu_name_any=gn_any, gpu_name_ptr=gn_ptr,
+        gpu_name_ids=gn_ids, src_backend_mask=a[:, 17].astype(np.uint32), off_backend_mask=a[:, 16].astype(np.uint32),
+        exclude_not_available=a[:, 18] != 0, region_any=r_any, region_ptr=r_ptr, region_ids=r_ids,
+        itype_any=t_any, itype_ptr=t_ptr, itype_ids=t_ids, flag_req=a[:, 19].astype(np.uint16),
+        flag_forbid=a[:, 20].astype(np.uint16), status_mask=a[:, 22].astype(np.uint8),
         blocks=blocks_a if blocks_a.any() else None,
     )
     if table.is_pool:
-        z_any, z_ptr, z_ids = zone.arrays()
         jc.fleet_any, jc.fleet_ids = np.array(fleet_any, bool), np.array(fleet_ids, np.int64)
         jc.name_any, jc.name_ids = np.array(inst_any, bool), np.array(inst_ids, np.int64)
         jc.zone_any, jc.zone_ptr, jc.zone_ids = z_any, z_ptr, z_ids

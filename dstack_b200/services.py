@@ -182,6 +182,15 @@ async def get_offers_by_requirements(
 # ---------------------------------------------------------------------------- batched, device-resident layer
 
 
+class _ProfileView:
+    """The three profile fields ``derive_backend_types_and_regions`` reads, without touching the profile."""
+
+    __slots__ = ("backends", "regions", "reservation")
+
+    def __init__(self, backends: Any, regions: Any, reservation: Any):
+        self.backends, self.regions, self.reservation = backends, regions, reservation
+
+
 def job_filter(profile: Any, requirements: Any, *, backend_types_of_project: Optional[Sequence[Any]] = None,
                exclude_not_available: bool = False, multinode: bool = False,
                master_job_provisioning_data: Optional[Any] = None, volumes: Optional[List[List[Any]]] = None,
@@ -192,11 +201,7 @@ def job_filter(profile: Any, requirements: Any, *, backend_types_of_project: Opt
     if backends is not None and len(backends) == 1 and M.BackendType.DSTACK in backends:
         backends = None
 
-    class _P:  # view of the profile without mutating it
-        pass
-
-    p = _P()
-    p.backends, p.regions, p.reservation = backends, profile.regions, profile.reservation
+    p = _ProfileView(backends, profile.regions, profile.reservation)
     backend_types, regions = derive_backend_types_and_regions(
         p, multinode=multinode, master_job_provisioning_data=master_job_provisioning_data, volumes=volumes,
         privileged=privileged, instance_mounts=instance_mounts)
