@@ -137,7 +137,10 @@ class ShardedMatcher:
         return pack_jobs(self.table, jobs)
 
     def prepare(self, packed: PackedJobs, k: int):
-        """Allocate the device buffers of a batch shape once (records stay resident)."""
+        """Allocate the device buffers of a batch shape once (records stay resident).  The cached
+        layout points at this matcher's per-context remap buffers (columns with more than 1024
+        entries): ``self.matcher`` is private to this object and must not serve other calls while
+        a batch is prepared -- a later ``_layout`` on the same column would replace the remap."""
         torch = self.torch
         j = len(packed.records)
         dev = self.dev
