@@ -327,3 +327,32 @@ def test_pool_index_refresh_patches_rows_in_place(matcher):
         assert len(want) == len(got) and all(rows[i] is w for i, w in zip(got, want))
     finally:
         index.close()
+
+
+def test_job_columns_keeps_the_table_independent_numbers_on_the_filter():
+    """``job_columns`` computes a filter's table-independent numbers once and keeps them on the
+    object (a pending job is matched again every pass): the second use must give the same columns
+    as the first, and ``dataclasses.replace`` must give a filter that is computed afresh."""
+    import dataclasses
+
+    from dstack_b200.encode import encode_table
+    from dstack_b200.ingest import job_columns
+    from workloads import synth
+
+    cat = synth.make_catalog(2_000, seed=5, n_shapes=64)
+    table = encode_table(cat.columns)
+    req = M.Requirements(resources=M.ResourcesSpec(cpu="4..", memory="16GB..", gpu="24GB..:1..2"), max_price=3.5,
+                         spot=False)
+    f = S.job_filter(M.Profile(name="p", regions=["eu-west-1"]), req, exclude_not_available=True)
+    first = job_columns(table, [f])
+    assert "_scalars" in f.__dict__
+    again = job_columns(table, [f])
+    for name, a in vars(first).items():
+        b = getattr(again, name)
+        if isinstance(a, np.ndarray):
+            assert np.array_equal(a, b, equal_nan=a.dtype.kind == "f"), name
+        else:
+            assert a == b or (a is None and b is None), name
+    g = dataclasses.replace(f, exclude_not_available=False)
+    assert "_scalars" not in g.__dict__
+    assert not job_columns(table, [g]).exclude_not_available[0] and first.exclude_not_available[0]
