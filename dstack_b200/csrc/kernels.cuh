@@ -160,30 +160,49 @@ struct BuildParams {
 #endif
 
 // Pieces of the row axis (see the header comment); shared by k_match and k_extract.  Every warp
-// of a piece gets the same whole number of windows (wpw), counted from the start of the piece's
+// of a piece gets the same whole number of windows, counted from the start of the piece's
 // segment, so the eight warps of a unit reach its closing barrier together and only the last
-// piece of a segment has short or empty shares.
+// piece of a segment has short or empty shares.  A segment is cut into coarse pieces (wpw windows
+// per warp) followed by fine ones (wpw_f): units are drawn in row order, so the last units of a
+// launch are short and the CTAs run out of work nearly together, while most rows are covered by
+// long units that stage their table once for many windows.
 struct Pieces {
   uint32_t n_groups;
   uint32_t n_blocks;     // 32-row blocks of the table
   uint32_t split_block;  // first block of the second segment
   uint32_t pa, pb;       // pieces in the first / second segment
-  uint32_t wpw;          // windows per warp
+  uint32_t ca, cb;       // of which coarse (the first ca / cb of the segment)
+  uint32_t wpw;          // windows per warp in a coarse piece
+  uint32_t wpw_f;        // ... in a fine piece (<= wpw)
   __host__ __device__ uint32_t per_group() const { return pa + pb; }
   __host__ __device__ uint32_t count() const { return n_groups * (pa + pb); }
   __host__ __device__ static uint32_t windows(uint32_t blocks) { return (blocks + WIN_BLOCKS - 1) / WIN_BLOCKS; }
-  // pieces needed for `blocks` blocks when every warp takes wpw windows
-  __host__ __device__ static uint32_t pieces_for(uint32_t blocks, uint32_t wpw) {
+  // pieces needed for `wins` windows when every warp takes wpw of them
+  __host__ __device__ static uint32_t pieces_for_windows(uint32_t wins, uint32_t wpw) {
     const uint32_t per_piece = wpw * MATCH_WARPS;
-    return (windows(blocks) + per_piece - 1) / per_piece;
+    return (wins + per_piece - 1) / per_piece;
+  }
+  // Cut a segment of `blocks` blocks: the last `fine_windows` windows (rounded up to whole coarse
+  // pieces' worth of remainder) in fine pieces.  Returns the piece count, sets `coarse`.
+  __host__ uint32_t cut(uint32_t blocks, uint32_t fine_windows, uint32_t& coarse) const {
+    const uint32_t wins = windows(blocks);
+    const uint32_t fine = fine_windows < wins ? fine_windows : wins;
+    coarse = (wins - fine) / (wpw * MATCH_WARPS);
+    return coarse + pieces_for_windows(wins - coarse * wpw * MATCH_WARPS, wpw_f);
   }
   // blocks [b0, b1) of warp `warp` of piece `pos`
   __host__ __device__ void warp_blocks(uint32_t pos, uint32_t warp, uint32_t& b0, uint32_t& b1) const {
-    uint32_t seg_lo = 0, seg_hi = split_block, i = pos;
-    if (pos >= pa) { seg_lo = split_block; seg_hi = n_blocks; i = pos - pa; }
-    const unsigned long long w0 = ((unsigned long long)i * MATCH_WARPS + warp) * wpw;  // first window
+    uint32_t seg_lo = 0, seg_hi = split_block, i = pos, c = ca;
+    if (pos >= pa) { seg_lo = split_block; seg_hi = n_blocks; i = pos - pa; c = cb; }
+    unsigned long long w0, len = wpw;  // first window, windows
+    if (i < c) {
+      w0 = ((unsigned long long)i * MATCH_WARPS + warp) * wpw;
+    } else {
+      w0 = (unsigned long long)c * MATCH_WARPS * wpw + ((unsigned long long)(i - c) * MATCH_WARPS + warp) * wpw_f;
+      len = wpw_f;
+    }
     const unsigned long long x0 = seg_lo + w0 * WIN_BLOCKS;
-    const unsigned long long x1 = x0 + (unsigned long long)wpw * WIN_BLOCKS;
+    const unsigned long long x1 = x0 + len * WIN_BLOCKS;
     b0 = x0 < seg_hi ? (uint32_t)x0 : seg_hi;
     b1 = x1 < seg_hi ? (uint32_t)x1 : seg_hi;
   }

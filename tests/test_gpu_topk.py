@@ -84,6 +84,7 @@ def test_long_slots_with_many_windows(monkeypatch):
     from dstack_b200.engine import Matcher
 
     monkeypatch.setenv("DSM_UNITS_PER_CTA", "1")  # tuning knobs are read when a context is created
+    monkeypatch.setenv("DSM_FINE_PCT", "0")       # no short units at the end of the row axis: long slots only
     matcher = Matcher(0)
     cat = synth.make_catalog(2_000_000, seed=71, n_shapes=1024)
     table = encode_table(cat.columns)
