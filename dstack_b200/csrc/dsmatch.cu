@@ -293,12 +293,14 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
   // first) go out in units a quarter as long, about two of them per resident CTA and at most 30 %
   // of the table, so that the CTAs finish nearly together while most rows are covered by long
   // units: 4096 jobs x 1 M rows 0.141 -> 0.134 ms, 16384 jobs x 8 M rows 3.47 -> 3.33 ms.  Fine
-  // units get longer if they alone would push a job past the 512 slots k_extract keeps in registers.
+  // units get longer if they alone would push a job past the slot count of its k_extract variant.
   pl.pc.wpw_f = ctx->force_wpw_f ? ctx->force_wpw_f : (pl.pc.wpw >= 4u ? std::max(2u, pl.pc.wpw / 4u) : pl.pc.wpw);
   if (pl.pc.wpw_f > pl.pc.wpw) pl.pc.wpw_f = pl.pc.wpw;
   const uint32_t wins_b = Pieces::windows(b_blocks);
-  const bool coarse_fits = (Pieces::pieces_for_windows(Pieces::windows(a_blocks), pl.pc.wpw) +
-                            Pieces::pieces_for_windows(wins_b, pl.pc.wpw)) * MATCH_WARPS <= 512u;
+  // k_extract: counts in registers up to 512 slots, a warp per job below 1024, else a CTA per job
+  const uint32_t coarse_slots = (Pieces::pieces_for_windows(Pieces::windows(a_blocks), pl.pc.wpw) +
+                                 Pieces::pieces_for_windows(wins_b, pl.pc.wpw)) * MATCH_WARPS;
+  const uint32_t slot_limit = coarse_slots <= 512u ? 512u : (coarse_slots < 1024u ? 1023u : 0xFFFFFFFFu);
   for (;;) {
     unsigned long long fine_total;
     if (ctx->fine_pct >= 0) {
@@ -311,7 +313,7 @@ static int make_plan(const dsm_ctx* ctx, const dsm_table* t, const dsm_layout* L
     const uint32_t fine_a = (uint32_t)(fine_total - fine_b);
     pl.pc.pa = pl.pc.cut(a_blocks, fine_a, pl.pc.ca);
     pl.pc.pb = pl.pc.cut(b_blocks, fine_b, pl.pc.cb);
-    if (pl.pc.per_group() * MATCH_WARPS <= 512u || !coarse_fits || pl.pc.wpw_f >= pl.pc.wpw || ctx->force_wpw_f) break;
+    if (pl.pc.per_group() * MATCH_WARPS <= slot_limit || pl.pc.wpw_f >= pl.pc.wpw || ctx->force_wpw_f) break;
     ++pl.pc.wpw_f;
   }
   pl.slots = pl.pc.per_group() * MATCH_WARPS;

@@ -186,6 +186,7 @@ struct Pieces {
   // pieces' worth of remainder) in fine pieces.  Returns the piece count, sets `coarse`.
   __host__ uint32_t cut(uint32_t blocks, uint32_t fine_windows, uint32_t& coarse) const {
     const uint32_t wins = windows(blocks);
+    if (fine_windows == 0u || wpw_f == wpw) return coarse = pieces_for_windows(wins, wpw);  // coarse pieces only
     const uint32_t fine = fine_windows < wins ? fine_windows : wins;
     coarse = (wins - fine) / (wpw * MATCH_WARPS);
     return coarse + pieces_for_windows(wins - coarse * wpw * MATCH_WARPS, wpw_f);

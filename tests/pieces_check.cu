@@ -15,7 +15,7 @@ int main() {
     pc.n_blocks = a_blocks + b_blocks; pc.split_block = a_blocks;
     pc.wpw = 1 + rand() % 40; pc.wpw_f = 1 + rand() % pc.wpw;
     uint32_t wins_b = Pieces::windows(b_blocks), wins_a = Pieces::windows(a_blocks);
-    uint32_t fine_total = rand() % (wins_a + wins_b + 5);
+    uint32_t fine_total = rand() % 5 == 0 ? 0 : rand() % (wins_a + wins_b + 5);
     uint32_t fine_b = std::min(wins_b, fine_total), fine_a = fine_total - fine_b;
     pc.pa = pc.cut(a_blocks, fine_a, pc.ca);
     pc.pb = pc.cut(b_blocks, fine_b, pc.cb);

@@ -2,14 +2,5 @@
 cd "$GRAFT_REPO_ROOT"
 run() { echo "== $*"; env "${@:4}" python tools/time_match.py $1 $2 $3 --check 16 2>&1 | grep -v "^columns" | tail -3; }
 run 4096 1048576 16 X=1
-run 4096 1048576 16 DSM_FINE_PCT=0
-run 4096 1048576 16 DSM_FINE_PCT=30
-run 4096 1048576 16 DSM_FINE_PCT=12
-run 4096 1048576 16 DSM_WPW_FINE=3
 run 4096 4194304 16 X=1
-run 4096 4194304 16 DSM_FINE_PCT=0
 run 16384 8388608 16 X=1
-run 16384 8388608 16 DSM_FINE_PCT=0
-run 16384 8388608 16 DSM_FINE_PCT=10
-run 256 10000000 16 X=1
-run 256 10000000 16 DSM_FINE_PCT=0
