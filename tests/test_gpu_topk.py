@@ -286,3 +286,33 @@ def test_largest_column_with_fewer_copies(matcher):
     _check(matcher, cat, sj, 16)
 
 
+
+
+def test_every_layout_of_one_batch_gives_the_same_answer(matcher):
+    """One catalog, one batch of jobs, four layouts: cpu and memory as one paired column or as two
+    range columns, jobs evaluated in the grouped order (whole groups skip trailing columns) or as
+    given.  All four must return the oracle's rows, counts and max-price rows."""
+    cat = synth.make_catalog(60_000, seed=95, n_shapes=1024)
+    sj = synth.make_jobs(cat, encode_table(cat.columns), 700, seed=96)
+    want = columnar.topk(cat.columns, sj.columns, 16)
+    seen = []
+    for pair in (None, False):
+        table = encode_table(cat.columns, pair_columns=pair)
+        assert (table.pair_entries is not None) == (pair is None)
+        dt = matcher.upload(table)
+        try:
+            for ordered in (True, False):
+                packed = pack_jobs(table, sj.columns)
+                assert packed.order is not None
+                if not ordered:
+                    packed.order = None
+                idx, cnt, mx = matcher.topk_rows(dt, packed, 16)
+                src = np.where(idx == NO_ROW, -1, table.perm[np.minimum(idx, table.n_rows - 1)]).astype(np.int64)
+                price = np.where(mx == NO_ROW, np.nan, table.price[np.minimum(mx, table.n_rows - 1)])
+                assert np.array_equal(src, want.index), (pair, ordered)
+                assert np.array_equal(cnt.astype(np.int64), want.count), (pair, ordered)
+                assert np.array_equal(np.nan_to_num(price, nan=-1.0), np.nan_to_num(want.max_price, nan=-1.0))
+                seen.append((src, cnt.copy()))
+        finally:
+            dt.close()
+    assert len(seen) == 4 and all(np.array_equal(seen[0][0], s) and np.array_equal(seen[0][1], c) for s, c in seen)
